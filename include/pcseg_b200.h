@@ -1,0 +1,200 @@
+/*
+ * pcseg_b200.h -- C ABI of the B200-native geometric segmentation hot path.
+ *
+ * Drop-in boundary for the hot path of theteamatx/x-edr-pointcloud-segmentation
+ * ("ps/" = pointcloud_segmentation/ in the reference tree).  Plain pointers and
+ * sizes only.  Clouds use the reference's boundary layout (ps/cloud.h:37-41,74;
+ * ps/multichannel_cloud_test.cc:209-218): column-major grid,
+ * index = col * rows + row, AoS float32 xyz (12 B per point), NaN = invalid,
+ * int32 labels with the sentinels of ps/segmentation.h:36-45.
+ *
+ * Every data pointer may be a HOST pointer or a DEVICE pointer on the context's
+ * GPU (detected with cudaPointerGetAttributes); outputs are written to wherever
+ * the caller's pointer lives.  All entry points return 0 on success; a nonzero
+ * status names the reference CHECK that would have aborted the process
+ * (ps/planar_region.h:257-268, ps/cluster_region.h:152-159,
+ * ps/mean_shift_segmentation.h:212-215) or a CUDA / capacity error.  There is
+ * no CPU fallback: without a usable CUDA device pcseg_create fails.
+ */
+#ifndef PCSEG_B200_H_
+#define PCSEG_B200_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct pcseg_ctx pcseg_ctx;
+typedef struct pcseg_regions pcseg_regions;
+typedef struct pcseg_batch pcseg_batch;
+
+enum {
+  PCSEG_OK = 0,
+  PCSEG_ERR_NULL = 1,        /* CHECK(ptr) */
+  PCSEG_ERR_DIMS = 2,        /* CHECK_EQ on rows/cols, CHECK_GT(rows, 1) */
+  PCSEG_ERR_CONFIG = 3,      /* config value the reference turns into UB (quirk Q8) */
+  PCSEG_ERR_CUDA = 4,        /* CUDA runtime error (see pcseg_last_error) */
+  PCSEG_ERR_CAPACITY = 5,    /* an internal per-frame buffer overflowed */
+  PCSEG_ERR_UNSUPPORTED = 6, /* documented limit of this implementation */
+  PCSEG_ERR_SEED_RANGE = 7   /* seed index outside [0, rows*cols) */
+};
+
+/* ps/algorithms.h:313-322 ComputeNormalsParams */
+typedef struct {
+  float min_neighbor_distance;      /* 0.1 */
+  float max_neighbor_distance;      /* 1.0 */
+  int include_diagonal_neighbors;   /* 1   */
+  int min_num_support_neighbors;    /* 4   */
+} pcseg_normals_params;
+
+/* ps/region_segmentation_config.proto:42-72 PlanarRegionConfigProto with the
+ * defaults of ps/planar_region.h:93-121 already applied by the caller. */
+typedef struct {
+  float max_plane_distance;               /* 0.05 */
+  float min_region_area;                  /* 0.05 */
+  int min_region_inliers;                 /* 5    */
+  int plane_model_reestimation_period;    /* 30   */
+  float discontinuity_min_range;          /* 1.2  */
+  float discontinuity_max_range;          /* 4.0  */
+  float discontinuity_normal_angle_diff;  /* 5.0  */
+  float discontinuity_z_diff;             /* 0.05 */
+  float discontinuity_z_ratio;            /* 0.7  */
+} pcseg_planar_config;
+
+/* ps/region_segmentation_config.proto:22-39 ClusterRegionConfigProto with the
+ * defaults of ps/cluster_region.h:53-63 applied. */
+typedef struct {
+  int min_region_inliers;             /* 7   */
+  float squared_distance_threshold;   /* 1.0 */
+  int half_search_window;             /* 1   (<= 3 supported) */
+} pcseg_cluster_config;
+
+void pcseg_default_normals_params(pcseg_normals_params*);
+void pcseg_default_planar_config(pcseg_planar_config*);
+void pcseg_default_cluster_config(pcseg_cluster_config*);
+
+/* One context per GPU; calls on one context are serialised on its stream. */
+int pcseg_create(int device, pcseg_ctx** out);
+void pcseg_destroy(pcseg_ctx*);
+const char* pcseg_status_string(int status);
+const char* pcseg_last_error(const pcseg_ctx*);
+/* Number of kernels this context has launched so far (bench.py gpu_launches). */
+long long pcseg_launch_count(const pcseg_ctx*);
+/* The CUDA stream (cudaStream_t as void*) the context launches on. */
+void* pcseg_stream(const pcseg_ctx*);
+
+/* Replaces ps/segmentation.cc:21-26 PrepareUnlabeledLabels: fill with -1. */
+int pcseg_prepare_unlabeled_labels(pcseg_ctx*, int* labels, int n);
+
+/* Replaces ps/algorithms.h:329-375 ComputeNormalsOrganized (both overloads;
+ * pass the full range for the second).  Only the translation of
+ * point_cloud_pose_sensor is used by the reference (:355).  normals is in/out:
+ * only cells inside [row_begin,row_end) x [col_begin,col_end) are written.
+ * curvature (nullable) receives PlaneEstimator::Curvature() per point
+ * (ps/plane_estimator.cc:106-111; extension output, NaN where the normal is). */
+int pcseg_normals_organized(pcseg_ctx*, const float* xyz, int rows, int cols,
+                            const double sensor_translation[3],
+                            const pcseg_normals_params* params, int row_begin,
+                            int row_end, int col_begin, int col_end,
+                            float* normals, float* curvature);
+
+/* Replaces ps/segmentation.h:239-292 SegmentRegions<PlanarRegion<>> with
+ * ps/planar_region.h:123-268 as the region model.  robot_q_xyzw is the
+ * quaternion of InputData::robot_pose_point_cloud (only used for the
+ * discontinuity side output, ps/planar_region.h:390).  labels is in/out.
+ * Seeds are consumed back to front (ps/segmentation.h:254-256). */
+int pcseg_segment_planar(pcseg_ctx*, const float* xyz, const float* normals,
+                         int rows, int cols, const float robot_q_xyzw[4],
+                         const int* seeds, int n_seeds,
+                         const pcseg_planar_config* cfg, int initial_id_offset,
+                         int* labels, pcseg_regions** out);
+
+/* Replaces SegmentRegions<ClusterRegion<>> (ps/cluster_region.h:47-176). */
+int pcseg_segment_cluster(pcseg_ctx*, const float* xyz, int rows, int cols,
+                          const int* seeds, int n_seeds,
+                          const pcseg_cluster_config* cfg, int initial_id_offset,
+                          int* labels, pcseg_regions** out);
+
+/* Replaces the iteration phase of ps/mean_shift_segmentation.h:217-260.
+ * modes_out: 8 floats per cloud cell {mode xyz, index row, index col,
+ * intensity, valid, is_seed}; cells that are not seeds have is_seed = 0. */
+int pcseg_mean_shift_modes(pcseg_ctx*, const float* xyz, int rows, int cols,
+                           const int* labels, int iterations, float* modes_out);
+
+/* Replaces ps/mean_shift_segmentation.h:207-330 SlidingMeanShift (iteration
+ * phase + sort + growth).  sort_mode 0 = the reference's std::sort permutation
+ * (libstdc++ introsort replayed on (intensity, seed order) keys), 1 = stable. */
+int pcseg_mean_shift(pcseg_ctx*, const float* xyz, int rows, int cols,
+                     const pcseg_cluster_config* cfg, int iterations,
+                     int initial_region_id_offset, int sort_mode, int* labels,
+                     pcseg_regions** out);
+
+/* Replaces ps/segmentation.h:190-230 FindSeedPointsFromPlaneSupport (quirk Q1
+ * reproduced literally).  Returns the number of seeds in *n_out. */
+int pcseg_seeds_plane_support(pcseg_ctx*, const float* xyz, const float* normals,
+                              int rows, int cols, int neighborhood_size,
+                              float max_plane_distance, int min_num_support,
+                              int* seeds_out, int cap, int* n_out);
+
+/* ---- Batched pipeline (extension: the reference has no batch entry point;
+ * a caller looping ComputeNormalsOrganized -> SegmentRegions<PlanarRegion> ->
+ * SegmentRegions<ClusterRegion> over independent frames binds this instead).
+ * Frames are contiguous: xyz[f][rows*cols][3]. ---- */
+enum {
+  PCSEG_SEEDS_ALL_DESCENDING = 0, /* seeds[k] = N-1-k, as ps/clustering_test.cc:57-59 */
+  PCSEG_SEEDS_PLANE_SUPPORT = 1,  /* FindSeedPointsFromPlaneSupport defaults, on device */
+  PCSEG_SEEDS_EXPLICIT = 2        /* caller-provided list shared by all frames */
+};
+typedef struct {
+  pcseg_normals_params normals;
+  pcseg_planar_config planar;
+  pcseg_cluster_config cluster;
+  double sensor_translation[3];
+  float robot_q_xyzw[4];
+  int planar_seed_mode;
+  const int* planar_seeds; /* PCSEG_SEEDS_EXPLICIT only */
+  int n_planar_seeds;
+  int run_cluster_stage;   /* seeds all descending, id offset = #planes of the frame */
+} pcseg_pipeline_params;
+
+int pcseg_batch_create(pcseg_ctx*, int n_frames, int rows, int cols,
+                       pcseg_batch** out);
+void pcseg_batch_destroy(pcseg_batch*);
+/* normals_out / labels_out nullable (results then stay on the device only). */
+int pcseg_batch_run(pcseg_batch*, const float* xyz,
+                    const pcseg_pipeline_params* params, float* normals_out,
+                    int* labels_out);
+/* Per-frame counters after a run: {n_planar, n_cluster, planar_inliers,
+ * cluster_inliers, boundary_len, error_flags, grow_steps, refits}. */
+int pcseg_batch_frame_stats(pcseg_batch*, int* stats8_per_frame);
+/* Materialises one frame's regions (kind 0 = planar, 1 = cluster). */
+int pcseg_batch_regions(pcseg_batch*, int frame, int kind, pcseg_regions** out);
+/* Device pointers of the batch's resident results (labels int32[F*N],
+ * normals float[F*N*3]); valid until pcseg_batch_destroy. */
+int* pcseg_batch_device_labels(pcseg_batch*);
+float* pcseg_batch_device_normals(pcseg_batch*);
+
+/* ---- Result accessors (host pointers valid until pcseg_regions_free).
+ * Mirror PlanarRegion's accessors (ps/planar_region.h:427-450) and
+ * ClusterRegion's (ps/cluster_region.h:161-168) as CSR arrays. ---- */
+int pcseg_regions_count(const pcseg_regions*);
+const int* pcseg_regions_inlier_offsets(const pcseg_regions*);        /* n+1 */
+const int* pcseg_regions_inlier_indices(const pcseg_regions*);
+const int* pcseg_regions_label_ids(const pcseg_regions*);             /* n   */
+const int* pcseg_regions_seed_indices(const pcseg_regions*);          /* n   */
+const float* pcseg_regions_planes(const pcseg_regions*);              /* 4n: normal, offset */
+const float* pcseg_regions_centroids(const pcseg_regions*);           /* 3n  */
+const float* pcseg_regions_areas(const pcseg_regions*);               /* n   */
+const float* pcseg_regions_estimators(const pcseg_regions*);          /* 10n: acc[6], sum xyz, weight */
+const int* pcseg_regions_boundary_offsets(const pcseg_regions*);      /* n+1 */
+const int* pcseg_regions_boundary_indices(const pcseg_regions*);
+const int* pcseg_regions_discontinuous_offsets(const pcseg_regions*); /* n+1 */
+const int* pcseg_regions_discontinuous_indices(const pcseg_regions*); /* sorted set */
+const int* pcseg_regions_hull_offsets(const pcseg_regions*);          /* n+1 (points) */
+const float* pcseg_regions_hull_points(const pcseg_regions*);         /* xyz */
+const float* pcseg_regions_seed_points(const pcseg_regions*);         /* 3n (mean shift) */
+void pcseg_regions_free(pcseg_regions*);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PCSEG_B200_H_ */

@@ -1,0 +1,246 @@
+// pcseg_math.cuh -- device arithmetic shared by all kernels.
+//
+// Everything here is fp32, round-to-nearest, compiled with -fmad=false so that
+// no multiply-add is contracted (the reference binary is baseline x86-64,
+// .bazelrc:1).  Reduction orders follow Eigen 3.4.0's fixed-size unroller:
+// sum/dot/squaredNorm/trace of 3 elements = e0 + (e1 + e2).
+#pragma once
+#include <cfloat>
+#include <cmath>
+#include <cuda_runtime.h>
+
+namespace pcseg {
+
+struct V3 {
+  float x, y, z;
+};
+
+__device__ __forceinline__ V3 ld3(const float* __restrict__ p, int idx) {
+  const float* q = p + 3 * (size_t)idx;
+  return V3{__ldg(q), __ldg(q + 1), __ldg(q + 2)};
+}
+__device__ __forceinline__ V3 vsub(V3 a, V3 b) { return V3{a.x - b.x, a.y - b.y, a.z - b.z}; }
+__device__ __forceinline__ V3 vadd(V3 a, V3 b) { return V3{a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ V3 vscale(float s, V3 a) { return V3{s * a.x, s * a.y, s * a.z}; }
+__device__ __forceinline__ V3 vdiv(V3 a, float s) { return V3{a.x / s, a.y / s, a.z / s}; }
+__device__ __forceinline__ V3 vneg(V3 a) { return V3{-a.x, -a.y, -a.z}; }
+__device__ __forceinline__ float vdot(V3 a, V3 b) { return a.x * b.x + (a.y * b.y + a.z * b.z); }
+__device__ __forceinline__ float vsqn(V3 a) { return a.x * a.x + (a.y * a.y + a.z * a.z); }
+__device__ __forceinline__ V3 vcross(V3 a, V3 b) {
+  return V3{a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x};
+}
+__device__ __forceinline__ bool finite1(float v) { return fabsf(v) <= FLT_MAX; }  // false for NaN/Inf
+__device__ __forceinline__ bool vfinite(V3 a) { return finite1(a.x) && finite1(a.y) && finite1(a.z); }
+__device__ __forceinline__ bool vhasnan(V3 a) { return (a.x != a.x) || (a.y != a.y) || (a.z != a.z); }
+
+// libm float trig of the reference (Eigen computeDirect: atan2f, cosf, sinf;
+// ps/planar_region.h:399 acosf) evaluated in double and rounded once.
+__device__ __forceinline__ float cr_atan2f(float y, float x) { return (float)atan2((double)y, (double)x); }
+__device__ __forceinline__ float cr_cosf(float x) { return (float)cos((double)x); }
+__device__ __forceinline__ float cr_sinf(float x) { return (float)sin((double)x); }
+__device__ __forceinline__ float cr_acosf(float x) { return (float)acos((double)x); }
+
+// Hyperplane(n, e): offset = -n.dot(e); absDistance = |n.dot(p) + offset|
+struct Plane {
+  V3 n;
+  float d;
+};
+__device__ __forceinline__ Plane make_plane(V3 n, V3 e) { return Plane{n, -vdot(n, e)}; }
+__device__ __forceinline__ float plane_abs_distance(const Plane& pl, V3 p) { return fabsf(vdot(pl.n, p) + pl.d); }
+
+// Quaternion * vector, Eigen QuaternionBase::_transformVector
+__device__ __forceinline__ V3 qrotate(float qx, float qy, float qz, float qw, V3 v) {
+  V3 qv{qx, qy, qz};
+  V3 uv = vcross(qv, v);
+  uv = vadd(uv, uv);
+  return vadd(vadd(v, vscale(qw, uv)), vcross(qv, uv));
+}
+
+// ---------------------------------------------------------------------------
+// Eigen 3.4.0 SelfAdjointEigenSolver<Matrix3f>::computeDirect (restated).
+// Symmetric input given by its lower triangle; outputs eigenvalues (ascending)
+// and eigenvector column 0 only (the reference reads eigenvalues()[0], [1] and
+// eigenvectors().col(0): ps/plane_estimator.cc:204-207).
+// ---------------------------------------------------------------------------
+struct Sym3 {
+  float m00, m10, m20, m11, m21, m22;
+};
+
+__device__ __forceinline__ V3 sym_col(const Sym3& s, int c) {
+  if (c == 0) return V3{s.m00, s.m10, s.m20};
+  if (c == 1) return V3{s.m10, s.m11, s.m21};
+  return V3{s.m20, s.m21, s.m22};
+}
+
+__device__ __forceinline__ void extract_kernel(const Sym3& t, V3* res, V3* representative) {
+  int i0 = 0;
+  float best = fabsf(t.m00);
+  float v1 = fabsf(t.m11);
+  if (v1 > best) { best = v1; i0 = 1; }
+  float v2 = fabsf(t.m22);
+  if (v2 > best) { best = v2; i0 = 2; }
+  V3 r = sym_col(t, i0);
+  V3 a = sym_col(t, (i0 + 1) % 3);
+  V3 b = sym_col(t, (i0 + 2) % 3);
+  V3 c0 = vcross(r, a);
+  V3 c1 = vcross(r, b);
+  float n0 = vsqn(c0);
+  float n1 = vsqn(c1);
+  *representative = r;
+  if (n0 > n1) *res = vdiv(c0, sqrtf(n0));
+  else *res = vdiv(c1, sqrtf(n1));
+}
+
+__device__ __noinline__ void eig3_direct(const Sym3& mat, float evals[3], V3* evec0) {
+  float shift = (mat.m00 + (mat.m11 + mat.m22)) / 3.0f;
+  Sym3 s = mat;
+  s.m00 -= shift;
+  s.m11 -= shift;
+  s.m22 -= shift;
+  float scale = fmaxf(fmaxf(fmaxf(fabsf(s.m00), fabsf(s.m10)), fmaxf(fabsf(s.m20), fabsf(s.m11))),
+                      fmaxf(fabsf(s.m21), fabsf(s.m22)));
+  if (scale > 0.0f) {
+    s.m00 /= scale; s.m10 /= scale; s.m20 /= scale;
+    s.m11 /= scale; s.m21 /= scale; s.m22 /= scale;
+  }
+  // computeRoots
+  const float s_inv3 = 1.0f / 3.0f;
+  const float s_sqrt3 = sqrtf(3.0f);
+  float c0 = s.m00 * s.m11 * s.m22 + 2.0f * s.m10 * s.m20 * s.m21 - s.m00 * s.m21 * s.m21 -
+             s.m11 * s.m20 * s.m20 - s.m22 * s.m10 * s.m10;
+  float c1 = s.m00 * s.m11 - s.m10 * s.m10 + s.m00 * s.m22 - s.m20 * s.m20 + s.m11 * s.m22 -
+             s.m21 * s.m21;
+  float c2 = s.m00 + s.m11 + s.m22;
+  float c2_over_3 = c2 * s_inv3;
+  float a_over_3 = (c2 * c2_over_3 - c1) * s_inv3;
+  a_over_3 = (a_over_3 < 0.0f) ? 0.0f : a_over_3;  // numext::maxi(a, 0)
+  float half_b = 0.5f * (c0 + c2_over_3 * (2.0f * c2_over_3 * c2_over_3 - c1));
+  float q = a_over_3 * a_over_3 * a_over_3 - half_b * half_b;
+  q = (q < 0.0f) ? 0.0f : q;
+  float rho = sqrtf(a_over_3);
+  float theta = cr_atan2f(sqrtf(q), half_b) * s_inv3;
+  float cos_theta = cr_cosf(theta);
+  float sin_theta = cr_sinf(theta);
+  evals[0] = c2_over_3 - rho * (cos_theta + s_sqrt3 * sin_theta);
+  evals[1] = c2_over_3 - rho * (cos_theta - s_sqrt3 * sin_theta);
+  evals[2] = c2_over_3 + 2.0f * rho * cos_theta;
+
+  V3 e0;
+  if ((evals[2] - evals[0]) <= FLT_EPSILON) {
+    e0 = V3{1.0f, 0.0f, 0.0f};
+  } else {
+    float d0 = evals[2] - evals[1];
+    float d1 = evals[1] - evals[0];
+    int k = 0, l = 2;
+    if (d0 > d1) { k = 2; l = 0; d0 = d1; }
+    Sym3 t = s;
+    float ek = evals[k];
+    t.m00 -= ek; t.m11 -= ek; t.m22 -= ek;
+    V3 vk, vl;
+    extract_kernel(t, &vk, &vl);
+    if (k == 0) {
+      e0 = vk;
+    } else {
+      if (d0 <= 2.0f * FLT_EPSILON * d1) {
+        float dd = vdot(vk, vl);
+        vl = V3{vl.x - dd * vl.x, vl.y - dd * vl.y, vl.z - dd * vl.z};
+        float z = vsqn(vl);
+        if (z > 0.0f) vl = vdiv(vl, sqrtf(z));
+      } else {
+        t = s;
+        float el = evals[l];
+        t.m00 -= el; t.m11 -= el; t.m22 -= el;
+        V3 dummy;
+        extract_kernel(t, &vl, &dummy);
+      }
+      e0 = vl;
+    }
+  }
+  *evec0 = e0;
+  evals[0] = evals[0] * scale + shift;
+  evals[1] = evals[1] * scale + shift;
+  evals[2] = evals[2] * scale + shift;
+}
+
+// ---------------------------------------------------------------------------
+// PlaneEstimator state + ComputePlane (ps/plane_estimator.cc:46-65,184-229).
+// ---------------------------------------------------------------------------
+struct Estimator {
+  float acc[6];
+  V3 csum;
+  float w;
+  Plane plane;     // plane_ (its normal is the orientation hint)
+  V3 centroid;
+  float curvature;
+  bool valid;
+  bool up_to_date;
+};
+
+__device__ __forceinline__ void est_clear(Estimator& e) {
+  for (int i = 0; i < 6; ++i) e.acc[i] = 0.0f;
+  e.csum = V3{0.0f, 0.0f, 0.0f};
+  e.w = 0.0f;
+  e.plane = Plane{V3{1.0f, 0.0f, 0.0f}, 0.0f};
+  e.centroid = V3{0.0f, 0.0f, 0.0f};
+  e.curvature = 0.0f;
+  e.valid = false;
+  e.up_to_date = true;
+}
+
+__device__ __forceinline__ void est_add(Estimator& e, V3 p) {
+  e.acc[0] += p.x * p.x;
+  e.acc[1] += p.x * p.y;
+  e.acc[2] += p.x * p.z;
+  e.acc[3] += p.y * p.y;
+  e.acc[4] += p.y * p.z;
+  e.acc[5] += p.z * p.z;
+  e.csum = vadd(e.csum, p);
+  e.w += 1.0f;
+  e.up_to_date = false;
+}
+
+// Caller guarantees e.w > 0 (the reference CHECK-aborts otherwise).
+__device__ __forceinline__ void est_compute(Estimator& e) {
+  e.up_to_date = true;
+  e.centroid = vdiv(e.csum, e.w);
+  float a0 = e.acc[0] / e.w, a1 = e.acc[1] / e.w, a2 = e.acc[2] / e.w;
+  float a3 = e.acc[3] / e.w, a4 = e.acc[4] / e.w, a5 = e.acc[5] / e.w;
+  Sym3 cov;
+  cov.m00 = a0 - e.centroid.x * e.centroid.x;
+  cov.m10 = a1 - e.centroid.x * e.centroid.y;
+  cov.m20 = a2 - e.centroid.x * e.centroid.z;
+  cov.m11 = a3 - e.centroid.y * e.centroid.y;
+  cov.m21 = a4 - e.centroid.y * e.centroid.z;
+  cov.m22 = a5 - e.centroid.z * e.centroid.z;
+  float evals[3];
+  V3 ev;
+  eig3_direct(cov, evals, &ev);
+  if (evals[1] > FLT_MIN) {
+    float smallest = evals[0];
+    if (vdot(e.plane.n, ev) > 0.0f) e.plane = make_plane(ev, e.centroid);
+    else e.plane = make_plane(vneg(ev), e.centroid);
+    float trace = cov.m00 + (cov.m11 + cov.m22);
+    if (trace > smallest && smallest > FLT_MIN) e.curvature = fabsf(smallest / trace);
+    else e.curvature = 0.0f;
+    e.valid = true;
+  } else {
+    e.curvature = 0.0f;
+    e.plane = make_plane(e.plane.n, e.centroid);
+    e.valid = false;
+  }
+}
+
+// SetNormalOrientation, ps/plane_estimator.cc:113-126
+__device__ __forceinline__ void est_set_orientation(Estimator& e, V3 hint) {
+  if (!e.up_to_date) est_compute(e);
+  if (e.valid) {
+    if (vdot(e.plane.n, hint) < 0.0f) {
+      e.plane.n = V3{e.plane.n.x * -1.0f, e.plane.n.y * -1.0f, e.plane.n.z * -1.0f};
+      e.plane.d *= -1.0f;
+    }
+  } else {
+    e.plane.n = hint;
+  }
+}
+
+}  // namespace pcseg
