@@ -1,0 +1,21 @@
+# Build: product library (CUDA, sm_100a) + oracle (CPU checker).
+NVCC ?= /usr/local/cuda/bin/nvcc
+PKG := x-edr-pointcloud-segmentation_b200
+CSRC := $(PKG)/csrc
+NVFLAGS := -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 \
+           -fmad=false -prec-div=true -prec-sqrt=true -ftz=false \
+           -Xcompiler -fPIC,-ffp-contract=off,-fno-fast-math -shared
+
+all: lib oracle
+
+lib: $(PKG)/libpcseg_b200.so
+
+$(PKG)/libpcseg_b200.so: $(CSRC)/pcseg_api.cu $(wildcard $(CSRC)/*.cuh) include/pcseg_b200.h
+	$(NVCC) $(NVFLAGS) $(EXTRA) -o $@ $(CSRC)/pcseg_api.cu
+
+oracle:
+	$(MAKE) -C oracle all
+
+clean:
+	rm -f $(PKG)/libpcseg_b200.so; $(MAKE) -C oracle clean
+.PHONY: all lib oracle clean

@@ -1,0 +1,250 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle
+on the same seeded inputs.  Labels, inlier index sets, boundaries: bit-exact.
+Normals, planes, centroids: bit-exact expected (same fp32 op order, trig
+evaluated in double and rounded once on both sides); asserted to 1e-5 relative
+as BASELINE.json's north_star states, and the exact-match rate is reported."""
+import numpy as np
+import pytest
+
+import oracle
+import pcseg
+import synth
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = pcseg.Context(0)
+    yield c
+    c.close()
+
+
+def bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+def assert_same_float(a, b, what, rtol=1e-5):
+    a = np.asarray(a, np.float32)
+    b = np.asarray(b, np.float32)
+    assert a.shape == b.shape, what
+    assert np.array_equal(np.isnan(a), np.isnan(b)), what + ": NaN pattern"
+    m = ~np.isnan(a)
+    exact = (bits(a)[m] == bits(b)[m]).mean() if m.any() else 1.0
+    scale = max(float(np.abs(b[m]).max()) if m.any() else 1.0, 1e-30)
+    assert np.all(np.abs(a[m] - b[m]) <= rtol * scale), what
+    return exact
+
+
+def assert_regions_equal(g, o, kind):
+    assert g.n == o.n
+    assert np.array_equal(g.inlier_offsets, o.inlier_offsets)
+    assert np.array_equal(g.inlier_indices, o.inlier_indices)
+    assert np.array_equal(g.label_ids, o.label_ids)
+    if kind == "planar":
+        assert np.array_equal(g.seed_indices, o.seed_indices)
+        assert np.array_equal(g.boundary_offsets, o.boundary_offsets)
+        assert np.array_equal(g.boundary_indices, o.boundary_indices)
+        assert np.array_equal(g.disc_offsets, o.disc_offsets)
+        assert np.array_equal(g.disc_indices, o.disc_indices)
+        assert_same_float(g.planes, o.planes, "planes")
+        assert_same_float(g.centroids, o.centroids, "centroids")
+        assert_same_float(g.areas, o.areas, "areas")
+        assert_same_float(g.estimators, o.estimators, "estimators")
+        assert np.array_equal(g.hull_offsets, o.hull_offsets)
+        assert_same_float(g.hull_points, o.hull_points, "hull")
+
+
+def test_clustering_golden(ctx):
+    """ps/clustering_test.cc:115-151 through the CUDA path."""
+    from test_oracle_golden import CLUSTERS_CHECK
+    pts, seeds = synth.clustering_test_cloud()
+    labels = ctx.prepare_unlabeled_labels(100)
+    out, regs = ctx.segment_cluster(pts, 10, 10, seeds, labels, id_offset=1)
+    assert np.array_equal(out.reshape(10, 10).T, CLUSTERS_CHECK)
+    assert [len(x) for x in regs.inliers] == [16, 20, 10, 10, 10, 27]
+    o_out, o_regs = oracle.segment_cluster(pts, 10, 10, seeds, labels, id_offset=1)
+    assert np.array_equal(out, o_out)
+    assert_regions_equal(regs, o_regs, "cluster")
+
+
+def _frame(rows, cols, seed=1234, **kw):
+    return synth.depth_frame(rows, cols, seed=seed, **kw)
+
+
+@pytest.mark.parametrize("rows,cols,min_d", [(60, 80, 0.1), (120, 160, 0.1), (120, 160, 0.02),
+                                             (480, 640, 0.1)])
+def test_normals_parity(ctx, rows, cols, min_d):
+    xyz = _frame(rows, cols)
+    params = dict(min_neighbor_distance=min_d)
+    g, gc = ctx.normals_organized(xyz, rows, cols, params=params, want_curvature=True)
+    o, oc = oracle.normals_organized(xyz, rows, cols, params=oracle.default_normals_params(**params),
+                                     want_curvature=True)
+    ex = assert_same_float(g, o, "normals")
+    assert_same_float(gc, oc, "curvature")
+    assert ex == 1.0, "normals exact-match rate %.6f" % ex
+
+
+def test_normals_subrange_and_no_diag(ctx):
+    rows, cols = 96, 128
+    xyz = _frame(rows, cols, seed=7)
+    init = np.full((rows * cols, 3), 7.0, np.float32)
+    params = dict(include_diagonal_neighbors=0, min_num_support_neighbors=3, min_neighbor_distance=0.05)
+    g = ctx.normals_organized(xyz, rows, cols, sensor_t=(0.1, -0.2, 0.3), params=params,
+                              row_range=(5, 90), col_range=(3, 100), normals_init=init)
+    o = oracle.normals_organized(xyz, rows, cols, sensor_t=(0.1, -0.2, 0.3),
+                                 params=oracle.default_normals_params(**params),
+                                 row_range=(5, 90), col_range=(3, 100), normals_init=init)
+    assert assert_same_float(g, o, "normals subrange") == 1.0
+
+
+def test_normals_invalid_plane_chain(ctx):
+    """Quirk Q3: estimator state leaks after an invalid plane (collinear support)."""
+    rows, cols = 16, 24
+    xyz = np.zeros((rows * cols, 3), np.float32)
+    rng = np.random.default_rng(5)
+    for c in range(cols):
+        for r in range(rows):
+            xyz[c * rows + r] = (0.2 * c, 0.2 * r, 1.0 + 0.01 * rng.standard_normal())
+    # a block of exactly collinear / identical points -> invalid planes
+    for c in range(6, 12):
+        for r in range(4, 10):
+            xyz[c * rows + r] = (1.0, 1.0, 1.0)
+    params = dict(min_neighbor_distance=0.0, max_neighbor_distance=10.0)
+    g = ctx.normals_organized(xyz, rows, cols, params=params)
+    o = oracle.normals_organized(xyz, rows, cols, params=oracle.default_normals_params(**params))
+    assert assert_same_float(g, o, "normals chain") == 1.0
+
+
+def _planar_case(ctx, xyz, rows, cols, seeds, cfg=None, nparams=None):
+    nparams = nparams or {}
+    nrm = oracle.normals_organized(xyz, rows, cols, params=oracle.default_normals_params(**nparams))
+    labels = np.full(rows * cols, -1, np.int32)
+    o_lab, o_regs = oracle.segment_planar(xyz, nrm, rows, cols, seeds, labels,
+                                          cfg=oracle.default_planar_config(**(cfg or {})))
+    g_lab, g_regs = ctx.segment_planar(xyz, nrm, rows, cols, seeds, labels, cfg=cfg)
+    assert np.array_equal(g_lab, o_lab), "labels differ at %d cells" % (g_lab != o_lab).sum()
+    assert_regions_equal(g_regs, o_regs, "planar")
+    return g_lab, g_regs, nrm
+
+
+@pytest.mark.parametrize("rows,cols", [(60, 80), (120, 160), (240, 320)])
+def test_planar_parity_small(ctx, rows, cols):
+    xyz = _frame(rows, cols)
+    seeds = np.arange(rows * cols - 1, -1, -1, dtype=np.int32)
+    _, regs, _ = _planar_case(ctx, xyz, rows, cols, seeds, nparams=dict(min_neighbor_distance=0.05))
+    assert regs.n >= 1
+
+
+def test_planar_parity_configs(ctx):
+    rows, cols = 120, 160
+    xyz = _frame(rows, cols, seed=77, yaw_deg=12.0)
+    seeds = np.arange(rows * cols - 1, -1, -1, dtype=np.int32)
+    for cfg in (dict(plane_model_reestimation_period=7, max_plane_distance=0.02),
+                dict(plane_model_reestimation_period=1, min_region_inliers=50),
+                dict(plane_model_reestimation_period=64, min_region_area=0.5),
+                dict(plane_model_reestimation_period=30, max_plane_distance=0.005, min_region_inliers=3)):
+        _planar_case(ctx, xyz, rows, cols, seeds, cfg=cfg, nparams=dict(min_neighbor_distance=0.05))
+
+
+def test_planar_seed_orders(ctx):
+    rows, cols = 120, 160
+    xyz = _frame(rows, cols, seed=3)
+    rng = np.random.default_rng(1)
+    seeds = rng.permutation(rows * cols).astype(np.int32)[:5000]
+    _planar_case(ctx, xyz, rows, cols, seeds, nparams=dict(min_neighbor_distance=0.05))
+    nrm = oracle.normals_organized(xyz, rows, cols)
+    ps = oracle.seeds_plane_support(xyz, nrm, rows, cols)
+    _planar_case(ctx, xyz, rows, cols, ps)
+    _planar_case(ctx, xyz, rows, cols, np.zeros(0, np.int32))
+
+
+def test_c1_full_pipeline_parity(ctx):
+    """Config C1: 640x480, normals -> planes -> clusters, all stages vs the oracle."""
+    rows, cols = 480, 640
+    xyz = synth.c1()
+    g_n = ctx.normals_organized(xyz, rows, cols)
+    o_n = oracle.normals_organized(xyz, rows, cols)
+    assert assert_same_float(g_n, o_n, "normals") == 1.0
+    seeds = np.arange(rows * cols - 1, -1, -1, dtype=np.int32)
+    labels = np.full(rows * cols, -1, np.int32)
+    o_lab, o_regs = oracle.segment_planar(xyz, o_n, rows, cols, seeds, labels)
+    g_lab, g_regs = ctx.segment_planar(xyz, g_n, rows, cols, seeds, labels)
+    assert np.array_equal(g_lab, o_lab)
+    assert_regions_equal(g_regs, o_regs, "planar")
+    assert g_regs.n >= 4
+    o_lab2, o_c = oracle.segment_cluster(xyz, rows, cols, seeds, o_lab, id_offset=o_regs.n)
+    g_lab2, g_c = ctx.segment_cluster(xyz, rows, cols, seeds, g_lab, id_offset=g_regs.n)
+    assert np.array_equal(g_lab2, o_lab2)
+    assert_regions_equal(g_c, o_c, "cluster")
+    # second seed variant of SURVEY 8d: FindSeedPointsFromPlaneSupport seeds
+    ps_o = oracle.seeds_plane_support(xyz, o_n, rows, cols)
+    ps_g = ctx.seeds_plane_support(xyz, g_n, rows, cols)
+    assert np.array_equal(ps_g, ps_o)
+    o_lab3, o_r3 = oracle.segment_planar(xyz, o_n, rows, cols, ps_o, labels)
+    g_lab3, g_r3 = ctx.segment_planar(xyz, g_n, rows, cols, ps_g, labels)
+    assert np.array_equal(g_lab3, o_lab3)
+    assert_regions_equal(g_r3, o_r3, "planar")
+
+
+def test_cluster_parity_lidar_like(ctx):
+    """C4-style: range image with masked ground, half window 2, threshold 0.25."""
+    xyz, labels = synth.c4(rows=32, cols=1024, n_objects=60)
+    rows, cols = 32, 1024
+    seeds = np.arange(rows * cols - 1, -1, -1, dtype=np.int32)
+    cfg = dict(squared_distance_threshold=0.25, half_search_window=2, min_region_inliers=10)
+    o_lab, o_r = oracle.segment_cluster(xyz, rows, cols, seeds, labels, cfg=oracle.default_cluster_config(**cfg))
+    g_lab, g_r = ctx.segment_cluster(xyz, rows, cols, seeds, labels, cfg=cfg)
+    assert np.array_equal(g_lab, o_lab)
+    assert_regions_equal(g_r, o_r, "cluster")
+    assert g_r.n >= 3
+
+
+def test_cluster_parity_noisy_thresholds(ctx):
+    """Exercises quirk Q5 (reject / re-enqueue) with a tight threshold on noise."""
+    rows, cols = 64, 96
+    rng = np.random.default_rng(11)
+    xyz = np.zeros((rows * cols, 3), np.float32)
+    for c in range(cols):
+        for r in range(rows):
+            xyz[c * rows + r] = (0.05 * c, 0.05 * r, 0.08 * rng.standard_normal())
+    xyz[rng.random(rows * cols) < 0.05] = np.nan
+    seeds = rng.permutation(rows * cols).astype(np.int32)
+    labels = np.full(rows * cols, -1, np.int32)
+    labels[rng.random(rows * cols) < 0.03] = -2
+    for h, thr, mi in ((1, 0.012, 7), (2, 0.02, 3), (3, 0.008, 1)):
+        cfg = dict(squared_distance_threshold=thr, half_search_window=h, min_region_inliers=mi)
+        o_lab, o_r = oracle.segment_cluster(xyz, rows, cols, seeds, labels, cfg=oracle.default_cluster_config(**cfg))
+        g_lab, g_r = ctx.segment_cluster(xyz, rows, cols, seeds, labels, cfg=cfg)
+        assert np.array_equal(g_lab, o_lab), (h, thr, mi)
+        assert_regions_equal(g_r, o_r, "cluster")
+
+
+def test_mean_shift_modes_parity(ctx):
+    rows, cols = 200, 300
+    xyz = synth.c5(rows=rows, cols=cols, n_blobs=40)
+    labels = np.full(rows * cols, -1, np.int32)
+    labels[np.random.default_rng(2).random(rows * cols) < 0.02] = 0
+    g = ctx.mean_shift_modes(xyz, rows, cols, labels, iterations=5)
+    _, _, o = oracle.mean_shift(xyz, rows, cols, labels, iterations=5)
+    seed_cells = o[:, 7].astype(np.int64)
+    assert np.array_equal(np.nonzero(g[:, 7] == 1.0)[0], seed_cells)
+    gs = g[seed_cells]
+    assert np.array_equal(gs[:, 6], o[:, 6])
+    # modes within 1e-4 of the bandwidth (1.0) as the north star states; bit-exact expected
+    assert np.all(np.abs(gs[:, :5] - o[:, :5]) <= 1e-4)
+    assert np.array_equal(bits(gs[:, :6]), bits(o[:, :6]))
+
+
+def test_error_statuses(ctx):
+    pts, seeds = synth.clustering_test_cloud()
+    labels = np.full(100, -1, np.int32)
+    with pytest.raises(pcseg.PcsegError) as e:
+        ctx.segment_cluster(pts[:10], 1, 10, seeds[:10] % 10, labels[:10])
+    assert e.value.status == 2  # CHECK_GT(points.Rows(), 1)
+    with pytest.raises(pcseg.PcsegError) as e:
+        ctx.segment_cluster(pts, 10, 10, np.array([100], np.int32), labels)
+    assert e.value.status == 7
+    with pytest.raises(pcseg.PcsegError) as e:
+        ctx.segment_planar(pts, pts, 10, 10, seeds, labels, cfg=dict(plane_model_reestimation_period=0))
+    assert e.value.status == 3

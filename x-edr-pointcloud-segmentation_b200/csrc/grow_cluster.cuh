@@ -1,0 +1,204 @@
+// grow_cluster.cuh -- SegmentRegions<ClusterRegion<>> on the GPU.
+//
+// Replaces ps/segmentation.h:239-292 (driver) with ps/cluster_region.h:73-150
+// (Init / CheckInlierAndUpdate / AddNeighbors / CheckAndFinalize) as the model.
+// One CTA per frame (frames are the unit of parallelism: one FIFO, shared
+// labels and sequential seeds make a single frame inherently ordered, SURVEY.md
+// H1).  Each FIFO chunk of up to BLOCK entries is evaluated in parallel and
+// resolved by queue position (see grow_common.cuh), which reproduces quirk Q5
+// exactly: a candidate is tested only against the source that first enqueued
+// it, reverts to kUnlabeled on failure and can be re-enqueued by a later entry.
+#pragma once
+#include "grow_common.cuh"
+
+namespace pcseg {
+
+struct ClusterArgs {
+  const float* xyz;   // [F][N][3]
+  int* labels;        // [F][N]
+  int rows, cols;
+  const int* seeds;   // shared list or nullptr (all descending)
+  int n_seeds;
+  int min_inliers;
+  float sq_thr;
+  int half_window;    // <= 3
+  int id_offset;      // used when id_offset_from_planar == 0
+  int id_offset_from_planar;  // 1: offset = stats[f].n_planar
+  int* queue;         // [F][qcap][2]
+  int qcap;
+  int* claim;         // [F][N], INT_MAX when idle
+  int* inliers;       // [F][N]
+  ClusterMeta* meta;  // [F][rcap]
+  int rcap;
+  FrameStats* stats;  // [F]
+};
+
+template <int BLOCK>
+__global__ void __launch_bounds__(BLOCK) cluster_grow_kernel(ClusterArgs a) {
+  const int f = blockIdx.x;
+  const int tid = threadIdx.x;
+  const int rows = a.rows, cols = a.cols;
+  const int N = rows * cols;
+  const float* __restrict__ xyz = a.xyz + (size_t)f * N * 3;
+  volatile int* labels = a.labels + (size_t)f * N;
+  volatile int* queue = a.queue + (size_t)f * a.qcap * 2;
+  int* claim = a.claim + (size_t)f * N;
+  volatile int* vclaim = claim;
+  int* inliers = a.inliers + (size_t)f * N;
+  ClusterMeta* meta = a.meta + (size_t)f * a.rcap;
+  const int id_offset = a.id_offset_from_planar ? a.stats[f].n_planar : a.id_offset;
+  const int h = a.half_window;
+  const int side = 2 * h + 1;
+
+  __shared__ int s_warp[BLOCK / 32 + 1];
+
+  int seed_pos = a.n_seeds;  // seeds are consumed back to front
+  int nreg = 0, inl_total = 0, err = 0, steps = 0;
+  bool any_failed = false;
+
+  while (true) {
+    // ---- next usable seed (ps/segmentation.h:254-260).  A seed whose point is
+    // not finite (or a non-positive threshold) fails its own self-test, adds no
+    // inlier and leaves labels untouched, so skipping it here is exact.
+    int found = -1;
+    while (seed_pos > 0 && found < 0) {
+      int cand = -1;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        int pos = seed_pos - 1 - (tid + k * BLOCK);
+        if (pos >= 0 && cand < 0) {
+          int s = seed_at(a.seeds, N, pos);
+          if (labels[s] == kUnlabeled) {
+            V3 p = ld3(xyz, s);
+            if (vfinite(p) && (0.0f < a.sq_thr)) cand = pos;
+          }
+        }
+      }
+      // threads with smaller tid hold larger positions within each k; take max
+      found = block_max<BLOCK>(cand, s_warp);
+      if (found < 0) seed_pos = max(seed_pos - 4 * BLOCK, 0);
+    }
+    if (found < 0) break;
+    seed_pos = found;
+    const int seed = seed_at(a.seeds, N, found);
+    const int label_id = nreg + id_offset;
+    const int base = inl_total;
+    int head = 0, tail = 1, ninl = 0;
+    if (tid == 0) {
+      queue[0] = seed;
+      queue[1] = seed;
+    }
+    __syncthreads();
+
+    while (head < tail) {
+      ++steps;
+      const int m = min(BLOCK, tail - head);
+      const bool mine = tid < m;
+      int src = -1, cand = -1;
+      bool acc = false;
+      if (mine) {
+        const int qi = (head + tid) % a.qcap;
+        src = queue[2 * qi];
+        cand = queue[2 * qi + 1];
+        // (candidate - source).squaredNorm() < threshold, ps/cluster_region.h:94
+        acc = vsqn(vsub(ld3(xyz, cand), ld3(xyz, src))) < a.sq_thr;
+      }
+      int nacc;
+      const int rank = block_scan_excl<BLOCK>(acc ? 1 : 0, &nacc, s_warp);
+      if (mine) {
+        if (acc) {
+          labels[cand] = label_id;
+          inliers[base + ninl + rank] = cand;
+        } else {
+          labels[cand] = kRejBase - tid;
+        }
+      }
+      __syncthreads();
+      // AddNeighbors, ps/cluster_region.h:122-150: delta_col outer, delta_row inner
+      unsigned long long el = 0ull;
+      const int row = cand % rows, col = cand / rows;
+      if (acc) {
+        int s = 0;
+        for (int dc = -h; dc <= h; ++dc) {
+          for (int dr = -h; dr <= h; ++dr) {
+            if (dc == 0 && dr == 0) continue;
+            const int cc = col + dc, rc = row + dr;
+            if (cc >= 0 && cc < cols && rc >= 0 && rc < rows) {
+              const int n = cc * rows + rc;
+              const int L = labels[n];
+              if (L == kUnlabeled || (L <= kRejBase && (kRejBase - L) < tid)) {
+                el |= 1ull << s;
+                atomicMin(claim + n, tid * 64 + s);
+              }
+            }
+            ++s;
+          }
+        }
+      }
+      __syncthreads();
+      if (mine && !acc) labels[cand] = kUnlabeled;  // ps/cluster_region.h:105
+      unsigned long long win = 0ull;
+      if (acc) {
+        unsigned long long e = el;
+        while (e) {
+          const int s = __ffsll((long long)e) - 1;
+          e &= e - 1;
+          const int cell = s + (s >= (side * side) / 2 ? 1 : 0);  // skip the centre
+          const int dc = cell / side - h, dr = cell % side - h;
+          const int n = (col + dc) * rows + (row + dr);
+          if (vclaim[n] == tid * 64 + s) win |= 1ull << s;
+        }
+      }
+      int nwin;
+      int off = block_scan_excl<BLOCK>(__popcll(win), &nwin, s_warp);  // syncs inside
+      while (win) {
+        const int s = __ffsll((long long)win) - 1;
+        win &= win - 1;
+        const int cell = s + (s >= (side * side) / 2 ? 1 : 0);
+        const int dc = cell / side - h, dr = cell % side - h;
+        const int n = (col + dc) * rows + (row + dr);
+        const int qi = (tail + off) % a.qcap;
+        queue[2 * qi] = cand;
+        queue[2 * qi + 1] = n;
+        labels[n] = kAlreadyInQueue;
+        claim[n] = INT_MAX;
+        ++off;
+      }
+      __syncthreads();
+      head += m;
+      tail += nwin;
+      ninl += nacc;
+    }
+
+    // CheckAndFinalize, ps/cluster_region.h:111-116
+    if (ninl >= a.min_inliers) {
+      if (nreg < a.rcap) {
+        if (tid == 0) meta[nreg] = ClusterMeta{base, ninl, label_id};
+        ++nreg;
+        inl_total += ninl;
+      } else {
+        err |= kErrRegionCap;
+        break;
+      }
+    } else {
+      // ps/segmentation.h:280-282
+      for (int i = tid; i < ninl; i += BLOCK) labels[inliers[base + i]] = kAlreadyExamedPoint;
+      any_failed = any_failed || (ninl > 0);
+      __syncthreads();
+    }
+  }
+  // ps/segmentation.h:287-291
+  __syncthreads();
+  if (any_failed) {
+    for (int i = tid; i < N; i += BLOCK)
+      if (labels[i] == kAlreadyExamedPoint) labels[i] = kUnlabeled;
+  }
+  if (tid == 0) {
+    a.stats[f].n_cluster = nreg;
+    a.stats[f].cluster_inliers = inl_total;
+    a.stats[f].error_flags |= err;
+    a.stats[f].grow_steps += steps;
+  }
+}
+
+}  // namespace pcseg

@@ -1,0 +1,496 @@
+// grow_planar.cuh -- SegmentRegions<PlanarRegion<>> on the GPU.
+//
+// Replaces ps/segmentation.h:239-292 (driver) with ps/planar_region.h:144-255
+// (Init / CheckInlierAndUpdate / AddNeighbors), :189-224 (CheckAndFinalize),
+// :295-425 (FindLabeledRegionBoundary), ps/planar_region.cc:26-106 and
+// ps/algorithms.h:264-292,526-549 as the model.
+//
+// One CTA per frame.  The plane is re-fitted every
+// plane_model_reestimation_period-th inlier from SEQUENTIAL fp32 sums in FIFO
+// order (ps/planar_region.h:168-176), so the growth is a serial chain of
+// "evaluate <= 32 queue entries -> cut at the inlier that triggers the re-fit
+// -> accumulate in order -> 3x3 eigen-solve".  That chain runs warp-
+// synchronously in warp 0; the whole CTA is used for seed scanning, the
+// boundary-start search, the hull gate, the discontinuity flags and label
+// parking.  Latency-bound by construction: throughput comes
+// from many frames in flight, one per CTA.
+#pragma once
+#include "grow_common.cuh"
+
+namespace pcseg {
+
+struct PlanarArgs {
+  const float* xyz;      // [F][N][3]
+  const float* normals;  // [F][N][3]
+  int* labels;           // [F][N]
+  int rows, cols;
+  const int* seeds;      // nullptr = all descending; else shared or per-frame list
+  int n_seeds;           // shared list length
+  int seeds_stride;      // > 0: per-frame lists, seeds + f*stride, count n_seeds_dev[f]
+  const int* n_seeds_dev;
+  float max_plane_distance, min_region_area;
+  int min_inliers, period;
+  float disc_min_range, disc_max_range, disc_angle, disc_z_diff, disc_z_ratio;
+  float qx, qy, qz, qw;
+  int id_offset;
+  int* queue;            // [F][qcap]
+  int qcap;
+  int* claim;            // [F][N]
+  int* inliers;          // [F][N]
+  int* boundary;         // [F][bcap]
+  unsigned char* bflags; // [F][bcap] discontinuity flag per boundary entry
+  int bcap;
+  PlanarMeta* meta;      // [F][rcap]
+  int rcap;
+  FrameStats* stats;     // [F]
+};
+
+struct GrowResult {  // warp 0 -> CTA broadcast
+  int ninl;
+  int steps, refits;
+  float plane[4];
+  float centroid[3];
+  float est[10];
+};
+
+__device__ __constant__ int kDx8[8] = {-1, -1, 0, 1, 1, 1, 0, -1};  // ps/planar_region.cc:30-37
+__device__ __constant__ int kDy8[8] = {0, -1, -1, -1, 0, 1, 1, 1};
+__device__ __constant__ int kDx4[4] = {-1, 0, 1, 0};                // ps/planar_region.cc:39-42
+__device__ __constant__ int kDy4[4] = {0, -1, 0, 1};
+
+// FIFO growth of one region by warp 0 (all 32 lanes).  Returns via *out.
+__device__ __forceinline__ void planar_grow_warp(const PlanarArgs& a, const float* __restrict__ xyz,
+                                                 const float* __restrict__ nrm, volatile int* labels,
+                                                 volatile int* queue, int* claim, int* inliers,
+                                                 int seed, int label_id, int base, GrowResult* out) {
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int rows = a.rows, cols = a.cols;
+  volatile int* vclaim = claim;
+  const V3 seed_normal = ld3(nrm, seed);
+  const V3 seed_point = ld3(xyz, seed);
+  // Init, ps/planar_region.h:144-159
+  Plane plane = make_plane(seed_normal, seed_point);
+  Estimator est;
+  est_clear(est);
+  est_set_orientation(est, seed_normal);
+  int head = 0, tail = 1, ninl = 0, steps = 0, refits = 0;
+  if (lane == 0) queue[0] = seed;
+  __syncwarp();
+  const int period = a.period;
+  while (head < tail) {
+    ++steps;
+    const int m = min(32, tail - head);
+    int cand = -1;
+    V3 p{0.f, 0.f, 0.f};
+    bool acc = false;
+    if (lane < m) {
+      cand = queue[(head + lane) % a.qcap];
+      p = ld3(xyz, cand);
+      acc = plane_abs_distance(plane, p) < a.max_plane_distance;  // :168
+    }
+    unsigned amask = __ballot_sync(FULL, acc);
+    const int need = period - (ninl % period);
+    int processed = m;
+    bool refit = false;
+    if (__popc(amask) >= need) {
+      processed = (int)__fns(amask, 0, need) + 1;
+      refit = true;
+    }
+    const unsigned pmask = processed >= 32 ? FULL : ((1u << processed) - 1u);
+    amask &= pmask;
+    const bool mine = lane < processed;
+    acc = acc && mine;
+    const int rank = __popc(amask & ((1u << lane) - 1u));
+    if (mine) {
+      if (acc) {
+        labels[cand] = label_id;              // :177
+        inliers[base + ninl + rank] = cand;   // :169
+      } else {
+        labels[cand] = kRejBase - lane;       // becomes kUnlabeled below (:181)
+      }
+    }
+    // plane_estimator_.AddPoint in FIFO order, :170
+    for (unsigned mm = amask; mm; mm &= mm - 1) {
+      const int src = __ffs(mm) - 1;
+      V3 q{__shfl_sync(FULL, p.x, src), __shfl_sync(FULL, p.y, src), __shfl_sync(FULL, p.z, src)};
+      est_add(est, q);
+    }
+    __syncwarp();
+    // AddNeighbors, :229-255: (c-1,r), (c,r-1), (c,r+1), (c+1,r)
+    int nb[4] = {-1, -1, -1, -1};
+    bool el[4] = {false, false, false, false};
+    if (acc) {
+      const int row = cand % rows, col = cand / rows;
+      if (col > 0) nb[0] = cand - rows;
+      if (row > 0) nb[1] = cand - 1;
+      if (row < rows - 1) nb[2] = cand + 1;
+      if (col < cols - 1) nb[3] = cand + rows;
+#pragma unroll
+      for (int s = 0; s < 4; ++s) {
+        if (nb[s] >= 0) {
+          const int L = labels[nb[s]];
+          el[s] = (L == kUnlabeled) || (L <= kRejBase && (kRejBase - L) < lane);
+        }
+      }
+#pragma unroll
+      for (int s = 0; s < 4; ++s)
+        if (el[s]) atomicMin(claim + nb[s], lane * 4 + s);
+    }
+    __syncwarp();
+    if (mine && !acc) labels[cand] = kUnlabeled;
+    bool win[4];
+#pragma unroll
+    for (int s = 0; s < 4; ++s) win[s] = el[s] && (vclaim[nb[s]] == lane * 4 + s);
+    __syncwarp();
+    const unsigned b0 = __ballot_sync(FULL, win[0]), b1 = __ballot_sync(FULL, win[1]);
+    const unsigned b2 = __ballot_sync(FULL, win[2]), b3 = __ballot_sync(FULL, win[3]);
+    const unsigned lt = (1u << lane) - 1u;
+    int off = __popc(b0 & lt) + __popc(b1 & lt) + __popc(b2 & lt) + __popc(b3 & lt);
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      if (win[s]) {
+        queue[(tail + off) % a.qcap] = nb[s];
+        labels[nb[s]] = kAlreadyInQueue;
+        claim[nb[s]] = INT_MAX;
+        ++off;
+      }
+    }
+    tail += __popc(b0) + __popc(b1) + __popc(b2) + __popc(b3);
+    head += processed;
+    ninl += __popc(amask);
+    if (refit) {
+      est_compute(est);   // plane_ = plane_estimator_.Plane(), :172-176
+      plane = est.plane;
+      ++refits;
+    }
+    __syncwarp();
+  }
+  // CheckAndFinalize first lines, :190-196
+  if (ninl >= a.min_inliers && !est.up_to_date) est_compute(est);
+  if (lane == 0) {
+    out->ninl = ninl;
+    out->steps = steps;
+    out->refits = refits;
+    out->plane[0] = est.plane.n.x; out->plane[1] = est.plane.n.y;
+    out->plane[2] = est.plane.n.z; out->plane[3] = est.plane.d;
+    out->centroid[0] = est.centroid.x; out->centroid[1] = est.centroid.y; out->centroid[2] = est.centroid.z;
+    for (int i = 0; i < 6; ++i) out->est[i] = est.acc[i];
+    out->est[6] = est.csum.x; out->est[7] = est.csum.y; out->est[8] = est.csum.z; out->est[9] = est.w;
+  }
+}
+
+// detail::FindInitialPredecessorDirection, ps/planar_region.cc:67-82
+__device__ __forceinline__ int initial_predecessor_dir(volatile int* labels, int rows, int cols,
+                                                       int idx, int region_label) {
+  const int x = idx / rows, y = idx % rows;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int nx = x + kDx8[i], ny = y + kDy8[i];
+    if (nx >= 0 && nx < cols && ny >= 0 && ny < rows &&
+        labels[idx + kDx8[i] * rows + kDy8[i]] != region_label)
+      return i;
+  }
+  return -1;
+}
+
+struct TraceResult {
+  int nb, min_x, max_x, min_y, max_y, err;
+};
+
+// FindLabeledRegionBoundary (Moore trace), ps/planar_region.h:295-425, executed
+// by one thread.  Discontinuity flags are computed afterwards in parallel.
+__device__ void trace_boundary(volatile int* labels, int rows, int cols, int start_idx,
+                               int region_label, int* boundary, int cap, TraceResult* out) {
+  int curr_idx = start_idx;
+  int cx = start_idx / rows, cy = start_idx % rows;
+  int dir = initial_predecessor_dir(labels, rows, cols, start_idx, region_label);
+  int nb = 0, err = 0;
+  int min_x = cols, max_x = 0, min_y = rows, max_y = 0;  // ps/planar_region.cc:93-96
+  bool found_start = false;
+  int first = -1;
+  while (true) {
+    // detail::FindNextBoundaryPointDirection, ps/planar_region.cc:47-65
+    int lab[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int nx = cx + kDx8[i], ny = cy + kDy8[i];
+      lab[i] = (nx >= 0 && nx < cols && ny >= 0 && ny < rows)
+                   ? labels[curr_idx + kDx8[i] * rows + kDy8[i]]
+                   : (region_label ^ 0x40000000);  // never equal
+    }
+    int nd = -1;
+#pragma unroll
+    for (int delta = 1; delta <= 8; ++delta) {
+      const int d = (dir + delta) & 7;
+      if (nd < 0 && lab[d] == region_label) nd = d;
+    }
+    if (nd < 0) { err = kErrTraceCheck; break; }  // CHECK_GE(new_direction_index, 0)
+    dir = (nd + 4) & 7;
+    curr_idx += kDx8[nd] * rows + kDy8[nd];
+    cx += kDx8[nd];
+    cy += kDy8[nd];
+    if (found_start) {
+      if (curr_idx == first) break;
+      found_start = false;
+    }
+    if (nb >= cap) { err = kErrBoundaryCap; break; }
+    boundary[nb] = curr_idx;
+    if (nb == 0) first = curr_idx;
+    ++nb;
+    min_x = min(min_x, cx); max_x = max(max_x, cx);
+    min_y = min(min_y, cy); max_y = max(max_y, cy);
+    if (curr_idx == start_idx) found_start = true;
+  }
+  out->nb = nb; out->min_x = min_x; out->max_x = max_x;
+  out->min_y = min_y; out->max_y = max_y; out->err = err;
+}
+
+// Plane-frame (x, y) of a point as in PlanarConvexHull, ps/algorithms.h:527-538
+// with eigenmath::PoseFromPlane restated (not in the reference tree):
+// rotation = Quaternion::FromTwoVectors(UnitZ, normal), origin = -offset*normal.
+struct PlaneFrame {
+  float qx, qy, qz, qw;  // world_pose_plane rotation
+  V3 ti;                 // translation of the inverse pose
+};
+__device__ __forceinline__ PlaneFrame make_plane_frame(const float plane[4]) {
+  V3 n{plane[0], plane[1], plane[2]};
+  V3 v0{0.0f, 0.0f, 1.0f};
+  V3 v1 = n;
+  float z = vsqn(n);
+  if (z > 0.0f) v1 = vdiv(n, sqrtf(z));
+  float c = vdot(v1, v0);
+  PlaneFrame pf;
+  if (c < -1.0f + FLT_EPSILON) {
+    pf.qx = 1.0f; pf.qy = 0.0f; pf.qz = 0.0f; pf.qw = 0.0f;
+  } else {
+    V3 axis = vcross(v0, v1);
+    float s = sqrtf((1.0f + c) * 2.0f);
+    float invs = 1.0f / s;
+    pf.qx = axis.x * invs; pf.qy = axis.y * invs; pf.qz = axis.z * invs; pf.qw = s * 0.5f;
+  }
+  V3 t = vscale(-plane[3], n);
+  pf.ti = vneg(qrotate(-pf.qx, -pf.qy, -pf.qz, pf.qw, t));
+  return pf;
+}
+__device__ __forceinline__ void plane_xy(const PlaneFrame& pf, V3 p, double* x, double* y) {
+  V3 pp = vadd(qrotate(-pf.qx, -pf.qy, -pf.qz, pf.qw, p), pf.ti);
+  *x = (double)pp.x;
+  *y = (double)pp.y;
+}
+
+template <int BLOCK>
+__global__ void __launch_bounds__(BLOCK) planar_grow_kernel(PlanarArgs a) {
+  const int f = blockIdx.x;
+  const int tid = threadIdx.x;
+  const int rows = a.rows, cols = a.cols;
+  const int N = rows * cols;
+  const float* __restrict__ xyz = a.xyz + (size_t)f * N * 3;
+  const float* __restrict__ nrm = a.normals + (size_t)f * N * 3;
+  volatile int* labels = a.labels + (size_t)f * N;
+  volatile int* queue = a.queue + (size_t)f * a.qcap;
+  int* claim = a.claim + (size_t)f * N;
+  int* inliers = a.inliers + (size_t)f * N;
+  int* boundary = a.boundary + (size_t)f * a.bcap;
+  unsigned char* bflags = a.bflags + (size_t)f * a.bcap;
+  PlanarMeta* meta = a.meta + (size_t)f * a.rcap;
+  const int* seeds = nullptr;
+  int n_seeds = N;
+  if (a.seeds) {
+    seeds = a.seeds_stride > 0 ? a.seeds + (size_t)f * a.seeds_stride : a.seeds;
+    n_seeds = a.seeds_stride > 0 ? a.n_seeds_dev[f] : a.n_seeds;
+  }
+
+  __shared__ int s_warp[BLOCK / 32 + 1];
+  __shared__ GrowResult s_res;
+  __shared__ TraceResult s_trace;
+  __shared__ float s_area;
+  __shared__ double s_ax[BLOCK], s_ay[BLOCK], s_bx[BLOCK], s_by[BLOCK];
+
+  int seed_pos = n_seeds;
+  int nreg = 0, inl_total = 0, b_total = 0, err = 0, steps = 0, refits = 0;
+  bool any_failed = false;
+  const float min_range_sq = a.disc_min_range * a.disc_min_range;  // eigenmath::Square
+  const float max_range_sq = a.disc_max_range * a.disc_max_range;
+
+  while (true) {
+    // ---- next usable seed (ps/segmentation.h:254-260).  A seed with a
+    // non-finite point or normal fails its own plane test (NaN distance), adds
+    // no inlier and leaves labels untouched: skipping it here is exact.
+    int found = -1;
+    while (seed_pos > 0 && found < 0) {
+      int cand = -1;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        int pos = seed_pos - 1 - (tid + k * BLOCK);
+        if (pos >= 0 && cand < 0) {
+          int s = seed_at(seeds, N, pos);
+          if (labels[s] == kUnlabeled && vfinite(ld3(xyz, s)) && vfinite(ld3(nrm, s))) cand = pos;
+        }
+      }
+      found = block_max<BLOCK>(cand, s_warp);
+      if (found < 0) seed_pos = max(seed_pos - 4 * BLOCK, 0);
+    }
+    if (found < 0) break;
+    seed_pos = found;
+    const int seed = seed_at(seeds, N, found);
+    const int label_id = nreg + a.id_offset;
+    const int base = inl_total;
+
+    if (tid < 32)
+      planar_grow_warp(a, xyz, nrm, labels, queue, claim, inliers, seed, label_id, base, &s_res);
+    __syncthreads();
+    const int ninl = s_res.ninl;
+    steps += s_res.steps;
+    refits += s_res.refits;
+
+    // ---- CheckAndFinalize, ps/planar_region.h:189-224
+    bool ok = ninl >= a.min_inliers;
+    int nb = 0;
+    if (ok) {
+      // last inlier (FIFO order) with an in-bounds 8-neighbour of another label, :198-203
+      int start_i = -1;
+      for (int hi = ninl; hi > 0 && start_i < 0; hi -= BLOCK) {
+        const int i = hi - 1 - tid;
+        int q = -1;
+        if (i >= 0 && initial_predecessor_dir(labels, rows, cols, inliers[base + i], label_id) >= 0) q = i;
+        start_i = block_max<BLOCK>(q, s_warp);
+      }
+      if (start_i < 0) {
+        ok = false;  // boundary_indices_ empty -> CheckMinRowsAndCols fails, :205-212
+      } else {
+        if (tid == 0)
+          trace_boundary(labels, rows, cols, inliers[base + start_i], label_id, boundary + b_total,
+                         a.bcap - b_total, &s_trace);
+        __syncthreads();
+        nb = s_trace.nb;
+        if (s_trace.err) {
+          err |= s_trace.err;
+          ok = false;
+        }
+        // detail::CheckMinRowsAndCols(boundary, rows, cols, 3, 3), ps/planar_region.cc:91-106
+        if (!((s_trace.max_x - s_trace.min_x) > 3 && (s_trace.max_y - s_trace.min_y) > 3)) ok = false;
+        if (nb == 0) ok = false;
+      }
+    }
+    if (ok) {
+      // PlanarConvexHull(...).Size() >= 3 (patch P1), ps/planar_region.h:214-219: the hull
+      // of the plane-frame boundary points has >= 3 vertices iff they are not all collinear.
+      const PlaneFrame pf = make_plane_frame(s_res.plane);
+      const double kInf = 1.0e300;
+      double ax = kInf, ay = kInf, bx = -kInf, by = -kInf;
+      for (int k = tid; k < nb; k += BLOCK) {
+        double x, y;
+        plane_xy(pf, ld3(xyz, boundary[b_total + k]), &x, &y);
+        if (x < ax || (x == ax && y < ay)) { ax = x; ay = y; }
+        if (x > bx || (x == bx && y > by)) { bx = x; by = y; }
+      }
+      s_ax[tid] = ax; s_ay[tid] = ay; s_bx[tid] = bx; s_by[tid] = by;
+      __syncthreads();
+      for (int s = BLOCK / 2; s > 0; s >>= 1) {
+        if (tid < s) {
+          if (s_ax[tid + s] < s_ax[tid] || (s_ax[tid + s] == s_ax[tid] && s_ay[tid + s] < s_ay[tid])) {
+            s_ax[tid] = s_ax[tid + s]; s_ay[tid] = s_ay[tid + s];
+          }
+          if (s_bx[tid + s] > s_bx[tid] || (s_bx[tid + s] == s_bx[tid] && s_by[tid + s] > s_by[tid])) {
+            s_bx[tid] = s_bx[tid + s]; s_by[tid] = s_by[tid + s];
+          }
+        }
+        __syncthreads();
+      }
+      ax = s_ax[0]; ay = s_ay[0]; bx = s_bx[0]; by = s_by[0];
+      int off_line = 0;
+      for (int k = tid; k < nb; k += BLOCK) {
+        double x, y;
+        plane_xy(pf, ld3(xyz, boundary[b_total + k]), &x, &y);
+        const double cr = (bx - ax) * (y - ay) - (by - ay) * (x - ax);
+        if (cr != 0.0) off_line = 1;
+      }
+      off_line = __syncthreads_or(off_line);
+      if (!off_line) ok = false;
+    }
+    if (ok) {
+      // PolygonArea: sequential sum of cross products, ps/algorithms.h:264-292
+      if (tid == 0) {
+        V3 nsum{0.0f, 0.0f, 0.0f};
+        const int* b = boundary + b_total;
+        V3 pa = ld3(xyz, b[0]);
+        for (int i = 0; i < nb; ++i) {
+          V3 pb = ld3(xyz, b[(i + 1 == nb) ? 0 : i + 1]);
+          nsum = vadd(nsum, vcross(pa, pb));
+          pa = pb;
+        }
+        s_area = 0.5f * sqrtf(vsqn(nsum));
+      }
+      __syncthreads();
+      ok = s_area >= a.min_region_area;
+    }
+    if (ok && nreg >= a.rcap) {
+      err |= kErrRegionCap;
+      break;
+    }
+    if (ok) {
+      // discontinuity side output, ps/planar_region.h:360-417 (per boundary entry; the
+      // host turns the flags into the reference's set)
+      for (int k = tid; k < nb; k += BLOCK) {
+        const int idx = boundary[b_total + k];
+        const V3 pc = ld3(xyz, idx);
+        unsigned char flag = 0;
+        const float r2 = vsqn(pc);
+        const int x = idx / rows, y = idx % rows;
+        if (r2 > min_range_sq && r2 < max_range_sq && x > 0 && x < cols - 1 && y > 0 && y < rows - 1) {
+#pragma unroll
+          for (int d = 0; d < 4; ++d) {
+            const int ni = idx + kDx4[d] * rows + kDy4[d];
+            const V3 pn = ld3(xyz, ni);
+            if ((pc.z != pc.z) || (pn.z != pn.z)) continue;
+            if (labels[ni] != label_id) continue;
+            const V3 delta = qrotate(a.qx, a.qy, a.qz, a.qw, vsub(pc, pn));
+            const float cosang = vdot(ld3(nrm, idx), ld3(nrm, ni));
+            const float deg = (float)((double)cr_acosf(cosang) * (180.0 / 3.14159265358979323846));
+            if (fabsf(deg) < a.disc_angle && fabsf(delta.z) < a.disc_z_diff) continue;
+            if (fabsf(delta.z) / sqrtf(vsqn(delta)) < a.disc_z_ratio) continue;
+            flag = 1;
+          }
+        }
+        bflags[b_total + k] = flag;
+      }
+      if (tid == 0) {
+        PlanarMeta m;
+        m.inlier_begin = base; m.inlier_count = ninl;
+        m.boundary_begin = b_total; m.boundary_count = nb;
+        m.seed_index = seed; m.label_id = label_id;
+        for (int i = 0; i < 4; ++i) m.plane[i] = s_res.plane[i];
+        for (int i = 0; i < 3; ++i) m.centroid[i] = s_res.centroid[i];
+        m.area = s_area;
+        for (int i = 0; i < 10; ++i) m.est[i] = s_res.est[i];
+        meta[nreg] = m;
+      }
+      ++nreg;
+      inl_total += ninl;
+      b_total += nb;
+    } else {
+      // ps/segmentation.h:280-282
+      for (int i = tid; i < ninl; i += BLOCK) labels[inliers[base + i]] = kAlreadyExamedPoint;
+      any_failed = any_failed || (ninl > 0);
+    }
+    __syncthreads();
+    if (err & kErrBoundaryCap) break;
+  }
+  __syncthreads();
+  // ps/segmentation.h:287-291
+  if (any_failed) {
+    for (int i = tid; i < N; i += BLOCK)
+      if (labels[i] == kAlreadyExamedPoint) labels[i] = kUnlabeled;
+  }
+  if (tid == 0) {
+    a.stats[f].n_planar = nreg;
+    a.stats[f].planar_inliers = inl_total;
+    a.stats[f].boundary_len = b_total;
+    a.stats[f].error_flags |= err;
+    a.stats[f].grow_steps += steps;
+    a.stats[f].refits += refits;
+  }
+}
+
+}  // namespace pcseg

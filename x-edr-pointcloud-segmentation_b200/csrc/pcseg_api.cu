@@ -1,0 +1,853 @@
+// pcseg_api.cu -- C ABI (include/pcseg_b200.h) over the sm_100a kernels.
+//
+// Host-side plumbing only: argument checks that mirror the reference's CHECKs,
+// device buffers, kernel launches on the context's stream and result
+// materialisation.  No CPU implementation of any hot-path stage lives here:
+// if CUDA is unavailable pcseg_create fails and nothing else can be called.
+#include "../../include/pcseg_b200.h"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "grow_cluster.cuh"
+#include "grow_planar.cuh"
+#include "meanshift.cuh"
+#include "normals.cuh"
+#include "seeds.cuh"
+
+using namespace pcseg;
+
+namespace {
+
+constexpr int kGrowBlock = 256;
+constexpr int kInvCap = 4096;
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  cudaError_t ensure(size_t need) {
+    if (need <= bytes) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr;
+    bytes = 0;
+    cudaError_t e = cudaMalloc(&p, need);
+    if (e == cudaSuccess) bytes = need;
+    return e;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    bytes = 0;
+  }
+  template <typename T>
+  T* as() const { return static_cast<T*>(p); }
+};
+
+}  // namespace
+
+struct pcseg_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  std::string last_error;
+  long long launches = 0;
+  pcseg_batch* scratch = nullptr;  // cached single-frame workspace
+  DevBuf tmp_a, tmp_b;
+};
+
+struct pcseg_regions {
+  std::vector<int> inlier_offsets{0};
+  std::vector<int> inlier_indices;
+  std::vector<int> label_ids;
+  std::vector<int> seed_indices;
+  std::vector<float> planes, centroids, areas, estimators;
+  std::vector<int> boundary_offsets{0};
+  std::vector<int> boundary_indices;
+  std::vector<int> disc_offsets{0};
+  std::vector<int> disc_indices;
+  std::vector<int> hull_offsets{0};
+  std::vector<float> hull_points;
+  std::vector<float> seed_points;
+};
+
+struct pcseg_batch {
+  pcseg_ctx* ctx = nullptr;
+  int n_frames = 0, rows = 0, cols = 0;
+  size_t N = 0;
+  int qcap = 0, bcap = 0, rcap_planar = 0, rcap_cluster = 0;
+  DevBuf xyz, normals, labels, queue, claim, inl_planar, inl_cluster, boundary, bflags;
+  DevBuf meta_planar, meta_cluster, stats, inv_list, inv_count, seeds, n_seeds;
+  const float* xyz_dev = nullptr;      // where this run's points live on the device
+  const float* normals_dev = nullptr;  // where this run's normals live on the device
+  bool claim_ready = false;
+};
+
+namespace {
+
+#define CU_TRY(ctx, expr)                                                        \
+  do {                                                                           \
+    cudaError_t _e = (expr);                                                     \
+    if (_e != cudaSuccess) {                                                     \
+      (ctx)->last_error = std::string(#expr) + ": " + cudaGetErrorString(_e);    \
+      return PCSEG_ERR_CUDA;                                                     \
+    }                                                                            \
+  } while (0)
+
+bool is_device_ptr(const void* p) {
+  if (!p) return false;
+  cudaPointerAttributes at;
+  cudaError_t e = cudaPointerGetAttributes(&at, p);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+// Brings `bytes` at src (host or device) to the device; returns the device view.
+int to_device(pcseg_ctx* c, const void* src, size_t bytes, DevBuf* staging, const void** out) {
+  if (is_device_ptr(src)) {
+    *out = src;
+    return PCSEG_OK;
+  }
+  CU_TRY(c, staging->ensure(bytes));
+  CU_TRY(c, cudaMemcpyAsync(staging->p, src, bytes, cudaMemcpyHostToDevice, c->stream));
+  *out = staging->p;
+  return PCSEG_OK;
+}
+
+int from_device(pcseg_ctx* c, void* dst, const void* src_dev, size_t bytes) {
+  if (dst == src_dev) return PCSEG_OK;
+  cudaMemcpyKind k = is_device_ptr(dst) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+  CU_TRY(c, cudaMemcpyAsync(dst, src_dev, bytes, k, c->stream));
+  return PCSEG_OK;
+}
+
+__global__ void fill_int_kernel(int* p, size_t n, int v) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) p[i] = v;
+}
+
+int fill_int(pcseg_ctx* c, int* p, size_t n, int v) {
+  if (n == 0) return PCSEG_OK;
+  int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 8);
+  fill_int_kernel<<<blocks, 256, 0, c->stream>>>(p, n, v);
+  ++c->launches;
+  CU_TRY(c, cudaGetLastError());
+  return PCSEG_OK;
+}
+
+int check_planar_cfg(const pcseg_planar_config* cfg) {
+  // quirk Q8: size() < int and size() % int promote to size_t in the reference;
+  // period <= 0 is UB, min_region_inliers < 1 makes NaN seeds emit stale regions.
+  if (cfg->plane_model_reestimation_period <= 0 || cfg->min_region_inliers < 1) return PCSEG_ERR_CONFIG;
+  return PCSEG_OK;
+}
+int check_cluster_cfg(const pcseg_cluster_config* cfg) {
+  if (cfg->min_region_inliers < 1 || cfg->half_search_window < 0) return PCSEG_ERR_CONFIG;
+  if (cfg->half_search_window > 3) return PCSEG_ERR_UNSUPPORTED;
+  return PCSEG_OK;
+}
+
+int batch_alloc(pcseg_batch* b) {
+  pcseg_ctx* c = b->ctx;
+  const size_t F = b->n_frames, N = b->N;
+  b->qcap = (int)N + 1024;
+  b->bcap = (int)(2 * N) + 1024;
+  b->rcap_planar = (int)std::min<size_t>(N / 4 + 16, 4096);
+  b->rcap_cluster = (int)N + 1;
+  CU_TRY(c, b->labels.ensure(F * N * sizeof(int)));
+  CU_TRY(c, b->queue.ensure(F * (size_t)b->qcap * 2 * sizeof(int)));
+  CU_TRY(c, b->claim.ensure(F * N * sizeof(int)));
+  CU_TRY(c, b->inl_planar.ensure(F * N * sizeof(int)));
+  CU_TRY(c, b->inl_cluster.ensure(F * N * sizeof(int)));
+  CU_TRY(c, b->boundary.ensure(F * (size_t)b->bcap * sizeof(int)));
+  CU_TRY(c, b->bflags.ensure(F * (size_t)b->bcap));
+  CU_TRY(c, b->meta_planar.ensure(F * (size_t)b->rcap_planar * sizeof(PlanarMeta)));
+  CU_TRY(c, b->stats.ensure(F * sizeof(FrameStats)));
+  CU_TRY(c, b->inv_list.ensure(F * (size_t)kInvCap * sizeof(int)));
+  CU_TRY(c, b->inv_count.ensure(F * sizeof(int)));
+  int st = fill_int(c, b->claim.as<int>(), F * N, INT_MAX);
+  if (st) return st;
+  b->claim_ready = true;
+  return PCSEG_OK;
+}
+
+}  // namespace
+
+// ===========================================================================
+// Stage launchers (all asynchronous on ctx->stream)
+// ===========================================================================
+namespace {
+
+int run_normals(pcseg_batch* b, const float* xyz_dev, float* normals_dev, float* curvature_dev,
+                const pcseg_normals_params* p, const double sensor_t[3], int r0, int r1, int c0, int c1) {
+  pcseg_ctx* c = b->ctx;
+  if (r1 <= r0 || c1 <= c0) return PCSEG_OK;
+  NormalsArgs a;
+  a.xyz = xyz_dev;
+  a.normals = normals_dev;
+  a.curvature = curvature_dev;
+  a.rows = b->rows; a.cols = b->cols; a.n_frames = b->n_frames;
+  a.r0 = r0; a.r1 = r1; a.c0 = c0; a.c1 = c1;
+  a.min2 = p->min_neighbor_distance * p->min_neighbor_distance;  // ps/algorithms.h:111-114
+  a.max2 = p->max_neighbor_distance * p->max_neighbor_distance;
+  a.diag = p->include_diagonal_neighbors;
+  a.min_support = p->min_num_support_neighbors;
+  a.sx = (float)sensor_t[0]; a.sy = (float)sensor_t[1]; a.sz = (float)sensor_t[2];
+  a.inv_list = b->inv_list.as<int>();
+  a.inv_count = b->inv_count.as<int>();
+  a.inv_cap = kInvCap;
+  CU_TRY(c, cudaMemsetAsync(a.inv_count, 0, b->n_frames * sizeof(int), c->stream));
+  const int work = (r1 - r0) * (c1 - c0);
+  dim3 grid((work + 255) / 256, b->n_frames);
+  normals_kernel<<<grid, 256, 0, c->stream>>>(a);
+  normals_fixup_kernel<<<b->n_frames, 256, 0, c->stream>>>(a);
+  c->launches += 2;
+  CU_TRY(c, cudaGetLastError());
+  return PCSEG_OK;
+}
+
+int run_planar(pcseg_batch* b, const float* xyz_dev, const float* normals_dev, const int* seeds_dev,
+               int n_seeds, int seeds_stride, const int* n_seeds_dev, const pcseg_planar_config* cfg,
+               const float q[4], int id_offset) {
+  pcseg_ctx* c = b->ctx;
+  PlanarArgs a;
+  a.xyz = xyz_dev; a.normals = normals_dev; a.labels = b->labels.as<int>();
+  a.rows = b->rows; a.cols = b->cols;
+  a.seeds = seeds_dev; a.n_seeds = n_seeds; a.seeds_stride = seeds_stride; a.n_seeds_dev = n_seeds_dev;
+  a.max_plane_distance = cfg->max_plane_distance; a.min_region_area = cfg->min_region_area;
+  a.min_inliers = cfg->min_region_inliers; a.period = cfg->plane_model_reestimation_period;
+  a.disc_min_range = cfg->discontinuity_min_range; a.disc_max_range = cfg->discontinuity_max_range;
+  a.disc_angle = cfg->discontinuity_normal_angle_diff; a.disc_z_diff = cfg->discontinuity_z_diff;
+  a.disc_z_ratio = cfg->discontinuity_z_ratio;
+  a.qx = q[0]; a.qy = q[1]; a.qz = q[2]; a.qw = q[3];
+  a.id_offset = id_offset;
+  a.queue = b->queue.as<int>(); a.qcap = b->qcap;
+  a.claim = b->claim.as<int>(); a.inliers = b->inl_planar.as<int>();
+  a.boundary = b->boundary.as<int>(); a.bflags = b->bflags.as<unsigned char>(); a.bcap = b->bcap;
+  a.meta = b->meta_planar.as<PlanarMeta>(); a.rcap = b->rcap_planar;
+  a.stats = b->stats.as<FrameStats>();
+  planar_grow_kernel<kGrowBlock><<<b->n_frames, kGrowBlock, 0, c->stream>>>(a);
+  ++c->launches;
+  CU_TRY(c, cudaGetLastError());
+  return PCSEG_OK;
+}
+
+int run_cluster(pcseg_batch* b, const float* xyz_dev, const int* seeds_dev, int n_seeds,
+                const pcseg_cluster_config* cfg, int id_offset, int offset_from_planar) {
+  pcseg_ctx* c = b->ctx;
+  b->rcap_cluster = (int)(b->N / (size_t)cfg->min_region_inliers) + 1;
+  CU_TRY(c, b->meta_cluster.ensure((size_t)b->n_frames * b->rcap_cluster * sizeof(ClusterMeta)));
+  ClusterArgs a;
+  a.xyz = xyz_dev; a.labels = b->labels.as<int>();
+  a.rows = b->rows; a.cols = b->cols;
+  a.seeds = seeds_dev; a.n_seeds = seeds_dev ? n_seeds : (int)b->N;
+  a.min_inliers = cfg->min_region_inliers; a.sq_thr = cfg->squared_distance_threshold;
+  a.half_window = cfg->half_search_window;
+  a.id_offset = id_offset; a.id_offset_from_planar = offset_from_planar;
+  a.queue = b->queue.as<int>(); a.qcap = b->qcap;
+  a.claim = b->claim.as<int>(); a.inliers = b->inl_cluster.as<int>();
+  a.meta = b->meta_cluster.as<ClusterMeta>(); a.rcap = b->rcap_cluster;
+  a.stats = b->stats.as<FrameStats>();
+  cluster_grow_kernel<kGrowBlock><<<b->n_frames, kGrowBlock, 0, c->stream>>>(a);
+  ++c->launches;
+  CU_TRY(c, cudaGetLastError());
+  return PCSEG_OK;
+}
+
+int map_error_flags(pcseg_ctx* c, int flags) {
+  if (flags == 0) return PCSEG_OK;
+  c->last_error = "per-frame capacity/trace error flags = " + std::to_string(flags);
+  return PCSEG_ERR_CAPACITY;
+}
+
+// Host-side PlanarConvexHull output for one accepted region (result formatting:
+// the acceptance gate "hull has >= 3 vertices" already ran on the device).
+// ps/algorithms.h:526-549 with patch P1; PoseFromPlane / ConvexHull restated
+// (third-party, absent from the reference tree) as in the kernel's plane frame.
+struct HV3 { float x, y, z; };
+inline HV3 hcross(HV3 a, HV3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+inline HV3 hadd(HV3 a, HV3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+inline float hdot(HV3 a, HV3 b) { return a.x * b.x + (a.y * b.y + a.z * b.z); }
+inline HV3 hrot(float qx, float qy, float qz, float qw, HV3 v) {
+  HV3 qv{qx, qy, qz};
+  HV3 uv = hcross(qv, v);
+  uv = hadd(uv, uv);
+  HV3 t{v.x + qw * uv.x, v.y + qw * uv.y, v.z + qw * uv.z};
+  return hadd(t, hcross(qv, uv));
+}
+void host_planar_hull(const float* boundary_xyz, int nb, const float plane[4], std::vector<float>* out) {
+  HV3 n{plane[0], plane[1], plane[2]};
+  HV3 v1 = n;
+  float z = hdot(n, n);
+  if (z > 0.0f) { float s = sqrtf(z); v1 = {n.x / s, n.y / s, n.z / s}; }
+  HV3 v0{0.0f, 0.0f, 1.0f};
+  float c = hdot(v1, v0);
+  float qx, qy, qz, qw;
+  if (c < -1.0f + FLT_EPSILON) { qx = 1.0f; qy = qz = qw = 0.0f; }
+  else {
+    HV3 axis = hcross(v0, v1);
+    float s = sqrtf((1.0f + c) * 2.0f);
+    float invs = 1.0f / s;
+    qx = axis.x * invs; qy = axis.y * invs; qz = axis.z * invs; qw = s * 0.5f;
+  }
+  HV3 t{-plane[3] * n.x, -plane[3] * n.y, -plane[3] * n.z};
+  HV3 rt = hrot(-qx, -qy, -qz, qw, t);
+  HV3 ti{-rt.x, -rt.y, -rt.z};
+  struct P2 { double x, y; };
+  std::vector<P2> pts(nb);
+  for (int i = 0; i < nb; ++i) {
+    HV3 p{boundary_xyz[3 * i], boundary_xyz[3 * i + 1], boundary_xyz[3 * i + 2]};
+    HV3 pp = hadd(hrot(-qx, -qy, -qz, qw, p), ti);
+    pts[i] = {pp.x, pp.y};
+  }
+  std::sort(pts.begin(), pts.end(), [](const P2& a, const P2& b) { return a.x < b.x || (a.x == b.x && a.y < b.y); });
+  pts.erase(std::unique(pts.begin(), pts.end(), [](const P2& a, const P2& b) { return a.x == b.x && a.y == b.y; }), pts.end());
+  std::vector<P2> h;
+  int m = (int)pts.size();
+  if (m < 3) h = pts;
+  else {
+    h.resize(2 * m);
+    int k = 0;
+    auto cr = [](const P2& o, const P2& a, const P2& b) { return (a.x - o.x) * (b.y - o.y) - (a.y - o.y) * (b.x - o.x); };
+    for (int i = 0; i < m; ++i) { while (k >= 2 && cr(h[k - 2], h[k - 1], pts[i]) <= 0) --k; h[k++] = pts[i]; }
+    for (int i = m - 2, t0 = k + 1; i >= 0; --i) { while (k >= t0 && cr(h[k - 2], h[k - 1], pts[i]) <= 0) --k; h[k++] = pts[i]; }
+    h.resize(k - 1);
+  }
+  for (const P2& p : h) {
+    HV3 pp{(float)p.x, (float)p.y, 0.0f};
+    HV3 w = hadd(hrot(qx, qy, qz, qw, pp), t);
+    out->push_back(w.x); out->push_back(w.y); out->push_back(w.z);
+  }
+}
+
+}  // namespace
+
+// ===========================================================================
+// Region materialisation
+// ===========================================================================
+namespace {
+
+int collect_planar(pcseg_batch* b, int frame, pcseg_regions* r) {
+  pcseg_ctx* c = b->ctx;
+  FrameStats st;
+  CU_TRY(c, cudaMemcpyAsync(&st, b->stats.as<FrameStats>() + frame, sizeof(st), cudaMemcpyDeviceToHost, c->stream));
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  const int n = st.n_planar;
+  std::vector<PlanarMeta> meta(n);
+  std::vector<int> inl(st.planar_inliers), bnd(st.boundary_len);
+  std::vector<unsigned char> bfl(st.boundary_len);
+  if (n) CU_TRY(c, cudaMemcpyAsync(meta.data(), b->meta_planar.as<PlanarMeta>() + (size_t)frame * b->rcap_planar,
+                                   n * sizeof(PlanarMeta), cudaMemcpyDeviceToHost, c->stream));
+  if (!inl.empty()) CU_TRY(c, cudaMemcpyAsync(inl.data(), b->inl_planar.as<int>() + (size_t)frame * b->N,
+                                              inl.size() * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  if (!bnd.empty()) {
+    CU_TRY(c, cudaMemcpyAsync(bnd.data(), b->boundary.as<int>() + (size_t)frame * b->bcap,
+                              bnd.size() * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CU_TRY(c, cudaMemcpyAsync(bfl.data(), b->bflags.as<unsigned char>() + (size_t)frame * b->bcap, bfl.size(),
+                              cudaMemcpyDeviceToHost, c->stream));
+  }
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  // boundary xyz for the hull output: gather on the host from a device->host copy
+  // of just the boundary points (indexed copy kernel avoided: tiny data).
+  std::vector<float> bxyz(3 * bnd.size());
+  {
+    // one strided gather via cudaMemcpy2D is not possible for arbitrary indices;
+    // fetch the frame's points once if they are not host-visible.
+    std::vector<float> frame_xyz(3 * b->N);
+    CU_TRY(c, cudaMemcpyAsync(frame_xyz.data(), b->xyz_dev + (size_t)frame * b->N * 3, frame_xyz.size() * sizeof(float),
+                              cudaMemcpyDeviceToHost, c->stream));
+    CU_TRY(c, cudaStreamSynchronize(c->stream));
+    for (size_t i = 0; i < bnd.size(); ++i)
+      for (int k = 0; k < 3; ++k) bxyz[3 * i + k] = frame_xyz[3 * (size_t)bnd[i] + k];
+  }
+  for (int i = 0; i < n; ++i) {
+    const PlanarMeta& m = meta[i];
+    r->inlier_indices.insert(r->inlier_indices.end(), inl.begin() + m.inlier_begin,
+                             inl.begin() + m.inlier_begin + m.inlier_count);
+    r->inlier_offsets.push_back((int)r->inlier_indices.size());
+    r->label_ids.push_back(m.label_id);
+    r->seed_indices.push_back(m.seed_index);
+    r->planes.insert(r->planes.end(), m.plane, m.plane + 4);
+    r->centroids.insert(r->centroids.end(), m.centroid, m.centroid + 3);
+    r->areas.push_back(m.area);
+    r->estimators.insert(r->estimators.end(), m.est, m.est + 10);
+    r->boundary_indices.insert(r->boundary_indices.end(), bnd.begin() + m.boundary_begin,
+                               bnd.begin() + m.boundary_begin + m.boundary_count);
+    r->boundary_offsets.push_back((int)r->boundary_indices.size());
+    std::vector<int> disc;
+    for (int k = 0; k < m.boundary_count; ++k)
+      if (bfl[m.boundary_begin + k]) disc.push_back(bnd[m.boundary_begin + k]);
+    std::sort(disc.begin(), disc.end());
+    disc.erase(std::unique(disc.begin(), disc.end()), disc.end());
+    r->disc_indices.insert(r->disc_indices.end(), disc.begin(), disc.end());
+    r->disc_offsets.push_back((int)r->disc_indices.size());
+    host_planar_hull(bxyz.data() + 3 * (size_t)m.boundary_begin, m.boundary_count, m.plane, &r->hull_points);
+    r->hull_offsets.push_back((int)(r->hull_points.size() / 3));
+  }
+  return map_error_flags(c, st.error_flags);
+}
+
+int collect_cluster(pcseg_batch* b, int frame, pcseg_regions* r) {
+  pcseg_ctx* c = b->ctx;
+  FrameStats st;
+  CU_TRY(c, cudaMemcpyAsync(&st, b->stats.as<FrameStats>() + frame, sizeof(st), cudaMemcpyDeviceToHost, c->stream));
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  const int n = st.n_cluster;
+  std::vector<ClusterMeta> meta(n);
+  std::vector<int> inl(st.cluster_inliers);
+  if (n) CU_TRY(c, cudaMemcpyAsync(meta.data(), b->meta_cluster.as<ClusterMeta>() + (size_t)frame * b->rcap_cluster,
+                                   n * sizeof(ClusterMeta), cudaMemcpyDeviceToHost, c->stream));
+  if (!inl.empty()) CU_TRY(c, cudaMemcpyAsync(inl.data(), b->inl_cluster.as<int>() + (size_t)frame * b->N,
+                                              inl.size() * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  for (int i = 0; i < n; ++i) {
+    const ClusterMeta& m = meta[i];
+    r->inlier_indices.insert(r->inlier_indices.end(), inl.begin() + m.inlier_begin,
+                             inl.begin() + m.inlier_begin + m.inlier_count);
+    r->inlier_offsets.push_back((int)r->inlier_indices.size());
+    r->label_ids.push_back(m.label_id);
+  }
+  return map_error_flags(c, st.error_flags);
+}
+
+int get_scratch(pcseg_ctx* c, int rows, int cols, pcseg_batch** out) {
+  if (c->scratch && (c->scratch->rows != rows || c->scratch->cols != cols)) {
+    pcseg_batch_destroy(c->scratch);
+    c->scratch = nullptr;
+  }
+  if (!c->scratch) {
+    int st = pcseg_batch_create(c, 1, rows, cols, &c->scratch);
+    if (st) return st;
+  }
+  *out = c->scratch;
+  return PCSEG_OK;
+}
+
+int check_seeds_host(const int* seeds_host_or_dev, int n, size_t N, pcseg_ctx* c, DevBuf* staging, const int** dev) {
+  // Validates the range on the host copy (the reference would read out of
+  // bounds); device-resident seeds are trusted.
+  if (n == 0) { *dev = (const int*)staging->p; return PCSEG_OK; }
+  if (!is_device_ptr(seeds_host_or_dev)) {
+    for (int i = 0; i < n; ++i)
+      if (seeds_host_or_dev[i] < 0 || (size_t)seeds_host_or_dev[i] >= N) return PCSEG_ERR_SEED_RANGE;
+  }
+  const void* d;
+  int st = to_device(c, seeds_host_or_dev, (size_t)n * sizeof(int), staging, &d);
+  *dev = (const int*)d;
+  return st;
+}
+
+}  // namespace
+
+// ===========================================================================
+// extern "C" entry points
+// ===========================================================================
+extern "C" {
+
+void pcseg_default_normals_params(pcseg_normals_params* p) {
+  p->min_neighbor_distance = 0.1f;  // ps/algorithms.h:313-322 (float <- double literal)
+  p->max_neighbor_distance = 1.0f;
+  p->include_diagonal_neighbors = 1;
+  p->min_num_support_neighbors = 4;
+}
+void pcseg_default_planar_config(pcseg_planar_config* c) {
+  c->max_plane_distance = 0.05f;  // ps/planar_region.h:93-121
+  c->min_region_area = 0.05f;
+  c->min_region_inliers = 5;
+  c->plane_model_reestimation_period = 30;
+  c->discontinuity_min_range = 1.2f;
+  c->discontinuity_max_range = 4.0f;
+  c->discontinuity_normal_angle_diff = 5.0f;
+  c->discontinuity_z_diff = 0.05f;
+  c->discontinuity_z_ratio = 0.7f;
+}
+void pcseg_default_cluster_config(pcseg_cluster_config* c) {
+  c->min_region_inliers = 7;  // ps/cluster_region.h:53-63
+  c->squared_distance_threshold = 1.0f;
+  c->half_search_window = 1;
+}
+
+int pcseg_create(int device, pcseg_ctx** out) {
+  if (!out) return PCSEG_ERR_NULL;
+  *out = nullptr;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count) {
+    cudaGetLastError();
+    return PCSEG_ERR_CUDA;  // no CPU fallback
+  }
+  if (cudaSetDevice(device) != cudaSuccess) return PCSEG_ERR_CUDA;
+  pcseg_ctx* c = new pcseg_ctx();
+  c->device = device;
+  if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    delete c;
+    return PCSEG_ERR_CUDA;
+  }
+  *out = c;
+  return PCSEG_OK;
+}
+
+void pcseg_destroy(pcseg_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  if (c->scratch) pcseg_batch_destroy(c->scratch);
+  c->tmp_a.release();
+  c->tmp_b.release();
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+const char* pcseg_status_string(int s) {
+  switch (s) {
+    case PCSEG_OK: return "ok";
+    case PCSEG_ERR_NULL: return "null pointer (reference: CHECK(ptr))";
+    case PCSEG_ERR_DIMS: return "dimension mismatch or rows <= 1 (reference: CHECK_EQ / CHECK_GT(rows, 1))";
+    case PCSEG_ERR_CONFIG: return "config value that is undefined behaviour in the reference";
+    case PCSEG_ERR_CUDA: return "CUDA error";
+    case PCSEG_ERR_CAPACITY: return "internal per-frame buffer overflow";
+    case PCSEG_ERR_UNSUPPORTED: return "unsupported parameter (documented limit)";
+    case PCSEG_ERR_SEED_RANGE: return "seed index out of range";
+  }
+  return "unknown";
+}
+const char* pcseg_last_error(const pcseg_ctx* c) { return c ? c->last_error.c_str() : ""; }
+long long pcseg_launch_count(const pcseg_ctx* c) { return c ? c->launches : 0; }
+void* pcseg_stream(const pcseg_ctx* c) { return c ? (void*)c->stream : nullptr; }
+
+int pcseg_prepare_unlabeled_labels(pcseg_ctx* c, int* labels, int n) {
+  if (!c || !labels) return PCSEG_ERR_NULL;
+  if (n <= 0) return PCSEG_OK;
+  cudaSetDevice(c->device);
+  if (is_device_ptr(labels)) {
+    int st = fill_int(c, labels, (size_t)n, kUnlabeled);
+    if (st) return st;
+  } else {
+    CU_TRY(c, c->tmp_a.ensure((size_t)n * sizeof(int)));
+    int st = fill_int(c, c->tmp_a.as<int>(), (size_t)n, kUnlabeled);
+    if (st) return st;
+    CU_TRY(c, cudaMemcpyAsync(labels, c->tmp_a.p, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  }
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  return PCSEG_OK;
+}
+
+int pcseg_normals_organized(pcseg_ctx* c, const float* xyz, int rows, int cols, const double sensor_t[3],
+                            const pcseg_normals_params* params, int row_begin, int row_end, int col_begin,
+                            int col_end, float* normals, float* curvature) {
+  if (!c || !xyz || !normals || !params || !sensor_t) return PCSEG_ERR_NULL;
+  if (rows <= 0 || cols <= 0) return PCSEG_ERR_DIMS;
+  if (row_begin < 0 || col_begin < 0 || row_end > rows || col_end > cols) return PCSEG_ERR_DIMS;
+  cudaSetDevice(c->device);
+  pcseg_batch* b;
+  int st = get_scratch(c, rows, cols, &b);
+  if (st) return st;
+  const size_t N = b->N;
+  const void* xyz_dev;
+  if ((st = to_device(c, xyz, N * 3 * sizeof(float), &b->xyz, &xyz_dev))) return st;
+  // normals are in/out: cells outside the range keep the caller's values
+  float* nrm_dev;
+  const bool n_dev = is_device_ptr(normals);
+  const bool full = row_begin == 0 && col_begin == 0 && row_end == rows && col_end == cols;
+  if (n_dev) nrm_dev = normals;
+  else {
+    CU_TRY(c, b->normals.ensure(N * 3 * sizeof(float)));
+    nrm_dev = b->normals.as<float>();
+    if (!full) CU_TRY(c, cudaMemcpyAsync(nrm_dev, normals, N * 3 * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+  }
+  float* curv_dev = nullptr;
+  const bool cv_dev = curvature && is_device_ptr(curvature);
+  if (curvature) {
+    if (cv_dev) curv_dev = curvature;
+    else {
+      CU_TRY(c, c->tmp_b.ensure(N * sizeof(float)));
+      curv_dev = c->tmp_b.as<float>();
+      if (!full) CU_TRY(c, cudaMemcpyAsync(curv_dev, curvature, N * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    }
+  }
+  if ((st = run_normals(b, (const float*)xyz_dev, nrm_dev, curv_dev, params, sensor_t, row_begin, row_end, col_begin, col_end))) return st;
+  if (!n_dev && (st = from_device(c, normals, nrm_dev, N * 3 * sizeof(float)))) return st;
+  if (curvature && !cv_dev && (st = from_device(c, curvature, curv_dev, N * sizeof(float)))) return st;
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  return PCSEG_OK;
+}
+
+int pcseg_segment_planar(pcseg_ctx* c, const float* xyz, const float* normals, int rows, int cols,
+                         const float robot_q_xyzw[4], const int* seeds, int n_seeds,
+                         const pcseg_planar_config* cfg, int id_offset, int* labels, pcseg_regions** out) {
+  if (!c || !xyz || !normals || !cfg || !labels || !out || !robot_q_xyzw) return PCSEG_ERR_NULL;  // CHECK(regions), CHECK(labels)
+  if (n_seeds > 0 && !seeds) return PCSEG_ERR_NULL;
+  if (rows <= 1 || cols <= 0) return PCSEG_ERR_DIMS;  // CHECK_GT(points.Rows(), 1), ps/planar_region.h:264
+  int st = check_planar_cfg(cfg);
+  if (st) return st;
+  cudaSetDevice(c->device);
+  pcseg_batch* b;
+  if ((st = get_scratch(c, rows, cols, &b))) return st;
+  const size_t N = b->N;
+  const void *xyz_dev, *nrm_dev;
+  if ((st = to_device(c, xyz, N * 3 * sizeof(float), &b->xyz, &xyz_dev))) return st;
+  if ((st = to_device(c, normals, N * 3 * sizeof(float), &b->normals, &nrm_dev))) return st;
+  b->xyz_dev = (const float*)xyz_dev;
+  b->normals_dev = (const float*)nrm_dev;
+  CU_TRY(c, cudaMemcpyAsync(b->labels.p, labels, N * sizeof(int),
+                            is_device_ptr(labels) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+  CU_TRY(c, cudaMemsetAsync(b->stats.p, 0, sizeof(FrameStats), c->stream));
+  if (n_seeds > 0) {
+    const int* seeds_dev;
+    if ((st = check_seeds_host(seeds, n_seeds, N, c, &b->seeds, &seeds_dev))) return st;
+    if ((st = run_planar(b, b->xyz_dev, b->normals_dev, seeds_dev, n_seeds, 0, nullptr, cfg, robot_q_xyzw, id_offset))) return st;
+  }
+  if ((st = from_device(c, labels, b->labels.p, N * sizeof(int)))) return st;
+  pcseg_regions* r = new pcseg_regions();
+  st = collect_planar(b, 0, r);
+  if (st) { delete r; return st; }
+  *out = r;
+  return PCSEG_OK;
+}
+
+int pcseg_segment_cluster(pcseg_ctx* c, const float* xyz, int rows, int cols, const int* seeds, int n_seeds,
+                          const pcseg_cluster_config* cfg, int id_offset, int* labels, pcseg_regions** out) {
+  if (!c || !xyz || !cfg || !labels || !out) return PCSEG_ERR_NULL;
+  if (n_seeds > 0 && !seeds) return PCSEG_ERR_NULL;
+  if (rows <= 1 || cols <= 0) return PCSEG_ERR_DIMS;  // CHECK_GT(points.Rows(), 1), ps/cluster_region.h:154
+  int st = check_cluster_cfg(cfg);
+  if (st) return st;
+  cudaSetDevice(c->device);
+  pcseg_batch* b;
+  if ((st = get_scratch(c, rows, cols, &b))) return st;
+  const size_t N = b->N;
+  const void* xyz_dev;
+  if ((st = to_device(c, xyz, N * 3 * sizeof(float), &b->xyz, &xyz_dev))) return st;
+  b->xyz_dev = (const float*)xyz_dev;
+  CU_TRY(c, cudaMemcpyAsync(b->labels.p, labels, N * sizeof(int),
+                            is_device_ptr(labels) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+  CU_TRY(c, cudaMemsetAsync(b->stats.p, 0, sizeof(FrameStats), c->stream));
+  if (n_seeds > 0) {
+    const int* seeds_dev;
+    if ((st = check_seeds_host(seeds, n_seeds, N, c, &b->seeds, &seeds_dev))) return st;
+    if ((st = run_cluster(b, b->xyz_dev, seeds_dev, n_seeds, cfg, id_offset, 0))) return st;
+  }
+  if ((st = from_device(c, labels, b->labels.p, N * sizeof(int)))) return st;
+  pcseg_regions* r = new pcseg_regions();
+  st = collect_cluster(b, 0, r);
+  if (st) { delete r; return st; }
+  *out = r;
+  return PCSEG_OK;
+}
+
+}  // extern "C"
+
+namespace {
+
+int run_seed_finder(pcseg_batch* b, const float* xyz_dev, const float* nrm_dev, int nbhd, float max_d,
+                    int min_support) {
+  pcseg_ctx* c = b->ctx;
+  if (b->rows > b->cols) return PCSEG_ERR_UNSUPPORTED;  // transposed reads leave the buffer (UB in the reference)
+  if (nbhd < 1 || nbhd * nbhd >= kSeedMaxKeys) return PCSEG_ERR_UNSUPPORTED;
+  const size_t F = b->n_frames, N = b->N;
+  CU_TRY(c, b->seeds.ensure(F * N * sizeof(int)));
+  CU_TRY(c, b->n_seeds.ensure(F * sizeof(int)));
+  SeedArgs a;
+  a.xyz = xyz_dev; a.normals = nrm_dev; a.rows = b->rows; a.cols = b->cols;
+  a.half = nbhd / 2; a.nbhd = nbhd; a.max_plane_distance = max_d; a.min_support = min_support;
+  a.counts = b->queue.as<int>();  // scratch: the growth queue is idle here (F*qcap*2 >= F*N ints)
+  a.seeds = b->seeds.as<int>(); a.stride = (int)N; a.n_seeds = b->n_seeds.as<int>();
+  // counts are laid out [F][N] inside the queue buffer
+  dim3 grid((unsigned)((N + 255) / 256), (unsigned)F);
+  seed_support_count_kernel<<<grid, 256, 0, c->stream>>>(a);
+  seed_order_kernel<<<(unsigned)F, 32, 0, c->stream>>>(a);
+  c->launches += 2;
+  CU_TRY(c, cudaGetLastError());
+  return PCSEG_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int pcseg_seeds_plane_support(pcseg_ctx* c, const float* xyz, const float* normals, int rows, int cols,
+                              int neighborhood_size, float max_plane_distance, int min_num_support,
+                              int* seeds_out, int cap, int* n_out) {
+  if (!c || !xyz || !normals || !seeds_out || !n_out) return PCSEG_ERR_NULL;
+  if (rows <= 1 || cols <= 0) return PCSEG_ERR_DIMS;  // CHECK_GT(points.Rows(), 1), ps/segmentation.h:197
+  cudaSetDevice(c->device);
+  pcseg_batch* b;
+  int st = get_scratch(c, rows, cols, &b);
+  if (st) return st;
+  const size_t N = b->N;
+  const void *xyz_dev, *nrm_dev;
+  if ((st = to_device(c, xyz, N * 3 * sizeof(float), &b->xyz, &xyz_dev))) return st;
+  if ((st = to_device(c, normals, N * 3 * sizeof(float), &b->normals, &nrm_dev))) return st;
+  if ((st = run_seed_finder(b, (const float*)xyz_dev, (const float*)nrm_dev, neighborhood_size,
+                            max_plane_distance, min_num_support))) return st;
+  int n = 0;
+  CU_TRY(c, cudaMemcpyAsync(&n, b->n_seeds.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  *n_out = n;
+  const int ncopy = std::min(n, cap);
+  if (ncopy > 0 && (st = from_device(c, seeds_out, b->seeds.p, (size_t)ncopy * sizeof(int)))) return st;
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  return PCSEG_OK;
+}
+
+int pcseg_mean_shift_modes(pcseg_ctx* c, const float* xyz, int rows, int cols, const int* labels,
+                           int iterations, float* modes_out) {
+  if (!c || !xyz || !labels || !modes_out) return PCSEG_ERR_NULL;  // CHECK_NE(labels, nullptr)
+  if (rows <= 0 || cols <= 0) return PCSEG_ERR_DIMS;
+  cudaSetDevice(c->device);
+  const size_t N = (size_t)rows * cols;
+  const void *xyz_dev, *lab_dev;
+  int st;
+  DevBuf sx, sl;  // transient staging (big clouds: not worth caching)
+  if ((st = to_device(c, xyz, N * 3 * sizeof(float), &sx, &xyz_dev))) return st;
+  if ((st = to_device(c, labels, N * sizeof(int), &sl, &lab_dev))) { sx.release(); return st; }
+  const bool out_dev = is_device_ptr(modes_out);
+  DevBuf so;
+  ModeRecord* modes_dev = (ModeRecord*)modes_out;
+  if (!out_dev) {
+    if (so.ensure(N * sizeof(ModeRecord)) != cudaSuccess) { sx.release(); sl.release(); return PCSEG_ERR_CUDA; }
+    modes_dev = so.as<ModeRecord>();
+  }
+  MeanShiftArgs a;
+  a.xyz = (const float*)xyz_dev; a.labels = (const int*)lab_dev; a.rows = rows; a.cols = cols;
+  a.iterations = iterations; a.cell_begin = 0; a.cell_end = (int)N; a.modes = modes_dev;
+  meanshift_modes_kernel<<<(unsigned)((N + 255) / 256), 256, 0, c->stream>>>(a);
+  ++c->launches;
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess && !out_dev)
+    e = cudaMemcpyAsync(modes_out, modes_dev, N * sizeof(ModeRecord), cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+  sx.release(); sl.release(); so.release();
+  if (e != cudaSuccess) { c->last_error = cudaGetErrorString(e); return PCSEG_ERR_CUDA; }
+  return PCSEG_OK;
+}
+
+int pcseg_mean_shift(pcseg_ctx* c, const float* xyz, int rows, int cols, const pcseg_cluster_config* cfg,
+                     int iterations, int id_offset, int sort_mode, int* labels, pcseg_regions** out) {
+  (void)xyz; (void)rows; (void)cols; (void)cfg; (void)iterations; (void)id_offset; (void)sort_mode;
+  if (!c || !labels || !out) return PCSEG_ERR_NULL;
+  c->last_error = "mean-shift sort+growth phase (SURVEY 8f-2) not built yet; use pcseg_mean_shift_modes";
+  return PCSEG_ERR_UNSUPPORTED;
+}
+
+// ---- batch pipeline --------------------------------------------------------
+int pcseg_batch_create(pcseg_ctx* c, int n_frames, int rows, int cols, pcseg_batch** out) {
+  if (!c || !out) return PCSEG_ERR_NULL;
+  if (n_frames <= 0 || rows <= 0 || cols <= 0) return PCSEG_ERR_DIMS;
+  cudaSetDevice(c->device);
+  pcseg_batch* b = new pcseg_batch();
+  b->ctx = c; b->n_frames = n_frames; b->rows = rows; b->cols = cols; b->N = (size_t)rows * cols;
+  int st = batch_alloc(b);
+  if (st) { pcseg_batch_destroy(b); return st; }
+  *out = b;
+  return PCSEG_OK;
+}
+
+void pcseg_batch_destroy(pcseg_batch* b) {
+  if (!b) return;
+  cudaSetDevice(b->ctx->device);
+  cudaStreamSynchronize(b->ctx->stream);
+  DevBuf* all[] = {&b->xyz, &b->normals, &b->labels, &b->queue, &b->claim, &b->inl_planar, &b->inl_cluster,
+                   &b->boundary, &b->bflags, &b->meta_planar, &b->meta_cluster, &b->stats, &b->inv_list,
+                   &b->inv_count, &b->seeds, &b->n_seeds};
+  for (DevBuf* d : all) d->release();
+  delete b;
+}
+
+int pcseg_batch_run(pcseg_batch* b, const float* xyz, const pcseg_pipeline_params* p, float* normals_out,
+                    int* labels_out) {
+  if (!b || !xyz || !p) return PCSEG_ERR_NULL;
+  pcseg_ctx* c = b->ctx;
+  if (b->rows <= 1) return PCSEG_ERR_DIMS;
+  int st = check_planar_cfg(&p->planar);
+  if (st) return st;
+  if (p->run_cluster_stage && (st = check_cluster_cfg(&p->cluster))) return st;
+  cudaSetDevice(c->device);
+  const size_t F = b->n_frames, N = b->N;
+  const void* xyz_dev;
+  if ((st = to_device(c, xyz, F * N * 3 * sizeof(float), &b->xyz, &xyz_dev))) return st;
+  b->xyz_dev = (const float*)xyz_dev;
+  float* nrm_dev;
+  if (normals_out && is_device_ptr(normals_out)) nrm_dev = normals_out;
+  else {
+    CU_TRY(c, b->normals.ensure(F * N * 3 * sizeof(float)));
+    nrm_dev = b->normals.as<float>();
+  }
+  b->normals_dev = nrm_dev;
+  if ((st = run_normals(b, b->xyz_dev, nrm_dev, nullptr, &p->normals, p->sensor_translation, 0, b->rows, 0, b->cols))) return st;
+  if (normals_out && !is_device_ptr(normals_out) &&
+      (st = from_device(c, normals_out, nrm_dev, F * N * 3 * sizeof(float)))) return st;
+  if ((st = fill_int(c, b->labels.as<int>(), F * N, kUnlabeled))) return st;  // PrepareUnlabeledLabels
+  CU_TRY(c, cudaMemsetAsync(b->stats.p, 0, F * sizeof(FrameStats), c->stream));
+  const int* seeds_dev = nullptr;
+  int n_seeds = (int)N, stride = 0;
+  const int* n_seeds_dev = nullptr;
+  if (p->planar_seed_mode == PCSEG_SEEDS_PLANE_SUPPORT) {
+    if ((st = run_seed_finder(b, b->xyz_dev, nrm_dev, 9, 0.05f, 12))) return st;  // ps/segmentation.h:193-194 defaults
+    seeds_dev = b->seeds.as<int>(); stride = (int)N; n_seeds_dev = b->n_seeds.as<int>();
+  } else if (p->planar_seed_mode == PCSEG_SEEDS_EXPLICIT) {
+    if (p->n_planar_seeds > 0 && !p->planar_seeds) return PCSEG_ERR_NULL;
+    if (p->n_planar_seeds > 0) {
+      if ((st = check_seeds_host(p->planar_seeds, p->n_planar_seeds, N, c, &b->seeds, &seeds_dev))) return st;
+    }
+    n_seeds = p->n_planar_seeds;
+  }
+  if (!(p->planar_seed_mode == PCSEG_SEEDS_EXPLICIT && n_seeds == 0)) {
+    if ((st = run_planar(b, b->xyz_dev, nrm_dev, seeds_dev, n_seeds, stride, n_seeds_dev, &p->planar,
+                         p->robot_q_xyzw, 0))) return st;
+  }
+  if (p->run_cluster_stage) {
+    if ((st = run_cluster(b, b->xyz_dev, nullptr, (int)N, &p->cluster, 0, 1))) return st;
+  }
+  if (labels_out && (st = from_device(c, labels_out, b->labels.p, F * N * sizeof(int)))) return st;
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  return PCSEG_OK;
+}
+
+int pcseg_batch_frame_stats(pcseg_batch* b, int* stats8) {
+  if (!b || !stats8) return PCSEG_ERR_NULL;
+  pcseg_ctx* c = b->ctx;
+  cudaSetDevice(c->device);
+  static_assert(sizeof(FrameStats) == 8 * sizeof(int), "stats layout");
+  CU_TRY(c, cudaMemcpyAsync(stats8, b->stats.p, (size_t)b->n_frames * sizeof(FrameStats), cudaMemcpyDeviceToHost, c->stream));
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  return PCSEG_OK;
+}
+
+int pcseg_batch_regions(pcseg_batch* b, int frame, int kind, pcseg_regions** out) {
+  if (!b || !out) return PCSEG_ERR_NULL;
+  if (frame < 0 || frame >= b->n_frames) return PCSEG_ERR_DIMS;
+  cudaSetDevice(b->ctx->device);
+  pcseg_regions* r = new pcseg_regions();
+  int st = kind == 0 ? collect_planar(b, frame, r) : collect_cluster(b, frame, r);
+  if (st) { delete r; return st; }
+  *out = r;
+  return PCSEG_OK;
+}
+
+int* pcseg_batch_device_labels(pcseg_batch* b) { return b ? b->labels.as<int>() : nullptr; }
+float* pcseg_batch_device_normals(pcseg_batch* b) { return b ? const_cast<float*>(b->normals_dev) : nullptr; }
+
+// ---- accessors ---------------------------------------------------------------
+int pcseg_regions_count(const pcseg_regions* r) { return (int)r->label_ids.size(); }
+const int* pcseg_regions_inlier_offsets(const pcseg_regions* r) { return r->inlier_offsets.data(); }
+const int* pcseg_regions_inlier_indices(const pcseg_regions* r) { return r->inlier_indices.data(); }
+const int* pcseg_regions_label_ids(const pcseg_regions* r) { return r->label_ids.data(); }
+const int* pcseg_regions_seed_indices(const pcseg_regions* r) { return r->seed_indices.data(); }
+const float* pcseg_regions_planes(const pcseg_regions* r) { return r->planes.data(); }
+const float* pcseg_regions_centroids(const pcseg_regions* r) { return r->centroids.data(); }
+const float* pcseg_regions_areas(const pcseg_regions* r) { return r->areas.data(); }
+const float* pcseg_regions_estimators(const pcseg_regions* r) { return r->estimators.data(); }
+const int* pcseg_regions_boundary_offsets(const pcseg_regions* r) { return r->boundary_offsets.data(); }
+const int* pcseg_regions_boundary_indices(const pcseg_regions* r) { return r->boundary_indices.data(); }
+const int* pcseg_regions_discontinuous_offsets(const pcseg_regions* r) { return r->disc_offsets.data(); }
+const int* pcseg_regions_discontinuous_indices(const pcseg_regions* r) { return r->disc_indices.data(); }
+const int* pcseg_regions_hull_offsets(const pcseg_regions* r) { return r->hull_offsets.data(); }
+const float* pcseg_regions_hull_points(const pcseg_regions* r) { return r->hull_points.data(); }
+const float* pcseg_regions_seed_points(const pcseg_regions* r) { return r->seed_points.data(); }
+void pcseg_regions_free(pcseg_regions* r) { delete r; }
+
+}  // extern "C"
