@@ -166,6 +166,13 @@ int pcseg_batch_run(pcseg_batch*, const float* xyz,
 /* Per-frame counters after a run: {n_planar, n_cluster, planar_inliers,
  * cluster_inliers, boundary_len, error_flags, grow_steps, refits}. */
 int pcseg_batch_frame_stats(pcseg_batch*, int* stats8_per_frame);
+/* Device time of the last run's stages in ms (CUDA events on the context's
+ * stream): {normals + fix-up, label init + seed finder, planar growth,
+ * cluster growth}. */
+int pcseg_batch_stage_times(pcseg_batch*, float* ms4);
+/* Diagnostics (only in -DPCSEG_PROFILE builds, else PCSEG_ERR_UNSUPPORTED):
+ * clock64 totals per growth phase, 8 per frame. */
+int pcseg_batch_profile(pcseg_batch*, long long* out8_per_frame);
 /* Materialises one frame's regions (kind 0 = planar, 1 = cluster). */
 int pcseg_batch_regions(pcseg_batch*, int frame, int kind, pcseg_regions** out);
 /* Device pointers of the batch's resident results (labels int32[F*N],

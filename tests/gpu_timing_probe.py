@@ -17,6 +17,13 @@ for mode, name in ((pcseg.SEEDS_ALL_DESCENDING, "alldesc"), (pcseg.SEEDS_PLANE_S
     for it in range(3):
         t = time.time(); b.run(frames, p, labels_out=labels); dt = time.time() - t
         print(name, "run %d: %.1f ms  (%.1f Mpts/s)" % (it, dt * 1e3, F * rows * cols / dt / 1e6), flush=True)
+    print(name, "stage ms", b.stage_times(), flush=True)
+    try:
+        pr = b.profile()
+        tot = pr.sum(axis=0).astype(float)
+        print(name, "phase cycles/step (frame avg): eval %.0f accum %.0f nbr+atomic %.0f enqueue %.0f refit %.0f" % tuple(tot[:5] / max(b.frame_stats()[:, 6].sum(), 1) / 3))
+    except Exception as e:
+        print("no profile", e)
     st = b.frame_stats()
     print("stats frame0", st[0], "max steps", st[:, 6].max(), "err", st[:, 5].max())
     # parity of frame 0 and last frame vs oracle

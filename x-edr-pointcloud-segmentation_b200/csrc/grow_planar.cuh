@@ -43,7 +43,16 @@ struct PlanarArgs {
   PlanarMeta* meta;      // [F][rcap]
   int rcap;
   FrameStats* stats;     // [F]
+  long long* prof;       // nullable: [F][8] clock64 totals per phase (diagnostics)
 };
+
+#ifdef PCSEG_PROFILE
+#define PROF_T(var) long long var = clock64()
+#define PROF_ACC(slot, t0, t1) prof_acc[slot] += (t1) - (t0)
+#else
+#define PROF_T(var)
+#define PROF_ACC(slot, t0, t1)
+#endif
 
 struct GrowResult {  // warp 0 -> CTA broadcast
   int ninl;
@@ -78,8 +87,12 @@ __device__ __forceinline__ void planar_grow_warp(const PlanarArgs& a, const floa
   if (lane == 0) queue[0] = seed;
   __syncwarp();
   const int period = a.period;
+#ifdef PCSEG_PROFILE
+  long long prof_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#endif
   while (head < tail) {
     ++steps;
+    PROF_T(t0);
     const int m = min(32, tail - head);
     int cand = -1;
     V3 p{0.f, 0.f, 0.f};
@@ -90,6 +103,8 @@ __device__ __forceinline__ void planar_grow_warp(const PlanarArgs& a, const floa
       acc = plane_abs_distance(plane, p) < a.max_plane_distance;  // :168
     }
     unsigned amask = __ballot_sync(FULL, acc);
+    PROF_T(t1);
+    PROF_ACC(0, t0, t1);
     const int need = period - (ninl % period);
     int processed = m;
     bool refit = false;
@@ -117,6 +132,8 @@ __device__ __forceinline__ void planar_grow_warp(const PlanarArgs& a, const floa
       est_add(est, q);
     }
     __syncwarp();
+    PROF_T(t2);
+    PROF_ACC(1, t1, t2);
     // AddNeighbors, :229-255: (c-1,r), (c,r-1), (c,r+1), (c+1,r)
     int nb[4] = {-1, -1, -1, -1};
     bool el[4] = {false, false, false, false};
@@ -138,6 +155,8 @@ __device__ __forceinline__ void planar_grow_warp(const PlanarArgs& a, const floa
         if (el[s]) atomicMin(claim + nb[s], lane * 4 + s);
     }
     __syncwarp();
+    PROF_T(t3);
+    PROF_ACC(2, t2, t3);
     if (mine && !acc) labels[cand] = kUnlabeled;
     bool win[4];
 #pragma unroll
@@ -159,13 +178,21 @@ __device__ __forceinline__ void planar_grow_warp(const PlanarArgs& a, const floa
     tail += __popc(b0) + __popc(b1) + __popc(b2) + __popc(b3);
     head += processed;
     ninl += __popc(amask);
+    PROF_T(t4);
+    PROF_ACC(3, t3, t4);
     if (refit) {
       est_compute(est);   // plane_ = plane_estimator_.Plane(), :172-176
       plane = est.plane;
       ++refits;
     }
     __syncwarp();
+    PROF_T(t5);
+    PROF_ACC(4, t4, t5);
   }
+#ifdef PCSEG_PROFILE
+  if (lane == 0 && a.prof)
+    for (int i = 0; i < 8; ++i) a.prof[(size_t)blockIdx.x * 8 + i] += prof_acc[i];
+#endif
   // CheckAndFinalize first lines, :190-196
   if (ninl >= a.min_inliers && !est.up_to_date) est_compute(est);
   if (lane == 0) {

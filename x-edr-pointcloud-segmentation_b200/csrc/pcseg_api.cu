@@ -82,6 +82,8 @@ struct pcseg_batch {
   const float* xyz_dev = nullptr;      // where this run's points live on the device
   const float* normals_dev = nullptr;  // where this run's normals live on the device
   bool claim_ready = false;
+  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  DevBuf prof;
 };
 
 namespace {
@@ -170,6 +172,10 @@ int batch_alloc(pcseg_batch* b) {
   CU_TRY(c, b->stats.ensure(F * sizeof(FrameStats)));
   CU_TRY(c, b->inv_list.ensure(F * (size_t)kInvCap * sizeof(int)));
   CU_TRY(c, b->inv_count.ensure(F * sizeof(int)));
+#ifdef PCSEG_PROFILE
+  CU_TRY(c, b->prof.ensure(F * 8 * sizeof(long long)));
+  CU_TRY(c, cudaMemset(b->prof.p, 0, F * 8 * sizeof(long long)));
+#endif
   int st = fill_int(c, b->claim.as<int>(), F * N, INT_MAX);
   if (st) return st;
   b->claim_ready = true;
@@ -231,6 +237,7 @@ int run_planar(pcseg_batch* b, const float* xyz_dev, const float* normals_dev, c
   a.boundary = b->boundary.as<int>(); a.bflags = b->bflags.as<unsigned char>(); a.bcap = b->bcap;
   a.meta = b->meta_planar.as<PlanarMeta>(); a.rcap = b->rcap_planar;
   a.stats = b->stats.as<FrameStats>();
+  a.prof = b->prof.as<long long>();
   planar_grow_kernel<kGrowBlock><<<b->n_frames, kGrowBlock, 0, c->stream>>>(a);
   ++c->launches;
   CU_TRY(c, cudaGetLastError());
@@ -742,6 +749,7 @@ int pcseg_batch_create(pcseg_ctx* c, int n_frames, int rows, int cols, pcseg_bat
   b->ctx = c; b->n_frames = n_frames; b->rows = rows; b->cols = cols; b->N = (size_t)rows * cols;
   int st = batch_alloc(b);
   if (st) { pcseg_batch_destroy(b); return st; }
+  for (auto& e : b->ev) cudaEventCreate(&e);
   *out = b;
   return PCSEG_OK;
 }
@@ -754,6 +762,8 @@ void pcseg_batch_destroy(pcseg_batch* b) {
                    &b->boundary, &b->bflags, &b->meta_planar, &b->meta_cluster, &b->stats, &b->inv_list,
                    &b->inv_count, &b->seeds, &b->n_seeds};
   for (DevBuf* d : all) d->release();
+  b->prof.release();
+  for (auto& e : b->ev) if (e) cudaEventDestroy(e);
   delete b;
 }
 
@@ -777,7 +787,9 @@ int pcseg_batch_run(pcseg_batch* b, const float* xyz, const pcseg_pipeline_param
     nrm_dev = b->normals.as<float>();
   }
   b->normals_dev = nrm_dev;
+  cudaEventRecord(b->ev[0], c->stream);
   if ((st = run_normals(b, b->xyz_dev, nrm_dev, nullptr, &p->normals, p->sensor_translation, 0, b->rows, 0, b->cols))) return st;
+  cudaEventRecord(b->ev[1], c->stream);
   if (normals_out && !is_device_ptr(normals_out) &&
       (st = from_device(c, normals_out, nrm_dev, F * N * 3 * sizeof(float)))) return st;
   if ((st = fill_int(c, b->labels.as<int>(), F * N, kUnlabeled))) return st;  // PrepareUnlabeledLabels
@@ -795,13 +807,16 @@ int pcseg_batch_run(pcseg_batch* b, const float* xyz, const pcseg_pipeline_param
     }
     n_seeds = p->n_planar_seeds;
   }
+  cudaEventRecord(b->ev[2], c->stream);
   if (!(p->planar_seed_mode == PCSEG_SEEDS_EXPLICIT && n_seeds == 0)) {
     if ((st = run_planar(b, b->xyz_dev, nrm_dev, seeds_dev, n_seeds, stride, n_seeds_dev, &p->planar,
                          p->robot_q_xyzw, 0))) return st;
   }
+  cudaEventRecord(b->ev[3], c->stream);
   if (p->run_cluster_stage) {
     if ((st = run_cluster(b, b->xyz_dev, nullptr, (int)N, &p->cluster, 0, 1))) return st;
   }
+  cudaEventRecord(b->ev[4], c->stream);
   if (labels_out && (st = from_device(c, labels_out, b->labels.p, F * N * sizeof(int)))) return st;
   CU_TRY(c, cudaStreamSynchronize(c->stream));
   return PCSEG_OK;
@@ -825,6 +840,25 @@ int pcseg_batch_regions(pcseg_batch* b, int frame, int kind, pcseg_regions** out
   int st = kind == 0 ? collect_planar(b, frame, r) : collect_cluster(b, frame, r);
   if (st) { delete r; return st; }
   *out = r;
+  return PCSEG_OK;
+}
+
+int pcseg_batch_stage_times(pcseg_batch* b, float* ms4) {
+  if (!b || !ms4) return PCSEG_ERR_NULL;
+  pcseg_ctx* c = b->ctx;
+  cudaSetDevice(c->device);
+  CU_TRY(c, cudaEventSynchronize(b->ev[4]));
+  // normals (+fix-up) | label init + seed finder | planar growth | cluster growth
+  for (int i = 0; i < 4; ++i) CU_TRY(c, cudaEventElapsedTime(ms4 + i, b->ev[i], b->ev[i + 1]));
+  return PCSEG_OK;
+}
+
+int pcseg_batch_profile(pcseg_batch* b, long long* out8_per_frame) {
+  if (!b || !out8_per_frame) return PCSEG_ERR_NULL;
+  pcseg_ctx* c = b->ctx;
+  if (!b->prof.p) return PCSEG_ERR_UNSUPPORTED;
+  CU_TRY(c, cudaMemcpy(out8_per_frame, b->prof.p, (size_t)b->n_frames * 8 * sizeof(long long), cudaMemcpyDeviceToHost));
+  CU_TRY(c, cudaMemset(b->prof.p, 0, (size_t)b->n_frames * 8 * sizeof(long long)));
   return PCSEG_OK;
 }
 

@@ -61,7 +61,7 @@ pcseg_last_error pcseg_launch_count pcseg_stream pcseg_prepare_unlabeled_labels
 pcseg_normals_organized pcseg_segment_planar pcseg_segment_cluster
 pcseg_mean_shift_modes pcseg_mean_shift pcseg_seeds_plane_support
 pcseg_batch_create pcseg_batch_destroy pcseg_batch_run pcseg_batch_frame_stats
-pcseg_batch_regions pcseg_batch_device_labels pcseg_batch_device_normals
+pcseg_batch_regions pcseg_batch_stage_times pcseg_batch_profile pcseg_batch_device_labels pcseg_batch_device_normals
 pcseg_regions_count pcseg_regions_inlier_offsets pcseg_regions_inlier_indices
 pcseg_regions_label_ids pcseg_regions_seed_indices pcseg_regions_planes
 pcseg_regions_centroids pcseg_regions_areas pcseg_regions_estimators
@@ -309,6 +309,16 @@ class Batch:
     def frame_stats(self):
         out = np.zeros((self.n_frames, 8), np.int32)
         self.ctx._check(self.ctx.L.pcseg_batch_frame_stats(self.h, _addr(out)))
+        return out
+
+    def stage_times(self):
+        out = np.zeros(4, np.float32)
+        self.ctx._check(self.ctx.L.pcseg_batch_stage_times(self.h, _addr(out)))
+        return dict(zip(("normals", "seeds", "planar", "cluster"), [float(v) for v in out]))
+
+    def profile(self):
+        out = np.zeros((self.n_frames, 8), np.int64)
+        self.ctx._check(self.ctx.L.pcseg_batch_profile(self.h, _addr(out)))
         return out
 
     def regions(self, frame, kind):
