@@ -1,0 +1,340 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the geometric segmentation hot path.
+
+Metric (BASELINE.json): Mpoints/s segmented (normals + region-grow + plane fit).
+Workload at N=1: config C2 -- a batch of 256 synthetic 640x480 organized depth
+frames (floor + 3 boxes + noise), plane + cluster segmentation, frames sharded
+frame-wise (no collective; weak scaling: 256 frames per GPU).
+
+One step = one pass of the pipeline (ComputeNormalsOrganized ->
+SegmentRegions<PlanarRegion> -> SegmentRegions<ClusterRegion>) over the batch.
+  value : inputs resident in HBM, device time (CUDA events), max over ranks
+  e2e   : same call with HOST (pinned) buffers: H2D of the points and D2H of
+          normals + labels inside the timed region
+  --impl reference : the reference algorithm's CPU implementation (oracle/_ref
+          when built, else the oracle port) on all host cores, bounded sample.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "x-edr-pointcloud-segmentation_b200")
+for _p in (PKG, os.path.join(ROOT, "oracle")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np
+
+ROWS, COLS = 480, 640
+N_PTS = ROWS * COLS
+FRAMES_PER_GPU = 256
+METRIC = "Mpoints/s segmented (normals+region-grow+plane fit)"
+UNIT = "Mpoints/s"
+
+
+def _gen_frame(i):
+    import synth
+    return synth.c2_frame(i, FRAMES_PER_GPU, ROWS, COLS)
+
+
+def gen_frames(indices):
+    """C2 frames, generated in parallel on the host cores."""
+    import multiprocessing as mp
+    procs = max(1, min(len(indices), os.cpu_count() or 1, 32))
+    if procs == 1:
+        return np.stack([_gen_frame(i) for i in indices])
+    with mp.get_context("fork").Pool(procs) as pool:
+        return np.stack(pool.map(_gen_frame, list(indices), chunksize=1))
+
+
+def _cpu_pipeline(xyz):
+    """The reference algorithm on the CPU for one frame (oracle port)."""
+    import oracle
+    nrm = oracle.normals_organized(xyz, ROWS, COLS)
+    seeds = np.arange(N_PTS - 1, -1, -1, dtype=np.int32)
+    labels = np.full(N_PTS, -1, np.int32)
+    lab, regs = oracle.segment_planar(xyz, nrm, ROWS, COLS, seeds, labels)
+    lab2, cl = oracle.segment_cluster(xyz, ROWS, COLS, seeds, lab, id_offset=regs.n)
+    return lab2, regs.n, cl.n
+
+
+_FRAMES = None  # shared with forked workers (copy-on-write)
+
+
+def _cpu_worker(i):
+    _, n_planar, n_cluster = _cpu_pipeline(_FRAMES[i])
+    return n_planar, n_cluster
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region."""
+
+    def __init__(self, gpu_index):
+        self.rows = []
+        self.proc = None
+        self.gpu = gpu_index
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + q, "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+                for k, nme in enumerate(names):
+                    if r[2 + k].lower().startswith("active"):
+                        reasons.add(nme)
+            except Exception:
+                pass
+        return {"sm_mhz": statistics.median(sm) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def measured_peak_gbs():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+def run_reference(args, rank, world):
+    """CPU arm: reference algorithm on all host cores, bounded sample per step."""
+    if rank != 0:
+        return
+    import multiprocessing as mp
+    cores = os.cpu_count() or 1
+    sample = min(FRAMES_PER_GPU, 4 * cores)
+    kind = "port"  # oracle/_ref (reference sources against shims) validates the port in tests/
+    global _FRAMES
+    _FRAMES = gen_frames(list(range(sample)))
+    with mp.get_context("fork").Pool(cores) as pool:
+        times = []
+        for it in range(args.warmup + args.steps):
+            t0 = time.perf_counter()
+            pool.map(_cpu_worker, list(range(sample)), chunksize=1)
+            dt = time.perf_counter() - t0
+            if it >= args.warmup:
+                times.append(dt)
+    ms = 1e3 * sum(times) / len(times)
+    value = sample * N_PTS / (ms * 1e-3) / 1e6
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic (seeded analytic ray casting, SURVEY.md 8d C2)",
+        "config": {"workload": "C2: 640x480 organized depth frames, normals+planes+clusters, seeds all-descending",
+                   "frames_per_step": sample, "rows": ROWS, "cols": COLS},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
+                         "sample": "%d frames per step over %d worker processes" % (sample, cores)},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--frames", type=int, default=FRAMES_PER_GPU)
+    ap.add_argument("--cpu-sample", type=int, default=16)
+    ap.add_argument("--seed-mode", default="alldesc", choices=["alldesc", "planesupport"])
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    import pcseg
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    F = args.frames
+    # frame ids are disjoint across ranks (frame-wise sharding: frame i -> GPU i mod G)
+    ids = [(rank + world * k) % (FRAMES_PER_GPU * 8) for k in range(F)]
+    host = torch.from_numpy(gen_frames(ids)).pin_memory()           # [F, N, 3] pinned
+    dev_xyz = host.to("cuda", non_blocking=False)
+    out_normals = torch.empty((F, N_PTS, 3), dtype=torch.float32).pin_memory()
+    out_labels = torch.empty((F, N_PTS), dtype=torch.int32).pin_memory()
+
+    ctx = pcseg.Context(local_rank)
+    batch = pcseg.Batch(ctx, F, ROWS, COLS)
+    mode = pcseg.SEEDS_ALL_DESCENDING if args.seed_mode == "alldesc" else pcseg.SEEDS_PLANE_SUPPORT
+    params = pcseg.pipeline_params(seed_mode=mode, run_cluster=True)
+    stream = torch.cuda.ExternalStream(ctx.stream)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world > 1:
+            t = torch.tensor([x], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        return x
+
+    def timed(fn, steps):
+        """K steps bracketed by barrier+sync, device time via CUDA events on the
+        library's stream; also the host wall clock."""
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream)
+        e1.synchronize()
+        wall = (time.perf_counter() - t0) * 1e3
+        barrier()
+        return max_over_ranks(e0.elapsed_time(e1)), max_over_ranks(wall)
+
+    # ---- device-resident arm (value) ----
+    run_dev = lambda: batch.run(dev_xyz.data_ptr(), params)
+    for _ in range(args.warmup):
+        run_dev()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    l0 = ctx.launches
+    stage_acc = {"normals": 0.0, "seeds": 0.0, "planar": 0.0, "cluster": 0.0}
+
+    def run_dev_acc():
+        run_dev()
+        for k, v in batch.stage_times().items():
+            stage_acc[k] += v
+
+    dev_ms, dev_wall = timed(run_dev_acc, args.steps)
+    launches = ctx.launches - l0
+    clocks = sampler.stop() if rank == 0 else None
+    stats = batch.frame_stats()
+    ms_per_step = dev_ms / args.steps
+    total_pts = F * N_PTS * world
+    value = total_pts / (ms_per_step * 1e-3) / 1e6
+
+    # ---- end-to-end arm (host buffers through the C ABI) ----
+    host_np = host.numpy()
+    on_np, ol_np = out_normals.numpy(), out_labels.numpy()
+    run_e2e = lambda: batch.run(host_np, params, normals_out=on_np, labels_out=ol_np)
+    for _ in range(2):
+        run_e2e()
+    e2e_ms, e2e_wall = timed(run_e2e, args.steps)
+    e2e_ms_step = max(e2e_ms, e2e_wall) / args.steps
+    e2e_value = total_pts / (e2e_ms_step * 1e-3) / 1e6
+    e2e_ok = int(stats[:, 5].max()) == 0
+
+    # ---- single frame latency ----
+    b1 = pcseg.Batch(ctx, 1, ROWS, COLS)
+    lat = []
+    for it in range(5):
+        t0 = time.perf_counter()
+        b1.run(dev_xyz.data_ptr(), params)
+        lat.append((time.perf_counter() - t0) * 1e3)
+    b1.close()
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (live stage timings) ----
+    stage_ms = {k: v / args.steps for k, v in stage_acc.items()}
+    peak, peak_kind = measured_peak_gbs()
+    dom = max(("planar", "normals", "cluster"), key=lambda k: stage_ms[k])
+    alg_bytes = {"normals": 24.0 * F * N_PTS,            # 12 B read + 12 B write per point
+                 "planar": 24.0 * F * N_PTS,             # point + label rd/wr + inlier index per point entering
+                 "cluster": 24.0 * float((F * N_PTS) - int(stats[:, 2].sum()))}
+    roof = {}
+    for k in ("normals", "planar", "cluster"):
+        ach = alg_bytes[k] / (stage_ms[k] * 1e-3) / 1e9 if stage_ms[k] > 0 else 0.0
+        roof[k] = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                   "traffic": None, "kernel_ms": stage_ms[k], "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)"}
+    roofline = dict(roof[dom])
+    roofline["kernel"] = {"planar": "planar_grow_kernel", "normals": "normals_kernel", "cluster": "cluster_grow_kernel"}[dom]
+    roofline["note"] = ("latency-bound serial FIFO chain (one re-fit per 30 inliers), not bandwidth-bound; "
+                        "see DESIGN.md and profiles/")
+
+    # ---- CPU baseline: oracle port, single thread, bounded sample ----
+    ns = min(args.cpu_sample, F)
+    t0 = time.perf_counter()
+    mismatched_frames = 0
+    for i in range(ns):
+        lab_cpu, _, _ = _cpu_pipeline(host_np[i])
+        mismatched_frames += int(not np.array_equal(lab_cpu, ol_np[i]))  # oracle as the checker
+    cpu_s = time.perf_counter() - t0
+    cpu_value = ns * N_PTS / cpu_s / 1e6
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic (seeded analytic ray casting, SURVEY.md 8d C2)",
+        "config": {"workload": "C2: batch of %d 640x480 organized depth frames per GPU, normals+planes+clusters, "
+                               "planar seeds %s, frame-wise sharding" % (F, args.seed_mode),
+                   "frames_per_gpu": F, "rows": ROWS, "cols": COLS, "points_per_step": total_pts,
+                   "l2": "inputs larger than L2 (%.0f MB of points per GPU per step)" % (F * N_PTS * 12 / 1e6)},
+        "p50_frame_ms": ms_per_step, "latency_ms_single_frame": statistics.median(lat),
+        "stage_ms": stage_ms,
+        "regions_per_frame": {"planar": float(stats[:, 0].mean()), "cluster": float(stats[:, 1].mean())},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(F * N_PTS * 12) * world,
+                "d2h_bytes_per_step": int(F * N_PTS * 16) * world, "ms_per_step": e2e_ms_step,
+                "outputs": "normals + labels to pinned host memory", "ok": e2e_ok},
+        "gpu_launches": int(launches),
+        "roofline": roofline, "roofline_all": roof,
+        "cpu_baseline": {"value": cpu_value, "unit": UNIT, "cores": 1, "kind": "port",
+                         "sample": "%d frames of the same batch, oracle port single-threaded, %.1f s" % (ns, cpu_s)},
+        "parity": {"frames_checked_vs_oracle": ns, "frames_with_label_mismatch": mismatched_frames},
+        "clocks": clocks, "host_cores": os.cpu_count(),
+    }
+    print(json.dumps(line), flush=True)
+    batch.close()
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -21,7 +21,7 @@ for mode, name in ((pcseg.SEEDS_ALL_DESCENDING, "alldesc"), (pcseg.SEEDS_PLANE_S
     try:
         pr = b.profile()
         tot = pr.sum(axis=0).astype(float)
-        print(name, "phase cycles/step (frame avg): eval %.0f accum %.0f nbr+atomic %.0f enqueue %.0f refit %.0f" % tuple(tot[:5] / max(b.frame_stats()[:, 6].sum(), 1) / 3))
+        print(name, "phase cycles/step: eval %.0f cut+accum %.0f nbr+claim %.0f enqueue %.0f refit %.0f | cut+stores %.0f masktest+rej %.0f" % tuple(tot[:7] / max(b.frame_stats()[:, 6].sum(), 1) / 3))
     except Exception as e:
         print("no profile", e)
     st = b.frame_stats()

@@ -91,6 +91,22 @@ __device__ __forceinline__ int block_max(int v, int* s_warp) {
   return r;
 }
 
+// cell -> (row, col) for cell < 2^24 without an integer division: float
+// reciprocal estimate corrected by one step (exact for the stated range).
+struct FastDiv {
+  int d;
+  float inv;
+};
+__host__ __device__ inline FastDiv make_fastdiv(int d) { return FastDiv{d, 1.0f / (float)d}; }
+__device__ __forceinline__ void fast_divmod(const FastDiv& fd, int x, int* q, int* r) {
+  int qq = __float2int_rz(((float)x + 0.5f) * fd.inv);
+  int rr = x - qq * fd.d;
+  if (rr < 0) { --qq; rr += fd.d; }
+  else if (rr >= fd.d) { ++qq; rr -= fd.d; }
+  *q = qq;
+  *r = rr;
+}
+
 // Seed list access: seeds == nullptr means "all indices descending"
 // (seeds[k] = N-1-k, ps/clustering_test.cc:57-59).
 __device__ __forceinline__ int seed_at(const int* seeds, int N, int k) {

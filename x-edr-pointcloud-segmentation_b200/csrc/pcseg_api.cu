@@ -8,12 +8,13 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
 
 #include "grow_cluster.cuh"
-#include "grow_planar.cuh"
+#include "planar_kernel.cuh"
 #include "meanshift.cuh"
 #include "normals.cuh"
 #include "seeds.cuh"
@@ -238,7 +239,22 @@ int run_planar(pcseg_batch* b, const float* xyz_dev, const float* normals_dev, c
   a.meta = b->meta_planar.as<PlanarMeta>(); a.rcap = b->rcap_planar;
   a.stats = b->stats.as<FrameStats>();
   a.prof = b->prof.as<long long>();
-  planar_grow_kernel<kGrowBlock><<<b->n_frames, kGrowBlock, 0, c->stream>>>(a);
+  // shared-memory fast path when the 1-bit/cell mask and the FIFO ring fit
+  a.mask_words = (int)((b->N + 31) / 32);
+  a.ring = 2048;
+  const size_t smem_fixed = 32 * 11 * sizeof(float) + kHashSize * sizeof(unsigned);
+  size_t smem = (size_t)a.mask_words * 4 + (size_t)a.ring * 20 + smem_fixed;
+  const size_t smem_static = 9 * 1024;  // static shared memory of the kernel (reductions)
+  const size_t smem_max = 227 * 1024 - smem_static;
+  bool use_smem = b->N < (1u << 24) && (size_t)a.mask_words * 4 + 256 * 20 + smem_fixed <= smem_max &&
+                  !getenv("PCSEG_FORCE_GLOBAL_PATH");
+  if (use_smem) {
+    while (smem > smem_max) { a.ring /= 2; smem = (size_t)a.mask_words * 4 + (size_t)a.ring * 20 + smem_fixed; }
+    CU_TRY(c, cudaFuncSetAttribute(planar_grow_kernel<kGrowBlock, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    planar_grow_kernel<kGrowBlock, true><<<b->n_frames, kGrowBlock, smem, c->stream>>>(a);
+  } else {
+    planar_grow_kernel<kGrowBlock, false><<<b->n_frames, kGrowBlock, 0, c->stream>>>(a);
+  }
   ++c->launches;
   CU_TRY(c, cudaGetLastError());
   return PCSEG_OK;

@@ -38,6 +38,12 @@ __device__ __forceinline__ bool vhasnan(V3 a) { return (a.x != a.x) || (a.y != a
 __device__ __forceinline__ float cr_atan2f(float y, float x) { return (float)atan2((double)y, (double)x); }
 __device__ __forceinline__ float cr_cosf(float x) { return (float)cos((double)x); }
 __device__ __forceinline__ float cr_sinf(float x) { return (float)sin((double)x); }
+__device__ __forceinline__ void cr_sincosf(float x, float* s, float* c) {
+  double sd, cd;
+  sincos((double)x, &sd, &cd);
+  *s = (float)sd;
+  *c = (float)cd;
+}
 __device__ __forceinline__ float cr_acosf(float x) { return (float)acos((double)x); }
 
 // Hyperplane(n, e): offset = -n.dot(e); absDistance = |n.dot(p) + offset|
@@ -119,8 +125,8 @@ __device__ __noinline__ void eig3_direct(const Sym3& mat, float evals[3], V3* ev
   q = (q < 0.0f) ? 0.0f : q;
   float rho = sqrtf(a_over_3);
   float theta = cr_atan2f(sqrtf(q), half_b) * s_inv3;
-  float cos_theta = cr_cosf(theta);
-  float sin_theta = cr_sinf(theta);
+  float cos_theta, sin_theta;
+  cr_sincosf(theta, &sin_theta, &cos_theta);
   evals[0] = c2_over_3 - rho * (cos_theta + s_sqrt3 * sin_theta);
   evals[1] = c2_over_3 - rho * (cos_theta - s_sqrt3 * sin_theta);
   evals[2] = c2_over_3 + 2.0f * rho * cos_theta;

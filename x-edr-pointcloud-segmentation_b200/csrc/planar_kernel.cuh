@@ -1,0 +1,261 @@
+// planar_kernel.cuh -- the per-frame planar segmentation kernel (seed loop,
+// FIFO growth, CheckAndFinalize).  See grow_planar.cuh / grow_planar_smem.cuh.
+#pragma once
+#include "grow_planar.cuh"
+#include "grow_planar_smem.cuh"
+
+namespace pcseg {
+
+// SMEM = true : labels mirrored as a 1-bit/cell mask + FIFO ring in dynamic
+//               shared memory (planar_grow_warp_smem); needs
+//               mask_words*4 + ring*20 + 32*11*4 + kHashSize*4 bytes.
+// SMEM = false: everything through L2 (planar_grow_warp); any cloud size.
+template <int BLOCK, bool SMEM>
+__global__ void __launch_bounds__(BLOCK) planar_grow_kernel(PlanarArgs a) {
+  extern __shared__ __align__(16) unsigned char dyn_smem[];
+  const int f = blockIdx.x;
+  const int tid = threadIdx.x;
+  const int rows = a.rows, cols = a.cols;
+  const int N = rows * cols;
+  const float* __restrict__ xyz = a.xyz + (size_t)f * N * 3;
+  const float* __restrict__ nrm = a.normals + (size_t)f * N * 3;
+  volatile int* labels = a.labels + (size_t)f * N;
+  volatile int* queue = a.queue + (size_t)f * a.qcap;
+  int* claim = a.claim + (size_t)f * N;
+  int* inliers = a.inliers + (size_t)f * N;
+  int* boundary = a.boundary + (size_t)f * a.bcap;
+  unsigned char* bflags = a.bflags + (size_t)f * a.bcap;
+  PlanarMeta* meta = a.meta + (size_t)f * a.rcap;
+  const int* seeds = nullptr;
+  int n_seeds = N;
+  if (a.seeds) {
+    seeds = a.seeds_stride > 0 ? a.seeds + (size_t)f * a.seeds_stride : a.seeds;
+    n_seeds = a.seeds_stride > 0 ? a.n_seeds_dev[f] : a.n_seeds;
+  }
+
+  __shared__ int s_warp[BLOCK / 32 + 1];
+  __shared__ GrowResult s_res;
+  __shared__ TraceResult s_trace;
+  __shared__ float s_area;
+  __shared__ double s_ax[BLOCK], s_ay[BLOCK], s_bx[BLOCK], s_by[BLOCK];
+
+  PlanarSmem sm;
+  int tag_base = 0;
+  if constexpr (SMEM) {
+    sm.mask = reinterpret_cast<unsigned*>(dyn_smem);
+    sm.q_tag = reinterpret_cast<int*>(sm.mask + a.mask_words);
+    sm.q_cell = sm.q_tag + a.ring;
+    sm.q_xyz = reinterpret_cast<float*>(sm.q_cell + a.ring);
+    sm.stage = sm.q_xyz + 3 * a.ring;
+    sm.htab = reinterpret_cast<unsigned*>(sm.stage + 32 * 11);
+    sm.ring = a.ring;
+    for (int i = tid; i < a.ring; i += BLOCK) sm.q_tag[i] = -1;
+    for (int i = tid; i < kHashSize; i += BLOCK) sm.htab[i] = kHashEmpty;
+    // mask bit <=> labels[cell] == kUnlabeled
+    const int lane = tid & 31;
+    for (int b0 = (tid >> 5) * 32; b0 < a.mask_words * 32; b0 += BLOCK) {
+      const int cell = b0 + lane;
+      const bool u = cell < N && labels[cell] == kUnlabeled;
+      const unsigned bits = __ballot_sync(0xffffffffu, u);
+      if (lane == 0) sm.mask[b0 >> 5] = bits;
+    }
+    __syncthreads();
+  }
+  (void)tag_base;
+
+  int seed_pos = n_seeds;
+  int nreg = 0, inl_total = 0, b_total = 0, err = 0, steps = 0, refits = 0;
+  bool any_failed = false;
+  const float min_range_sq = a.disc_min_range * a.disc_min_range;  // eigenmath::Square
+  const float max_range_sq = a.disc_max_range * a.disc_max_range;
+
+  while (true) {
+    // ---- next usable seed (ps/segmentation.h:254-260).  A seed with a
+    // non-finite point or normal fails its own plane test (NaN distance), adds
+    // no inlier and leaves labels untouched: skipping it here is exact.
+    int found = -1;
+    while (seed_pos > 0 && found < 0) {
+      int cand = -1;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        int pos = seed_pos - 1 - (tid + k * BLOCK);
+        if (pos >= 0 && cand < 0) {
+          int s = seed_at(seeds, N, pos);
+          bool unl;
+          if constexpr (SMEM) unl = mask_test(sm.mask, s);
+          else unl = labels[s] == kUnlabeled;
+          if (unl && vfinite(ld3(xyz, s)) && vfinite(ld3(nrm, s))) cand = pos;
+        }
+      }
+      found = block_max<BLOCK>(cand, s_warp);
+      if (found < 0) seed_pos = max(seed_pos - 4 * BLOCK, 0);
+    }
+    if (found < 0) break;
+    seed_pos = found;
+    const int seed = seed_at(seeds, N, found);
+    const int label_id = nreg + a.id_offset;
+    const int base = inl_total;
+
+    if (tid < 32) {
+      if constexpr (SMEM)
+        planar_grow_warp_smem(a, xyz, nrm, a.labels + (size_t)f * N, a.queue + (size_t)f * a.qcap, inliers, seed,
+                              label_id, base, tag_base, sm, &s_res);
+      else
+        planar_grow_warp(a, xyz, nrm, labels, queue, claim, inliers, seed, label_id, base, &s_res);
+    }
+    __syncthreads();
+    const int ninl = s_res.ninl;
+    tag_base += s_res.tail;
+    steps += s_res.steps;
+    refits += s_res.refits;
+
+    // ---- CheckAndFinalize, ps/planar_region.h:189-224
+    bool ok = ninl >= a.min_inliers;
+    int nb = 0;
+    if (ok) {
+      // last inlier (FIFO order) with an in-bounds 8-neighbour of another label, :198-203
+      int start_i = -1;
+      for (int hi = ninl; hi > 0 && start_i < 0; hi -= BLOCK) {
+        const int i = hi - 1 - tid;
+        int q = -1;
+        if (i >= 0 && initial_predecessor_dir(labels, rows, cols, inliers[base + i], label_id) >= 0) q = i;
+        start_i = block_max<BLOCK>(q, s_warp);
+      }
+      if (start_i < 0) {
+        ok = false;  // boundary_indices_ empty -> CheckMinRowsAndCols fails, :205-212
+      } else {
+        if (tid == 0)
+          trace_boundary(labels, rows, cols, inliers[base + start_i], label_id, boundary + b_total,
+                         a.bcap - b_total, &s_trace);
+        __syncthreads();
+        nb = s_trace.nb;
+        if (s_trace.err) {
+          err |= s_trace.err;
+          ok = false;
+        }
+        // detail::CheckMinRowsAndCols(boundary, rows, cols, 3, 3), ps/planar_region.cc:91-106
+        if (!((s_trace.max_x - s_trace.min_x) > 3 && (s_trace.max_y - s_trace.min_y) > 3)) ok = false;
+        if (nb == 0) ok = false;
+      }
+    }
+    if (ok) {
+      // PlanarConvexHull(...).Size() >= 3 (patch P1), ps/planar_region.h:214-219: the hull
+      // of the plane-frame boundary points has >= 3 vertices iff they are not all collinear.
+      const PlaneFrame pf = make_plane_frame(s_res.plane);
+      const double kInf = 1.0e300;
+      double ax = kInf, ay = kInf, bx = -kInf, by = -kInf;
+      for (int k = tid; k < nb; k += BLOCK) {
+        double x, y;
+        plane_xy(pf, ld3(xyz, boundary[b_total + k]), &x, &y);
+        if (x < ax || (x == ax && y < ay)) { ax = x; ay = y; }
+        if (x > bx || (x == bx && y > by)) { bx = x; by = y; }
+      }
+      s_ax[tid] = ax; s_ay[tid] = ay; s_bx[tid] = bx; s_by[tid] = by;
+      __syncthreads();
+      for (int s = BLOCK / 2; s > 0; s >>= 1) {
+        if (tid < s) {
+          if (s_ax[tid + s] < s_ax[tid] || (s_ax[tid + s] == s_ax[tid] && s_ay[tid + s] < s_ay[tid])) {
+            s_ax[tid] = s_ax[tid + s]; s_ay[tid] = s_ay[tid + s];
+          }
+          if (s_bx[tid + s] > s_bx[tid] || (s_bx[tid + s] == s_bx[tid] && s_by[tid + s] > s_by[tid])) {
+            s_bx[tid] = s_bx[tid + s]; s_by[tid] = s_by[tid + s];
+          }
+        }
+        __syncthreads();
+      }
+      ax = s_ax[0]; ay = s_ay[0]; bx = s_bx[0]; by = s_by[0];
+      int off_line = 0;
+      for (int k = tid; k < nb; k += BLOCK) {
+        double x, y;
+        plane_xy(pf, ld3(xyz, boundary[b_total + k]), &x, &y);
+        const double cr = (bx - ax) * (y - ay) - (by - ay) * (x - ax);
+        if (cr != 0.0) off_line = 1;
+      }
+      off_line = __syncthreads_or(off_line);
+      if (!off_line) ok = false;
+    }
+    if (ok) {
+      // PolygonArea: sequential sum of cross products, ps/algorithms.h:264-292
+      if (tid == 0) {
+        V3 nsum{0.0f, 0.0f, 0.0f};
+        const int* b = boundary + b_total;
+        V3 pa = ld3(xyz, b[0]);
+        for (int i = 0; i < nb; ++i) {
+          V3 pb = ld3(xyz, b[(i + 1 == nb) ? 0 : i + 1]);
+          nsum = vadd(nsum, vcross(pa, pb));
+          pa = pb;
+        }
+        s_area = 0.5f * sqrtf(vsqn(nsum));
+      }
+      __syncthreads();
+      ok = s_area >= a.min_region_area;
+    }
+    if (ok && nreg >= a.rcap) {
+      err |= kErrRegionCap;
+      break;
+    }
+    if (ok) {
+      // discontinuity side output, ps/planar_region.h:360-417 (per boundary entry; the
+      // host turns the flags into the reference's set)
+      for (int k = tid; k < nb; k += BLOCK) {
+        const int idx = boundary[b_total + k];
+        const V3 pc = ld3(xyz, idx);
+        unsigned char flag = 0;
+        const float r2 = vsqn(pc);
+        const int x = idx / rows, y = idx % rows;
+        if (r2 > min_range_sq && r2 < max_range_sq && x > 0 && x < cols - 1 && y > 0 && y < rows - 1) {
+#pragma unroll
+          for (int d = 0; d < 4; ++d) {
+            const int ni = idx + kDx4[d] * rows + kDy4[d];
+            const V3 pn = ld3(xyz, ni);
+            if ((pc.z != pc.z) || (pn.z != pn.z)) continue;
+            if (labels[ni] != label_id) continue;
+            const V3 delta = qrotate(a.qx, a.qy, a.qz, a.qw, vsub(pc, pn));
+            const float cosang = vdot(ld3(nrm, idx), ld3(nrm, ni));
+            const float deg = (float)((double)cr_acosf(cosang) * (180.0 / 3.14159265358979323846));
+            if (fabsf(deg) < a.disc_angle && fabsf(delta.z) < a.disc_z_diff) continue;
+            if (fabsf(delta.z) / sqrtf(vsqn(delta)) < a.disc_z_ratio) continue;
+            flag = 1;
+          }
+        }
+        bflags[b_total + k] = flag;
+      }
+      if (tid == 0) {
+        PlanarMeta m;
+        m.inlier_begin = base; m.inlier_count = ninl;
+        m.boundary_begin = b_total; m.boundary_count = nb;
+        m.seed_index = seed; m.label_id = label_id;
+        for (int i = 0; i < 4; ++i) m.plane[i] = s_res.plane[i];
+        for (int i = 0; i < 3; ++i) m.centroid[i] = s_res.centroid[i];
+        m.area = s_area;
+        for (int i = 0; i < 10; ++i) m.est[i] = s_res.est[i];
+        meta[nreg] = m;
+      }
+      ++nreg;
+      inl_total += ninl;
+      b_total += nb;
+    } else {
+      // ps/segmentation.h:280-282
+      for (int i = tid; i < ninl; i += BLOCK) labels[inliers[base + i]] = kAlreadyExamedPoint;
+      any_failed = any_failed || (ninl > 0);
+    }
+    __syncthreads();
+    if (err & kErrBoundaryCap) break;
+  }
+  __syncthreads();
+  // ps/segmentation.h:287-291
+  if (any_failed) {
+    for (int i = tid; i < N; i += BLOCK)
+      if (labels[i] == kAlreadyExamedPoint) labels[i] = kUnlabeled;
+  }
+  if (tid == 0) {
+    a.stats[f].n_planar = nreg;
+    a.stats[f].planar_inliers = inl_total;
+    a.stats[f].boundary_len = b_total;
+    a.stats[f].error_flags |= err;
+    a.stats[f].grow_steps += steps;
+    a.stats[f].refits += refits;
+  }
+}
+
+}  // namespace pcseg
