@@ -8,6 +8,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cuda_runtime.h>
+#include "cr_trig.cuh"
 
 namespace pcseg {
 
@@ -124,9 +125,9 @@ __device__ __noinline__ void eig3_direct(const Sym3& mat, float evals[3], V3* ev
   float q = a_over_3 * a_over_3 * a_over_3 - half_b * half_b;
   q = (q < 0.0f) ? 0.0f : q;
   float rho = sqrtf(a_over_3);
-  float theta = cr_atan2f(sqrtf(q), half_b) * s_inv3;
+  float theta = cr_atan2f_pos(sqrtf(q), half_b) * s_inv3;  // sqrt(q) >= +0: atan2f in [0, pi]
   float cos_theta, sin_theta;
-  cr_sincosf(theta, &sin_theta, &cos_theta);
+  cr_sincosf_small(theta, &sin_theta, &cos_theta);
   evals[0] = c2_over_3 - rho * (cos_theta + s_sqrt3 * sin_theta);
   evals[1] = c2_over_3 - rho * (cos_theta - s_sqrt3 * sin_theta);
   evals[2] = c2_over_3 + 2.0f * rho * cos_theta;

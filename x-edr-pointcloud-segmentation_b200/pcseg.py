@@ -11,7 +11,7 @@ from types import SimpleNamespace
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpcseg_b200.so")
+LIB_PATH = os.environ.get("PCSEG_LIB", os.path.join(_HERE, "libpcseg_b200.so"))
 _LIB = None
 
 F32P = C.POINTER(C.c_float)
