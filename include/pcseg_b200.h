@@ -171,8 +171,8 @@ int pcseg_batch_frame_stats(pcseg_batch*, int* stats8_per_frame);
  * cluster growth}. */
 int pcseg_batch_stage_times(pcseg_batch*, float* ms4);
 /* Diagnostics (only in -DPCSEG_PROFILE builds, else PCSEG_ERR_UNSUPPORTED):
- * clock64 totals per growth phase, 8 per frame. */
-int pcseg_batch_profile(pcseg_batch*, long long* out8_per_frame);
+ * clock64 totals / event counts of the planar growth roles, 16 per frame. */
+int pcseg_batch_profile(pcseg_batch*, long long* out16_per_frame);
 /* Materialises one frame's regions (kind 0 = planar, 1 = cluster). */
 int pcseg_batch_regions(pcseg_batch*, int frame, int kind, pcseg_regions** out);
 /* Device pointers of the batch's resident results (labels int32[F*N],

@@ -43,7 +43,7 @@ struct PlanarArgs {
   PlanarMeta* meta;      // [F][rcap]
   int rcap;
   FrameStats* stats;     // [F]
-  long long* prof;       // nullable: [F][8] clock64 totals per phase (diagnostics)
+  long long* prof;       // nullable: [F][16] clock64 totals / counters (diagnostics)
   int ring;              // smem ring entries (power of two) for the shared-memory path
   int mask_words;        // ceil(N / 32)
 };
@@ -51,7 +51,9 @@ struct PlanarArgs {
 #ifdef PCSEG_PROFILE
 #define PROF_T(var) long long var = clock64()
 #define PROF_ACC(slot, t0, t1) prof_acc[slot] += (t1) - (t0)
+#define PROF_CNT(slot, n) prof_acc[slot] += (n)
 #else
+#define PROF_CNT(slot, n)
 #define PROF_T(var)
 #define PROF_ACC(slot, t0, t1)
 #endif
@@ -194,7 +196,7 @@ __device__ __forceinline__ void planar_grow_warp(const PlanarArgs& a, const floa
   }
 #ifdef PCSEG_PROFILE
   if (lane == 0 && a.prof)
-    for (int i = 0; i < 8; ++i) a.prof[(size_t)blockIdx.x * 8 + i] += prof_acc[i];
+    for (int i = 0; i < 8; ++i) a.prof[(size_t)blockIdx.x * 16 + i] += prof_acc[i];
 #endif
   // CheckAndFinalize first lines, :190-196
   if (ninl >= a.min_inliers && !est.up_to_date) est_compute(est);
@@ -212,7 +214,9 @@ __device__ __forceinline__ void planar_grow_warp(const PlanarArgs& a, const floa
 }
 
 // detail::FindInitialPredecessorDirection, ps/planar_region.cc:67-82
-__device__ __forceinline__ int initial_predecessor_dir(volatile int* labels, int rows, int cols,
+// Label reads here and in trace_boundary are plain (L1-cached) loads: the frame's
+// labels are written only by this CTA and every write is ordered by a barrier.
+__device__ __forceinline__ int initial_predecessor_dir(const int* labels, int rows, int cols,
                                                        int idx, int region_label) {
   const int x = idx / rows, y = idx % rows;
 #pragma unroll
@@ -231,7 +235,7 @@ struct TraceResult {
 
 // FindLabeledRegionBoundary (Moore trace), ps/planar_region.h:295-425, executed
 // by one thread.  Discontinuity flags are computed afterwards in parallel.
-__device__ void trace_boundary(volatile int* labels, int rows, int cols, int start_idx,
+__device__ void trace_boundary(const int* labels, int rows, int cols, int start_idx,
                                int region_label, int* boundary, int cap, TraceResult* out) {
   int curr_idx = start_idx;
   int cx = start_idx / rows, cy = start_idx % rows;

@@ -174,8 +174,8 @@ int batch_alloc(pcseg_batch* b) {
   CU_TRY(c, b->inv_list.ensure(F * (size_t)kInvCap * sizeof(int)));
   CU_TRY(c, b->inv_count.ensure(F * sizeof(int)));
 #ifdef PCSEG_PROFILE
-  CU_TRY(c, b->prof.ensure(F * 8 * sizeof(long long)));
-  CU_TRY(c, cudaMemset(b->prof.p, 0, F * 8 * sizeof(long long)));
+  CU_TRY(c, b->prof.ensure(F * 16 * sizeof(long long)));
+  CU_TRY(c, cudaMemset(b->prof.p, 0, F * 16 * sizeof(long long)));
 #endif
   int st = fill_int(c, b->claim.as<int>(), F * N, INT_MAX);
   if (st) return st;
@@ -244,7 +244,7 @@ int run_planar(pcseg_batch* b, const float* xyz_dev, const float* normals_dev, c
   a.ring = 2048;
   const size_t smem_fixed = 32 * 11 * sizeof(float) + kHashSize * sizeof(unsigned);
   size_t smem = (size_t)a.mask_words * 4 + (size_t)a.ring * 20 + smem_fixed;
-  const size_t smem_static = 9 * 1024;  // static shared memory of the kernel (reductions)
+  const size_t smem_static = 12 * 1024;  // static shared memory of the kernel (reductions)
   const size_t smem_max = 227 * 1024 - smem_static;
   bool use_smem = b->N < (1u << 24) && (size_t)a.mask_words * 4 + 256 * 20 + smem_fixed <= smem_max &&
                   !getenv("PCSEG_FORCE_GLOBAL_PATH");
@@ -869,12 +869,12 @@ int pcseg_batch_stage_times(pcseg_batch* b, float* ms4) {
   return PCSEG_OK;
 }
 
-int pcseg_batch_profile(pcseg_batch* b, long long* out8_per_frame) {
-  if (!b || !out8_per_frame) return PCSEG_ERR_NULL;
+int pcseg_batch_profile(pcseg_batch* b, long long* out16_per_frame) {
+  if (!b || !out16_per_frame) return PCSEG_ERR_NULL;
   pcseg_ctx* c = b->ctx;
   if (!b->prof.p) return PCSEG_ERR_UNSUPPORTED;
-  CU_TRY(c, cudaMemcpy(out8_per_frame, b->prof.p, (size_t)b->n_frames * 8 * sizeof(long long), cudaMemcpyDeviceToHost));
-  CU_TRY(c, cudaMemset(b->prof.p, 0, (size_t)b->n_frames * 8 * sizeof(long long)));
+  CU_TRY(c, cudaMemcpy(out16_per_frame, b->prof.p, (size_t)b->n_frames * 16 * sizeof(long long), cudaMemcpyDeviceToHost));
+  CU_TRY(c, cudaMemset(b->prof.p, 0, (size_t)b->n_frames * 16 * sizeof(long long)));
   return PCSEG_OK;
 }
 

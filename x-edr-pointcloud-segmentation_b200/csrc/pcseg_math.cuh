@@ -141,7 +141,7 @@ __device__ __noinline__ void eig3_direct(const Sym3& mat, float evals[3], V3* ev
     int k = 0, l = 2;
     if (d0 > d1) { k = 2; l = 0; d0 = d1; }
     Sym3 t = s;
-    float ek = evals[k];
+    float ek = (k == 0) ? evals[0] : evals[2];  // selects, not indexing: evals stays in registers
     t.m00 -= ek; t.m11 -= ek; t.m22 -= ek;
     V3 vk, vl;
     extract_kernel(t, &vk, &vl);
@@ -155,7 +155,7 @@ __device__ __noinline__ void eig3_direct(const Sym3& mat, float evals[3], V3* ev
         if (z > 0.0f) vl = vdiv(vl, sqrtf(z));
       } else {
         t = s;
-        float el = evals[l];
+        float el = (l == 0) ? evals[0] : evals[2];
         t.m00 -= el; t.m11 -= el; t.m22 -= el;
         V3 dummy;
         extract_kernel(t, &vl, &dummy);
@@ -206,28 +206,47 @@ __device__ __forceinline__ void est_add(Estimator& e, V3 p) {
   e.up_to_date = false;
 }
 
-// Caller guarantees e.w > 0 (the reference CHECK-aborts otherwise).
-__device__ __forceinline__ void est_compute(Estimator& e) {
-  e.up_to_date = true;
-  e.centroid = vdiv(e.csum, e.w);
-  float a0 = e.acc[0] / e.w, a1 = e.acc[1] / e.w, a2 = e.acc[2] / e.w;
-  float a3 = e.acc[3] / e.w, a4 = e.acc[4] / e.w, a5 = e.acc[5] / e.w;
+// ComputePlane split in two: est_raw is everything that depends only on the
+// sums (centroid, covariance, eigen-solve); est_apply is the part that also
+// depends on the PREVIOUS plane normal (eigenvector sign, invalid-plane
+// fallback).  The planar growth computes est_raw for several speculative
+// re-fits concurrently and applies them in order (grow_planar_pipe.cuh).
+struct RawFit {
+  V3 centroid;
+  V3 ev;          // eigenvector of the smallest eigenvalue
+  float smallest; // eigenvalues()[0]
+  float trace;
+  bool valid;     // eigenvalues()[1] > FLT_MIN
+};
+
+// Caller guarantees w > 0 (the reference CHECK-aborts otherwise).
+__device__ __forceinline__ RawFit est_raw(const float acc[6], V3 csum, float w) {
+  RawFit r;
+  r.centroid = vdiv(csum, w);
+  float a0 = acc[0] / w, a1 = acc[1] / w, a2 = acc[2] / w;
+  float a3 = acc[3] / w, a4 = acc[4] / w, a5 = acc[5] / w;
   Sym3 cov;
-  cov.m00 = a0 - e.centroid.x * e.centroid.x;
-  cov.m10 = a1 - e.centroid.x * e.centroid.y;
-  cov.m20 = a2 - e.centroid.x * e.centroid.z;
-  cov.m11 = a3 - e.centroid.y * e.centroid.y;
-  cov.m21 = a4 - e.centroid.y * e.centroid.z;
-  cov.m22 = a5 - e.centroid.z * e.centroid.z;
+  cov.m00 = a0 - r.centroid.x * r.centroid.x;
+  cov.m10 = a1 - r.centroid.x * r.centroid.y;
+  cov.m20 = a2 - r.centroid.x * r.centroid.z;
+  cov.m11 = a3 - r.centroid.y * r.centroid.y;
+  cov.m21 = a4 - r.centroid.y * r.centroid.z;
+  cov.m22 = a5 - r.centroid.z * r.centroid.z;
   float evals[3];
-  V3 ev;
-  eig3_direct(cov, evals, &ev);
-  if (evals[1] > FLT_MIN) {
-    float smallest = evals[0];
-    if (vdot(e.plane.n, ev) > 0.0f) e.plane = make_plane(ev, e.centroid);
-    else e.plane = make_plane(vneg(ev), e.centroid);
-    float trace = cov.m00 + (cov.m11 + cov.m22);
-    if (trace > smallest && smallest > FLT_MIN) e.curvature = fabsf(smallest / trace);
+  eig3_direct(cov, evals, &r.ev);
+  r.valid = evals[1] > FLT_MIN;
+  r.smallest = evals[0];
+  r.trace = cov.m00 + (cov.m11 + cov.m22);
+  return r;
+}
+
+__device__ __forceinline__ void est_apply(Estimator& e, const RawFit& r) {
+  e.up_to_date = true;
+  e.centroid = r.centroid;
+  if (r.valid) {
+    if (vdot(e.plane.n, r.ev) > 0.0f) e.plane = make_plane(r.ev, e.centroid);
+    else e.plane = make_plane(vneg(r.ev), e.centroid);
+    if (r.trace > r.smallest && r.smallest > FLT_MIN) e.curvature = fabsf(r.smallest / r.trace);
     else e.curvature = 0.0f;
     e.valid = true;
   } else {
@@ -235,6 +254,11 @@ __device__ __forceinline__ void est_compute(Estimator& e) {
     e.plane = make_plane(e.plane.n, e.centroid);
     e.valid = false;
   }
+}
+
+__device__ __forceinline__ void est_compute(Estimator& e) {
+  const RawFit r = est_raw(e.acc, e.csum, e.w);
+  est_apply(e, r);
 }
 
 // SetNormalOrientation, ps/plane_estimator.cc:113-126

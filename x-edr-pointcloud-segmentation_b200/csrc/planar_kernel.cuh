@@ -3,6 +3,7 @@
 #pragma once
 #include "grow_planar.cuh"
 #include "grow_planar_smem.cuh"
+#include "grow_planar_pipe.cuh"
 
 namespace pcseg {
 
@@ -37,11 +38,19 @@ __global__ void __launch_bounds__(BLOCK) planar_grow_kernel(PlanarArgs a) {
   __shared__ GrowResult s_res;
   __shared__ TraceResult s_trace;
   __shared__ float s_area;
+  __shared__ float s_cross[3 * BLOCK];
   __shared__ double s_ax[BLOCK], s_ay[BLOCK], s_bx[BLOCK], s_by[BLOCK];
 
   PlanarSmem sm;
   int tag_base = 0;
+  int refit_last = 0;  // warp R: newest ticket seen on its slot
+  __shared__ PipeCtl s_ctl;
+  static_assert(!SMEM || (BLOCK == 256 && kPipeDW == 4), "pipeline roles: warp 0 = A, 1 = B, 2/3/6/7 = re-fit");
   if constexpr (SMEM) {
+    if (tid == 0) {
+      s_ctl.ticket = 0;
+      for (int i = 0; i < kPipeDW; ++i) { s_ctl.req_ticket[i] = 0; s_ctl.res_ticket[i] = 0; s_ctl.req_expect[i] = 0; }
+    }
     sm.mask = reinterpret_cast<unsigned*>(dyn_smem);
     sm.q_tag = reinterpret_cast<int*>(sm.mask + a.mask_words);
     sm.q_cell = sm.q_tag + a.ring;
@@ -69,7 +78,11 @@ __global__ void __launch_bounds__(BLOCK) planar_grow_kernel(PlanarArgs a) {
   const float min_range_sq = a.disc_min_range * a.disc_min_range;  // eigenmath::Square
   const float max_range_sq = a.disc_max_range * a.disc_max_range;
 
+#ifdef PCSEG_PROFILE
+  long long kp_seed = 0, kp_fin = 0, kp_regions = 0, kp_tiny = 0;
+#endif
   while (true) {
+    PROF_T(k0);
     // ---- next usable seed (ps/segmentation.h:254-260).  A seed with a
     // non-finite point or normal fails its own plane test (NaN distance), adds
     // no inlier and leaves labels untouched: skipping it here is exact.
@@ -91,17 +104,36 @@ __global__ void __launch_bounds__(BLOCK) planar_grow_kernel(PlanarArgs a) {
       if (found < 0) seed_pos = max(seed_pos - 4 * BLOCK, 0);
     }
     if (found < 0) break;
+    PROF_T(k1);
+#ifdef PCSEG_PROFILE
+    kp_seed += k1 - k0;
+    ++kp_regions;
+#endif
     seed_pos = found;
     const int seed = seed_at(seeds, N, found);
     const int label_id = nreg + a.id_offset;
     const int base = inl_total;
 
-    if (tid < 32) {
-      if constexpr (SMEM)
-        planar_grow_warp_smem(a, xyz, nrm, a.labels + (size_t)f * N, a.queue + (size_t)f * a.qcap, inliers, seed,
-                              label_id, base, tag_base, sm, &s_res);
-      else
-        planar_grow_warp(a, xyz, nrm, labels, queue, claim, inliers, seed, label_id, base, &s_res);
+    if constexpr (SMEM) {
+      int* gqueue = a.queue + (size_t)f * a.qcap;
+      if (tid == 0) {
+        const V3 sp = ld3(xyz, seed);
+        sm.q_tag[0] = tag_base;
+        sm.q_cell[0] = seed;
+        sm.q_xyz[0] = sp.x; sm.q_xyz[1] = sp.y; sm.q_xyz[2] = sp.z;
+        gqueue[0] = seed;
+        s_ctl.tail_pub = 1;
+        s_ctl.b_done = 0;
+        s_ctl.a_verified = 0;
+        s_ctl.done = 0;
+      }
+      __syncthreads();
+      const int warp = tid >> 5;
+      if (warp == 0) pipe_warp_A(a, xyz, nrm, gqueue, seed, tag_base, sm, s_ctl, &s_res);
+      else if (warp == 1) pipe_warp_B(a, xyz, a.labels + (size_t)f * N, gqueue, inliers, label_id, base, tag_base, sm, s_ctl);
+      else if ((warp & 3) >= 2) pipe_warp_R(s_ctl, (warp & 1) + ((warp >> 2) << 1), refit_last);
+    } else {
+      if (tid < 32) planar_grow_warp(a, xyz, nrm, labels, queue, claim, inliers, seed, label_id, base, &s_res);
     }
     __syncthreads();
     const int ninl = s_res.ninl;
@@ -109,6 +141,7 @@ __global__ void __launch_bounds__(BLOCK) planar_grow_kernel(PlanarArgs a) {
     steps += s_res.steps;
     refits += s_res.refits;
 
+    PROF_T(k2);
     // ---- CheckAndFinalize, ps/planar_region.h:189-224
     bool ok = ninl >= a.min_inliers;
     int nb = 0;
@@ -118,14 +151,14 @@ __global__ void __launch_bounds__(BLOCK) planar_grow_kernel(PlanarArgs a) {
       for (int hi = ninl; hi > 0 && start_i < 0; hi -= BLOCK) {
         const int i = hi - 1 - tid;
         int q = -1;
-        if (i >= 0 && initial_predecessor_dir(labels, rows, cols, inliers[base + i], label_id) >= 0) q = i;
+        if (i >= 0 && initial_predecessor_dir(const_cast<const int*>(labels), rows, cols, inliers[base + i], label_id) >= 0) q = i;
         start_i = block_max<BLOCK>(q, s_warp);
       }
       if (start_i < 0) {
         ok = false;  // boundary_indices_ empty -> CheckMinRowsAndCols fails, :205-212
       } else {
         if (tid == 0)
-          trace_boundary(labels, rows, cols, inliers[base + start_i], label_id, boundary + b_total,
+          trace_boundary(const_cast<const int*>(labels), rows, cols, inliers[base + start_i], label_id, boundary + b_total,
                          a.bcap - b_total, &s_trace);
         __syncthreads();
         nb = s_trace.nb;
@@ -175,17 +208,29 @@ __global__ void __launch_bounds__(BLOCK) planar_grow_kernel(PlanarArgs a) {
       if (!off_line) ok = false;
     }
     if (ok) {
-      // PolygonArea: sequential sum of cross products, ps/algorithms.h:264-292
-      if (tid == 0) {
-        V3 nsum{0.0f, 0.0f, 0.0f};
+      // PolygonArea, ps/algorithms.h:264-292: the cross products p_i x p_(i+1) are
+      // computed by the whole CTA (batches of BLOCK, staged in shared memory so the
+      // scattered point loads overlap); their SUM stays sequential fp32 in polygon order.
+      {
         const int* b = boundary + b_total;
-        V3 pa = ld3(xyz, b[0]);
-        for (int i = 0; i < nb; ++i) {
-          V3 pb = ld3(xyz, b[(i + 1 == nb) ? 0 : i + 1]);
-          nsum = vadd(nsum, vcross(pa, pb));
-          pa = pb;
+        V3 nsum{0.0f, 0.0f, 0.0f};
+        for (int i0 = 0; i0 < nb; i0 += BLOCK) {
+          const int i = i0 + tid;
+          if (i < nb) {
+            const V3 pa = ld3(xyz, b[i]);
+            const V3 pb = ld3(xyz, b[(i + 1 == nb) ? 0 : i + 1]);
+            const V3 c = vcross(pa, pb);
+            s_cross[3 * tid] = c.x; s_cross[3 * tid + 1] = c.y; s_cross[3 * tid + 2] = c.z;
+          }
+          __syncthreads();
+          if (tid == 0) {
+            const int cnt = min(BLOCK, nb - i0);
+            for (int k = 0; k < cnt; ++k)
+              nsum = vadd(nsum, V3{s_cross[3 * k], s_cross[3 * k + 1], s_cross[3 * k + 2]});
+          }
+          __syncthreads();
         }
-        s_area = 0.5f * sqrtf(vsqn(nsum));
+        if (tid == 0) s_area = 0.5f * sqrtf(vsqn(nsum));
       }
       __syncthreads();
       ok = s_area >= a.min_region_area;
@@ -240,6 +285,9 @@ __global__ void __launch_bounds__(BLOCK) planar_grow_kernel(PlanarArgs a) {
       any_failed = any_failed || (ninl > 0);
     }
     __syncthreads();
+#ifdef PCSEG_PROFILE
+    { long long k3 = clock64(); kp_fin += k3 - k2; if (ninl < a.min_inliers) ++kp_tiny; }
+#endif
     if (err & kErrBoundaryCap) break;
   }
   __syncthreads();
@@ -248,6 +296,13 @@ __global__ void __launch_bounds__(BLOCK) planar_grow_kernel(PlanarArgs a) {
     for (int i = tid; i < N; i += BLOCK)
       if (labels[i] == kAlreadyExamedPoint) labels[i] = kUnlabeled;
   }
+#ifdef PCSEG_PROFILE
+  if (tid == 0 && a.prof) {
+    a.prof[(size_t)f * 16 + 13] += kp_seed;
+    a.prof[(size_t)f * 16 + 14] += kp_fin;
+    a.prof[(size_t)f * 16 + 15] += kp_regions * 1000000 + kp_tiny;
+  }
+#endif
   if (tid == 0) {
     a.stats[f].n_planar = nreg;
     a.stats[f].planar_inliers = inl_total;

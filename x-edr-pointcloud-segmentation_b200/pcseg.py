@@ -317,7 +317,7 @@ class Batch:
         return dict(zip(("normals", "seeds", "planar", "cluster"), [float(v) for v in out]))
 
     def profile(self):
-        out = np.zeros((self.n_frames, 8), np.int64)
+        out = np.zeros((self.n_frames, 16), np.int64)
         self.ctx._check(self.ctx.L.pcseg_batch_profile(self.h, _addr(out)))
         return out
 
