@@ -97,7 +97,7 @@ __global__ void __launch_bounds__(BLOCK) cluster_grow_kernel(ClusterArgs a) {
       int src = -1, cand = -1;
       bool acc = false;
       if (mine) {
-        const int qi = (head + tid) % a.qcap;
+        const int qi = (head + tid) & (a.qcap - 1);
         src = queue[2 * qi];
         cand = queue[2 * qi + 1];
         // (candidate - source).squaredNorm() < threshold, ps/cluster_region.h:94
@@ -157,7 +157,7 @@ __global__ void __launch_bounds__(BLOCK) cluster_grow_kernel(ClusterArgs a) {
         const int cell = s + (s >= (side * side) / 2 ? 1 : 0);
         const int dc = cell / side - h, dr = cell % side - h;
         const int n = (col + dc) * rows + (row + dr);
-        const int qi = (tail + off) % a.qcap;
+        const int qi = (tail + off) & (a.qcap - 1);
         queue[2 * qi] = cand;
         queue[2 * qi + 1] = n;
         labels[n] = kAlreadyInQueue;

@@ -103,7 +103,7 @@ __device__ __forceinline__ void planar_grow_warp(const PlanarArgs& a, const floa
     V3 p{0.f, 0.f, 0.f};
     bool acc = false;
     if (lane < m) {
-      cand = queue[(head + lane) % a.qcap];
+      cand = queue[(head + lane) & (a.qcap - 1)];
       p = ld3(xyz, cand);
       acc = plane_abs_distance(plane, p) < a.max_plane_distance;  // :168
     }
@@ -174,7 +174,7 @@ __device__ __forceinline__ void planar_grow_warp(const PlanarArgs& a, const floa
 #pragma unroll
     for (int s = 0; s < 4; ++s) {
       if (win[s]) {
-        queue[(tail + off) % a.qcap] = nb[s];
+        queue[(tail + off) & (a.qcap - 1)] = nb[s];
         labels[nb[s]] = kAlreadyInQueue;
         claim[nb[s]] = INT_MAX;
         ++off;

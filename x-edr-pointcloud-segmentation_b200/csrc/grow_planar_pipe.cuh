@@ -15,10 +15,11 @@
 //                the chunk; identical accept bits => identical sums, the chunk
 //                is VERIFIED (else A rolls back to it).  Only verified chunks
 //                are handed on, so nothing speculative ever reaches memory.
-//   warp 1  "B"  expands verified chunks in order: labels, inlier list,
-//                neighbour tests against the 1-bit mask, min-(lane,slot) claims,
-//                ordered enqueue with cp.async prefetch of the xyz into the ring.
-//   warps 2..    "R" each owns one re-fit slot: est_raw (centroid, covariance,
+//   warps 4-7 "B" expand verified chunks in order, one (entry, slot) pair per
+//                thread: labels, inlier list, neighbour tests against the 1-bit
+//                mask, min-key claims, ordered enqueue with cp.async prefetch of
+//                the xyz into the ring.
+//   6 warps  "R" each owns one re-fit slot: est_raw (centroid, covariance,
 //                eigen-solve) of posted sums.  The only part of ComputePlane
 //                that depends on the previous plane (eigenvector sign,
 //                ps/plane_estimator.cc:208-216) is applied by A in order.
@@ -31,7 +32,7 @@
 
 namespace pcseg {
 
-constexpr int kPipeDW = 4;    // re-fit warps / slots: warps 2, 3, 6, 7 (not on A's / B's scheduler)
+constexpr int kPipeDW = 6;    // re-fit warps / slots: warps 1, 2, 3, 9, 10, 11 of the 12-warp CTA
 constexpr int kPipeNC = 16;   // chunk records in flight
 constexpr int kPipeHash = kHashSize;
 
@@ -74,7 +75,7 @@ __device__ __forceinline__ void pipe_read_entry(const PipeSmem& sm, const int* g
     const volatile float* q = sm.q_xyz + 3 * slot;
     *p = V3{q[0], q[1], q[2]};
   } else {
-    const int c = *(volatile const int*)(gqueue + pos % qcap);
+    const int c = *(volatile const int*)(gqueue + (pos & (qcap - 1)));
     *cell = c;
     *p = ld3(xyz, c);
   }
@@ -342,155 +343,183 @@ __device__ __forceinline__ void pipe_warp_R(PipeCtl& ctl, int s, int& last) {
 }
 
 // ---------------------------------------------------------------------------
-// Warp B: expansion of verified chunks (labels, inliers, AddNeighbors).
+// Group B (4 warps, 128 threads): expansion of verified chunks -- labels,
+// inlier list, AddNeighbors.  Thread t handles ONE (entry, slot) pair of the
+// chunk, e = t >> 2, s = t & 3, so t itself is the (lane, slot) order key of
+// grow_common.cuh: a neighbour cell is enqueued by its smallest claiming t and
+// the winners are appended in t order.  The four warps meet at named barrier 1.
 // ---------------------------------------------------------------------------
-__device__ __forceinline__ void pipe_warp_B(const PlanarArgs& a, const float* __restrict__ xyz, int* labels,
-                                            int* gqueue, int* inliers, int label_id, int base, int tag_base,
-                                            const PipeSmem& sm, PipeCtl& ctl) {
+constexpr int kPipeBThreads = 128;
+
+__device__ __forceinline__ void pipe_bar_B() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+struct PipeBShared {
+  volatile int cmd;
+  volatile unsigned wb[4];     // per-warp winner ballots
+  volatile int unres[4];       // per-warp "some claim still probing"
+  volatile int cand[32];       // chunk cells (rejection rule)
+};
+
+__device__ __forceinline__ void pipe_group_B(const PlanarArgs& a, const float* __restrict__ xyz, int* labels,
+                                             int* gqueue, int* inliers, int label_id, int base, int tag_base,
+                                             const PipeSmem& sm, PipeCtl& ctl, PipeBShared& bs, int t) {
   const unsigned FULL = 0xffffffffu;
-  const int lane = threadIdx.x & 31;
+  const int lane = t & 31, bw = t >> 5;
+  const int e = t >> 2, s = t & 3;
   const int rows = a.rows, cols = a.cols;
   const int R = sm.ring;
   const FastDiv fdrows = make_fastdiv(rows);
-  int k = 0, tail = 1, ninl = 0;
+  int k = 0, pub_k = 0, tail = 1, ninl = 0;
 #ifdef PCSEG_PROFILE
   long long prof_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 #endif
   while (true) {
     PROF_T(t0);
-    if (ctl.a_verified <= k) {
-      if (ctl.done) break;
-      PROF_T(tw);
-      PROF_ACC(3, t0, tw);
+    if (t == 0) {
+      int cmd;
+      while (true) {
+        if (ctl.a_verified > k) { cmd = 1; break; }
+        if (pub_k < k) { cmd = 2; break; }  // idle with unpublished enqueues: flush
+        if (ctl.done) { cmd = 0; break; }
+      }
+      __threadfence_block();
+      bs.cmd = cmd;
+    }
+    pipe_bar_B();
+    const int cmd = bs.cmd;
+    if (cmd == 0) break;
+    if (cmd == 2) {
+      cp_async_wait<0>();
+      pipe_bar_B();
+      if (t == 0) {
+        __threadfence_block();
+        ctl.tail_pub = tail;
+        __threadfence_block();
+        ctl.b_done = k;
+      }
+      pub_k = k;
       continue;
     }
-    __threadfence_block();
     PROF_T(t1);
     const int r = k % kPipeNC;
     const int head = ctl.cr_head[r];
     const int processed = ctl.cr_proc[r];
     const unsigned amask = ctl.cr_amask[r];
-    const bool mine = lane < processed;
-    const bool acc = (amask >> lane) & 1u;
-    const unsigned rejmask = __ballot_sync(FULL, mine && !acc);
+    const unsigned pmask = processed >= 32 ? FULL : ((1u << processed) - 1u);
+    const unsigned rejmask = ~amask & pmask;
+    const bool mine = e < processed;
+    const bool acc = (amask >> e) & 1u;
     int cand = -1;
     if (mine) {
-      const int pos = head + lane;
+      const int pos = head + e;
       const int slot = pos & (R - 1);
       if (((volatile int*)sm.q_tag)[slot] == tag_base + pos) cand = ((volatile int*)sm.q_cell)[slot];
-      else cand = *(volatile int*)(gqueue + pos % a.qcap);
+      else cand = *(volatile int*)(gqueue + (pos & (a.qcap - 1)));
     }
-    const int rank = __popc(amask & ((1u << lane) - 1u));
-    // AddNeighbors, ps/planar_region.h:229-255: (c-1,r), (c,r-1), (c,r+1), (c+1,r)
-    int nb[4] = {-1, -1, -1, -1};
-    bool el[4] = {false, false, false, false};
+    // AddNeighbors, ps/planar_region.h:229-255: slot 0 (c-1,r), 1 (c,r-1), 2 (c,r+1), 3 (c+1,r)
+    int nb = -1;
     if (acc) {
-      labels[cand] = label_id;             // :177
-      inliers[base + ninl + rank] = cand;  // :169
-      // only the seed can still have its bit set when it is accepted
-      if (k == 0) atomicAnd(&sm.mask[cand >> 5], ~(1u << (cand & 31)));
       int row, col;
       fast_divmod(fdrows, cand, &col, &row);
-      if (col > 0) nb[0] = cand - rows;
-      if (row > 0) nb[1] = cand - 1;
-      if (row < rows - 1) nb[2] = cand + 1;
-      if (col < cols - 1) nb[3] = cand + rows;
+      if (s == 0) { if (col > 0) nb = cand - rows; }
+      else if (s == 1) { if (row > 0) nb = cand - 1; }
+      else if (s == 2) { if (row < rows - 1) nb = cand + 1; }
+      else { if (col < cols - 1) nb = cand + rows; }
+      if (s == 0) {
+        labels[cand] = label_id;                                                  // :177
+        inliers[base + ninl + __popc(amask & ((1u << e) - 1u))] = cand;           // :169
+        // only the seed can still have its bit set when it is accepted
+        if (k == 0) atomicAnd(&sm.mask[cand >> 5], ~(1u << (cand & 31)));
+      }
     }
-    __syncwarp();
-    if (acc) {
-#pragma unroll
-      for (int s = 0; s < 4; ++s) el[s] = nb[s] >= 0 && mask_test(sm.mask, nb[s]);
-    }
-    // a cell rejected at lane q is kUnlabeled again for every later lane (:181)
-    for (unsigned rm = rejmask; rm; rm &= rm - 1) {
-      const int q = __ffs(rm) - 1;
-      const int cq = __shfl_sync(FULL, cand, q);
-      if (acc && lane > q) {
-#pragma unroll
-        for (int s = 0; s < 4; ++s) el[s] = el[s] || (nb[s] == cq);
+    bool el = nb >= 0 && mask_test(sm.mask, nb);
+    // a cell rejected at entry q is kUnlabeled again for every later entry (:181)
+    if (rejmask) {
+      if (s == 0 && mine) bs.cand[e] = cand;
+      pipe_bar_B();
+      if (nb >= 0) {
+        for (unsigned rm = rejmask & ((1u << e) - 1u); rm; rm &= rm - 1)
+          el = el || (nb == bs.cand[__ffs(rm) - 1]);
       }
     }
     PROF_T(t2);
-    // smallest (lane, slot) key per neighbour cell wins the enqueue
-    bool win[4] = {false, false, false, false};
-    int probe[4];
-#pragma unroll
-    for (int s = 0; s < 4; ++s) probe[s] = (int)(((unsigned)nb[s] * 2654435761u) >> 21) & (kPipeHash - 1);
-    bool unres[4] = {el[0], el[1], el[2], el[3]};
-    while (__any_sync(FULL, unres[0] || unres[1] || unres[2] || unres[3])) {
-#pragma unroll
-      for (int s = 0; s < 4; ++s)
-        if (unres[s]) atomicMin(&sm.htab[probe[s]], ((unsigned)nb[s] << 7) | (unsigned)(lane * 4 + s));
-      __syncwarp();
-#pragma unroll
-      for (int s = 0; s < 4; ++s) {
-        if (unres[s]) {
-          const unsigned v = ((volatile unsigned*)sm.htab)[probe[s]];
-          if ((int)(v >> 7) == nb[s]) {
-            win[s] = (v & 127u) == (unsigned)(lane * 4 + s);
-            unres[s] = false;
-          } else {
-            probe[s] = (probe[s] + 1) & (kPipeHash - 1);
-          }
+    // smallest key t per neighbour cell wins the enqueue
+    bool win = false, unres = el, first = true;
+    int probe = (int)(((unsigned)nb * 2654435761u) >> 21) & (kPipeHash - 1);
+    while (true) {
+      if (unres) atomicMin(&sm.htab[probe], ((unsigned)nb << 7) | (unsigned)t);
+      pipe_bar_B();
+      // every mask test of this chunk is done: rejected cells become unlabeled again
+      // (ordered before the winners clear their bits, after the next barrier)
+      if (first && mine && !acc && s == 0) atomicOr(&sm.mask[cand >> 5], 1u << (cand & 31));
+      first = false;
+      if (unres) {
+        const unsigned v = ((volatile unsigned*)sm.htab)[probe];
+        if ((int)(v >> 7) == nb) {
+          win = (v & 127u) == (unsigned)t;
+          unres = false;
+        } else {
+          probe = (probe + 1) & (kPipeHash - 1);
         }
       }
-      __syncwarp();
+      const unsigned wbal = __ballot_sync(FULL, win);
+      const unsigned ubal = __ballot_sync(FULL, unres);
+      if (lane == 0) {
+        bs.wb[bw] = wbal;
+        bs.unres[bw] = ubal != 0u;
+      }
+      pipe_bar_B();
+      if (!(bs.unres[0] | bs.unres[1] | bs.unres[2] | bs.unres[3])) break;
+      pipe_bar_B();  // everyone has read the flags before they are rewritten
     }
     PROF_T(t3);
-    if (mine && !acc) atomicOr(&sm.mask[cand >> 5], 1u << (cand & 31));
-    __syncwarp();
-    const unsigned b0 = __ballot_sync(FULL, win[0]), b1 = __ballot_sync(FULL, win[1]);
-    const unsigned b2 = __ballot_sync(FULL, win[2]), b3 = __ballot_sync(FULL, win[3]);
-    const unsigned lt = (1u << lane) - 1u;
-    int off = __popc(b0 & lt) + __popc(b1 & lt) + __popc(b2 & lt) + __popc(b3 & lt);
+    const unsigned w0 = bs.wb[0], w1 = bs.wb[1], w2 = bs.wb[2], w3 = bs.wb[3];
+    const int c0 = __popc(w0), c1 = __popc(w1), c2 = __popc(w2), c3 = __popc(w3);
+    const unsigned myb = bw == 0 ? w0 : (bw == 1 ? w1 : (bw == 2 ? w2 : w3));
+    const int off = (bw > 0 ? c0 : 0) + (bw > 1 ? c1 : 0) + (bw > 2 ? c2 : 0) + __popc(myb & ((1u << lane) - 1u));
     const int new_head = head + processed;
-#pragma unroll
-    for (int s = 0; s < 4; ++s) {
-      if (win[s]) {
-        const int n = nb[s];
-        sm.htab[probe[s]] = kHashEmpty;
-        atomicAnd(&sm.mask[n >> 5], ~(1u << (n & 31)));  // kAlreadyInUnexaminedPointsQueue
-        const int qp = tail + off;
-        gqueue[qp % a.qcap] = n;
-        if (qp - new_head < R) {
-          const int sl = qp & (R - 1);
-          sm.q_tag[sl] = tag_base + qp;
-          sm.q_cell[sl] = n;
-          const float* src = xyz + 3 * (size_t)n;
-          cp_async4(sm.q_xyz + 3 * sl, src);
-          cp_async4(sm.q_xyz + 3 * sl + 1, src + 1);
-          cp_async4(sm.q_xyz + 3 * sl + 2, src + 2);
-        }
-        ++off;
+    if (win) {
+      sm.htab[probe] = kHashEmpty;
+      atomicAnd(&sm.mask[nb >> 5], ~(1u << (nb & 31)));  // kAlreadyInUnexaminedPointsQueue
+      const int qp = tail + off;
+      gqueue[qp & (a.qcap - 1)] = nb;
+      if (qp - new_head < R) {
+        const int sl = qp & (R - 1);
+        sm.q_tag[sl] = tag_base + qp;
+        sm.q_cell[sl] = nb;
+        const float* src = xyz + 3 * (size_t)nb;
+        cp_async4(sm.q_xyz + 3 * sl, src);
+        cp_async4(sm.q_xyz + 3 * sl + 1, src + 1);
+        cp_async4(sm.q_xyz + 3 * sl + 2, src + 2);
       }
     }
     cp_async_commit();
     const int tail_prev = tail;
-    tail += __popc(b0) + __popc(b1) + __popc(b2) + __popc(b3);
+    tail += c0 + c1 + c2 + c3;
     ninl += __popc(amask);
     ++k;
-    // publish: everything when A has nothing else to do, else lag one chunk
-    // behind so that the xyz copies stay off the critical path
-    const bool flush = ctl.a_verified == k;
-    if (flush) cp_async_wait<0>();
-    else cp_async_wait<1>();
-    __syncwarp();
-    if (lane == 0) {
+    // publish one chunk behind, so that the xyz copies stay off the critical path
+    cp_async_wait<1>();
+    pipe_bar_B();
+    if (t == 0) {
       __threadfence_block();
-      ctl.tail_pub = flush ? tail : tail_prev;
+      ctl.tail_pub = tail_prev;
       __threadfence_block();
-      ctl.b_done = k;
+      ctl.b_done = k - 1;
     }
+    pub_k = k - 1;
     PROF_T(t4);
     PROF_ACC(0, t1, t2);
     PROF_ACC(1, t2, t3);
     PROF_ACC(2, t3, t4);
+    PROF_ACC(3, t0, t1);
     PROF_CNT(4, 1);
   }
   cp_async_wait<0>();
 #ifdef PCSEG_PROFILE
-  if (lane == 0 && a.prof)
+  if (t == 0 && a.prof)
     for (int i = 0; i < 8; ++i) a.prof[(size_t)blockIdx.x * 16 + 8 + i] += prof_acc[i];
 #endif
 }
+
 }  // namespace pcseg

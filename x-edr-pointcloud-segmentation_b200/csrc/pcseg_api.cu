@@ -24,6 +24,7 @@ using namespace pcseg;
 namespace {
 
 constexpr int kGrowBlock = 256;
+constexpr int kPipeBlock = 384;  // planar fast path: 12 warps (grow_planar_pipe.cuh)
 constexpr int kInvCap = 4096;
 
 struct DevBuf {
@@ -158,7 +159,8 @@ int check_cluster_cfg(const pcseg_cluster_config* cfg) {
 int batch_alloc(pcseg_batch* b) {
   pcseg_ctx* c = b->ctx;
   const size_t F = b->n_frames, N = b->N;
-  b->qcap = (int)N + 1024;
+  b->qcap = 1024;  // power of two >= N + 1024: queue positions wrap with a mask
+  while ((size_t)b->qcap < N + 1024) b->qcap <<= 1;
   b->bcap = (int)(2 * N) + 1024;
   b->rcap_planar = (int)std::min<size_t>(N / 4 + 16, 4096);
   b->rcap_cluster = (int)N + 1;
@@ -244,14 +246,20 @@ int run_planar(pcseg_batch* b, const float* xyz_dev, const float* normals_dev, c
   a.ring = 2048;
   const size_t smem_fixed = 32 * 11 * sizeof(float) + kHashSize * sizeof(unsigned);
   size_t smem = (size_t)a.mask_words * 4 + (size_t)a.ring * 20 + smem_fixed;
-  const size_t smem_static = 12 * 1024;  // static shared memory of the kernel (reductions)
+  cudaFuncAttributes fattr;
+  CU_TRY(c, cudaFuncGetAttributes(&fattr, planar_grow_kernel<kPipeBlock, true>));
+  const size_t smem_static = fattr.sharedSizeBytes;
+  // two frames per SM when they fit (228 KB per SM, 1 KB reserved per CTA), else one
+  const size_t smem_two = (228 * 1024) / 2 - 1024 - smem_static;
   const size_t smem_max = 227 * 1024 - smem_static;
   bool use_smem = b->N < (1u << 24) && (size_t)a.mask_words * 4 + 256 * 20 + smem_fixed <= smem_max &&
                   !getenv("PCSEG_FORCE_GLOBAL_PATH");
   if (use_smem) {
+    if (smem > smem_two && (size_t)a.mask_words * 4 + 1024 * 20 + smem_fixed <= smem_two) a.ring = 1024;
+    smem = (size_t)a.mask_words * 4 + (size_t)a.ring * 20 + smem_fixed;
     while (smem > smem_max) { a.ring /= 2; smem = (size_t)a.mask_words * 4 + (size_t)a.ring * 20 + smem_fixed; }
-    CU_TRY(c, cudaFuncSetAttribute(planar_grow_kernel<kGrowBlock, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    planar_grow_kernel<kGrowBlock, true><<<b->n_frames, kGrowBlock, smem, c->stream>>>(a);
+    CU_TRY(c, cudaFuncSetAttribute(planar_grow_kernel<kPipeBlock, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    planar_grow_kernel<kPipeBlock, true><<<b->n_frames, kPipeBlock, smem, c->stream>>>(a);
   } else {
     planar_grow_kernel<kGrowBlock, false><<<b->n_frames, kGrowBlock, 0, c->stream>>>(a);
   }
@@ -681,7 +689,13 @@ int run_seed_finder(pcseg_batch* b, const float* xyz_dev, const float* nrm_dev, 
   // counts are laid out [F][N] inside the queue buffer
   dim3 grid((unsigned)((N + 255) / 256), (unsigned)F);
   seed_support_count_kernel<<<grid, 256, 0, c->stream>>>(a);
-  seed_order_kernel<<<(unsigned)F, 32, 0, c->stream>>>(a);
+  {
+    const int nkeys = nbhd * nbhd + 1;
+    const size_t smem = (size_t)kSeedWarps * nkeys * sizeof(int);
+    if (smem > 48 * 1024)
+      CU_TRY(c, cudaFuncSetAttribute(seed_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    seed_order_kernel<<<(unsigned)F, 32 * kSeedWarps, smem, c->stream>>>(a, nkeys);
+  }
   c->launches += 2;
   CU_TRY(c, cudaGetLastError());
   return PCSEG_OK;

@@ -55,42 +55,76 @@ __global__ void __launch_bounds__(256) seed_support_count_kernel(SeedArgs a) {
   a.counts[(size_t)f * N + t] = result;
 }
 
-// One warp per frame: stable counting sort of (count, index) by count.
-__global__ void __launch_bounds__(32) seed_order_kernel(SeedArgs a) {
+// One CTA of kSeedWarps warps per frame: stable counting sort of (count, index)
+// by count.  Warp w owns the contiguous cell segment [w*seg, (w+1)*seg); the
+// per-(warp, key) histogram scanned key-major / warp-minor gives every warp the
+// start of its run inside each key's block, so the output order is "ascending
+// key, ascending cell index within a key" (= std::multimap insertion order).
+// Dynamic shared memory: kSeedWarps * nkeys ints, nkeys = nbhd*nbhd + 1.
+constexpr int kSeedWarps = 32;
+
+__global__ void __launch_bounds__(32 * kSeedWarps) seed_order_kernel(SeedArgs a, int nkeys) {
+  extern __shared__ int s_hist[];  // [kSeedWarps][nkeys]
+  __shared__ int s_keybase[kSeedMaxKeys];
   const unsigned FULL = 0xffffffffu;
-  const int f = blockIdx.x, lane = threadIdx.x;
+  const int f = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int N = a.rows * a.cols;
   const int* counts = a.counts + (size_t)f * N;
   int* out = a.seeds + (size_t)f * a.stride;
-  __shared__ int s_run[kSeedMaxKeys];
-  for (int k = lane; k < kSeedMaxKeys; k += 32) s_run[k] = 0;
-  __syncwarp();
-  for (int i = lane; i < N; i += 32) {
+  const int seg = ((N + kSeedWarps - 1) / kSeedWarps + 31) & ~31;
+  const int c0 = min(warp * seg, N), c1 = min(c0 + seg, N);
+  int* hist = s_hist + warp * nkeys;
+  for (int k = threadIdx.x; k < kSeedWarps * nkeys; k += blockDim.x) s_hist[k] = 0;
+  __syncthreads();
+  for (int i = c0 + lane; i < c1; i += 32) {
     const int key = counts[i];
-    if (key >= 0) atomicAdd(&s_run[key], 1);
+    if (key >= 0) atomicAdd(&hist[key], 1);
   }
-  __syncwarp();
-  if (lane == 0) {
-    int acc = 0;
-    for (int k = 0; k < kSeedMaxKeys; ++k) {
-      const int c = s_run[k];
-      s_run[k] = acc;
-      acc += c;
+  __syncthreads();
+  // per-key totals, exclusive scan over keys by warp 0, then warp-minor offsets
+  for (int k = threadIdx.x; k < nkeys; k += blockDim.x) {
+    int t = 0;
+    for (int w = 0; w < kSeedWarps; ++w) t += s_hist[w * nkeys + k];
+    s_keybase[k] = t;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    int carry = 0;
+    for (int k0 = 0; k0 < nkeys; k0 += 32) {
+      const int k = k0 + lane;
+      const int v = (k < nkeys) ? s_keybase[k] : 0;
+      int x = v;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(FULL, x, o);
+        if (lane >= o) x += y;
+      }
+      if (k < nkeys) s_keybase[k] = carry + x - v;
+      carry += __shfl_sync(FULL, x, 31);
     }
-    a.n_seeds[f] = acc;
+    if (lane == 0) a.n_seeds[f] = carry;
   }
-  __syncwarp();
-  for (int i0 = 0; i0 < N; i0 += 32) {
+  __syncthreads();
+  for (int k = threadIdx.x; k < nkeys; k += blockDim.x) {
+    int run = s_keybase[k];
+    for (int w = 0; w < kSeedWarps; ++w) {
+      const int c = s_hist[w * nkeys + k];
+      s_hist[w * nkeys + k] = run;
+      run += c;
+    }
+  }
+  __syncthreads();
+  for (int i0 = c0; i0 < c1; i0 += 32) {
     const int i = i0 + lane;
-    const int key = (i < N) ? counts[i] : -1;
+    const int key = (i < c1) ? counts[i] : -1;
     const unsigned peers = __match_any_sync(FULL, key);
     if (key >= 0) {
       const int leader = __ffs(peers) - 1;
       const int rank = __popc(peers & ((1u << lane) - 1u));
       int basepos = 0;
       if (lane == leader) {
-        basepos = s_run[key];
-        s_run[key] = basepos + __popc(peers);
+        basepos = hist[key];
+        hist[key] = basepos + __popc(peers);
       }
       basepos = __shfl_sync(peers, basepos, leader);
       out[basepos + rank] = i;  // seed index = col * Rows + row = linear cell index
