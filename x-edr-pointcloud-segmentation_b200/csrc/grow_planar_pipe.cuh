@@ -8,18 +8,21 @@
 // by value speculation and spread over the warps of the frame's CTA:
 //
 //   warp 0  "A"  walks the queue in chunks of <= 32 entries cut at the inlier
-//                that triggers a re-fit, evaluates each chunk with the NEWEST
-//                FINAL plane it has (possibly several re-fits stale), adds the
-//                moments in FIFO order and posts the sums of every re-fit.
-//                When the true plane of a chunk becomes final it re-evaluates
-//                the chunk; identical accept bits => identical sums, the chunk
-//                is VERIFIED (else A rolls back to it).  Only verified chunks
-//                are handed on, so nothing speculative ever reaches memory.
+//                that triggers a re-fit and evaluates each chunk with the NEWEST
+//                FINAL plane it has (possibly several re-fits stale).  When the
+//                true plane of a chunk becomes final, A proves that no accept
+//                bit can differ (plane change x point magnitude < the chunk's
+//                distance margin, fp32 error included) or else re-evaluates the
+//                chunk; identical accept bits => identical chunk, the chunk is
+//                VERIFIED (else A rolls back to it).  Only verified chunks are
+//                expanded, so nothing speculative ever reaches memory.
+//   warp 1  "S"  adds the moments of the chunks' inliers in FIFO order
+//                (sequential fp32) and posts the sums of every re-fit.
 //   warps 4-7 "B" expand verified chunks in order, one (entry, slot) pair per
 //                thread: labels, inlier list, neighbour tests against the 1-bit
 //                mask, min-key claims, ordered enqueue with cp.async prefetch of
 //                the xyz into the ring.
-//   6 warps  "R" each owns one re-fit slot: est_raw (centroid, covariance,
+//   5 warps  "R" each owns one re-fit slot: est_raw (centroid, covariance,
 //                eigen-solve) of posted sums.  The only part of ComputePlane
 //                that depends on the previous plane (eigenvector sign,
 //                ps/plane_estimator.cc:208-216) is applied by A in order.
@@ -32,25 +35,38 @@
 
 namespace pcseg {
 
-constexpr int kPipeDW = 6;    // re-fit warps / slots: warps 1, 2, 3, 9, 10, 11 of the 12-warp CTA
+constexpr int kPipeDW = 5;    // re-fit warps / slots: warps 2, 3, 9, 10, 11 of the 12-warp CTA
 constexpr int kPipeNC = 16;   // chunk records in flight
+constexpr int kPipePH = 8;    // plane history (> kPipeDW)
 constexpr int kPipeHash = kHashSize;
 
 struct PipeCtl {
   // B -> A
   volatile int tail_pub;    // queue entries [0, tail_pub) are complete (cell, xyz)
-  volatile int b_done;      // chunks fully expanded
-  // A -> B
-  volatile int a_verified;  // chunks [0, a_verified) are final
+  volatile int b_done;      // chunks whose enqueues are all inside tail_pub
+  // S -> A
+  volatile int s_done;      // chunks accumulated
+  volatile int s_ack;       // roll-back epoch acknowledged
+  volatile float cur_s[10]; // sums after chunk s_done - 1
+  // A -> B, S
+  volatile int a_verified;  // chunks [0, a_verified) are final             (B)
+  volatile int a_spec;      // chunk records [0, a_spec) are written         (S)
+  volatile int rb_epoch;    // bumped by A on a roll-back to chunk rb_chunk  (S)
+  volatile int rb_chunk;
   volatile int done;        // region finished: all role loops exit
-  // chunk records (written by A before a_verified passes them)
+  // chunk records (written by A before a_spec passes them)
   volatile int cr_head[kPipeNC];
   volatile int cr_proc[kPipeNC];
   volatile unsigned cr_amask[kPipeNC];
+  volatile int cr_post[kPipeNC];   // 0, or the ticket of the re-fit this chunk ends with
+  volatile int cr_slot[kPipeNC];
   // A-private per chunk
   int cr_m[kPipeNC];
   unsigned cr_all[kPipeNC];
-  int cr_vreq[kPipeNC], cr_used[kPipeNC], cr_inper[kPipeNC], cr_ninl[kPipeNC], cr_refit[kPipeNC];
+  int cr_vreq[kPipeNC], cr_used[kPipeNC], cr_inper[kPipeNC], cr_ninl[kPipeNC];
+  float cr_margin[kPipeNC], cr_pmax[kPipeNC];
+  float ph[kPipePH][4];            // plane of version v at v % kPipePH
+  // S-private per chunk: sums before the chunk
   float cr_snap[kPipeNC][10];
   // re-fit slots
   volatile float req_s[kPipeDW][10];
@@ -58,7 +74,7 @@ struct PipeCtl {
   volatile float res_v[kPipeDW][8];  // centroid xyz, ev xyz, smallest, trace
   volatile int res_valid[kPipeDW];
   volatile int res_ticket[kPipeDW];
-  int req_chunk[kPipeDW];    // A-private: chunk whose end posted the request
+  int req_chunk[kPipeDW];    // A-private: chunk whose end posts the request
   int req_expect[kPipeDW];   // A-private: ticket A waits for
   int ticket;                // persists across regions
 };
@@ -83,8 +99,8 @@ __device__ __forceinline__ void pipe_read_entry(const PipeSmem& sm, const int* g
 
 
 // ---------------------------------------------------------------------------
-// Warp A: speculative evaluation, ordered moment sums, verification, plane
-// finalisation, termination.
+// Warp A: speculative evaluation, verification, plane finalisation,
+// termination.
 // ---------------------------------------------------------------------------
 __device__ __forceinline__ void pipe_warp_A(const PlanarArgs& a, const float* __restrict__ xyz,
                                             const float* __restrict__ nrm, const int* gqueue, int seed,
@@ -100,21 +116,26 @@ __device__ __forceinline__ void pipe_warp_A(const PlanarArgs& a, const float* __
   Plane plane = make_plane(seed_normal, seed_point);
   V3 prev_n = seed_normal;          // normal of plane_estimator_'s plane_ (sign reference)
   V3 centroid{0.0f, 0.0f, 0.0f};
-  float accj = 0.0f;                // lane j < 10 owns accumulator j: acc[0..5], csum xyz, weight
   int head = 0, ninl = 0, inper = 0;
   int c_spec = 0, c_ver = 0, n_posted = 0, n_final = 0;
-  int tail_seen = 1, b_done_seen = 0;
+  int slot_post = 0, slot_fin = 0;  // n_posted % kPipeDW, n_final % kPipeDW
+  int tail_seen = 1, b_done_seen = 0, s_done_seen = 0;
   int ticket = ctl.ticket;
+  int epoch = 0;
   int refits = 0, steps = 0;
+  if (lane == 0) {
+    ctl.ph[0][0] = plane.n.x; ctl.ph[0][1] = plane.n.y; ctl.ph[0][2] = plane.n.z; ctl.ph[0][3] = plane.d;
+  }
+  __syncwarp();
 #ifdef PCSEG_PROFILE
   long long prof_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 #endif
   while (true) {
     bool progressed = false;
     PROF_T(t0);
-    // (1) apply the next re-fit once the chunk that posted it is verified
+    // (1) apply the next re-fit once the chunk that posts it is verified
     if (n_final < n_posted) {
-      const int s = n_final % kPipeDW;
+      const int s = slot_fin;
       if (ctl.req_chunk[s] < c_ver && ctl.res_ticket[s] == ctl.req_expect[s]) {
         __threadfence_block();
         centroid = V3{ctl.res_v[s][0], ctl.res_v[s][1], ctl.res_v[s][2]};
@@ -124,7 +145,13 @@ __device__ __forceinline__ void pipe_warp_A(const PlanarArgs& a, const float* __
         plane = make_plane(n, centroid);
         prev_n = n;
         ++n_final;
+        slot_fin = (slot_fin + 1 == kPipeDW) ? 0 : slot_fin + 1;
         ++refits;
+        if (lane == 0) {
+          float* h = ctl.ph[n_final % kPipePH];
+          h[0] = plane.n.x; h[1] = plane.n.y; h[2] = plane.n.z; h[3] = plane.d;
+        }
+        __syncwarp();
         progressed = true;
       }
     }
@@ -134,17 +161,35 @@ __device__ __forceinline__ void pipe_warp_A(const PlanarArgs& a, const float* __
       const int r = c_ver % kPipeNC;
       if (ctl.cr_vreq[r] == n_final) {
         bool ok = true;
-        if (ctl.cr_used[r] != n_final) {
-          const int m = ctl.cr_m[r];
-          bool acc = false;
-          if (lane < m) {
-            int cand;
-            V3 p;
-            pipe_read_entry(sm, gqueue, a.qcap, xyz, tag_base, ctl.cr_head[r] + lane, &cand, &p);
-            acc = plane_abs_distance(plane, p) < thr;
+        const int used = ctl.cr_used[r];
+        if (used != n_final) {
+          // |dist'(p) - dist(p)| <= |dn|_1 * max|p_k| + |dd| for every entry; plus the fp32
+          // rounding of both evaluations (<= ~8 roundings of magnitude |n|_1 max|p_k| + |d|).
+          const float* h = ctl.ph[used % kPipePH];
+          const float ux = h[0], uy = h[1], uz = h[2], ud = h[3];
+          const float pmax = ctl.cr_pmax[r];
+          const float dn = fabsf(plane.n.x - ux) + fabsf(plane.n.y - uy) + fabsf(plane.n.z - uz);
+          const float dd = fabsf(plane.d - ud);
+          const float nsum = fmaxf(fabsf(ux) + fabsf(uy) + fabsf(uz),
+                                   fabsf(plane.n.x) + fabsf(plane.n.y) + fabsf(plane.n.z));
+          const float dmax = fmaxf(fabsf(ud), fabsf(plane.d));
+          const float bound = (dn * pmax + dd) * 1.01f + 2.0e-6f * (nsum * pmax + dmax);
+          if (!(bound < ctl.cr_margin[r])) {  // inconclusive (or NaN): evaluate again
+            PROF_CNT(6, 1);
+            const int m = ctl.cr_m[r];
+            bool acc = false;
+            if (lane < m) {
+              int cand;
+              V3 p;
+              pipe_read_entry(sm, gqueue, a.qcap, xyz, tag_base, ctl.cr_head[r] + lane, &cand, &p);
+              acc = plane_abs_distance(plane, p) < thr;
+            }
+            ok = __ballot_sync(FULL, acc) == ctl.cr_all[r];
           }
-          ok = __ballot_sync(FULL, acc) == ctl.cr_all[r];
         }
+#ifdef PCSEG_FORCE_ROLLBACK
+        if (used != n_final && (c_ver % PCSEG_FORCE_ROLLBACK) == PCSEG_FORCE_ROLLBACK - 1) ok = false;
+#endif
         if (ok) {
           ++c_ver;
           if (lane == 0) {
@@ -156,9 +201,19 @@ __device__ __forceinline__ void pipe_warp_A(const PlanarArgs& a, const float* __
           head = ctl.cr_head[r];
           ninl = ctl.cr_ninl[r];
           inper = ctl.cr_inper[r];
-          if (lane < 10) accj = ctl.cr_snap[r][lane];
           c_spec = c_ver;
           n_posted = n_final;
+          slot_post = slot_fin;
+          ++epoch;
+          if (lane == 0) {
+            ctl.a_spec = c_spec;
+            ctl.rb_chunk = c_spec;
+            __threadfence_block();
+            ctl.rb_epoch = epoch;
+          }
+          while (ctl.s_ack != epoch) {}
+          __threadfence_block();
+          s_done_seen = ctl.s_done;
         }
         progressed = true;
       }
@@ -166,7 +221,8 @@ __device__ __forceinline__ void pipe_warp_A(const PlanarArgs& a, const float* __
     PROF_T(t2);
     // (3) speculate on the next chunk with the newest final plane
     if (c_spec - b_done_seen >= kPipeNC) b_done_seen = ctl.b_done;
-    if (c_spec - b_done_seen < kPipeNC && n_posted - n_final < kPipeDW) {
+    if (c_spec - s_done_seen >= kPipeNC) s_done_seen = ctl.s_done;
+    if (c_spec - b_done_seen < kPipeNC && c_spec - s_done_seen < kPipeNC && n_posted - n_final < kPipeDW) {
       if (head >= tail_seen) {
         tail_seen = ctl.tail_pub;
         __threadfence_block();
@@ -181,13 +237,21 @@ __device__ __forceinline__ void pipe_warp_A(const PlanarArgs& a, const float* __
       if (tail_seen - head >= 32 || (head < tail_seen && b_done_seen >= c_spec)) {
         const int m = min(32, tail_seen - head);
         bool acc = false;
-        V3 p{0.0f, 0.0f, 0.0f};
+        unsigned mg = 0x7f800000u, pm = 0u;  // +inf margin / zero magnitude: entry can never flip
         if (lane < m) {
           int cand;
+          V3 p;
           pipe_read_entry(sm, gqueue, a.qcap, xyz, tag_base, head + lane, &cand, &p);
-          acc = plane_abs_distance(plane, p) < thr;  // ps/planar_region.h:168
+          const float ad = plane_abs_distance(plane, p);
+          acc = ad < thr;  // ps/planar_region.h:168
+          if (vfinite(p)) {
+            mg = __float_as_uint(fabsf(ad - thr));
+            pm = __float_as_uint(fmaxf(fmaxf(fabsf(p.x), fabsf(p.y)), fabsf(p.z)));
+          }
         }
         const unsigned all = __ballot_sync(FULL, acc);
+        const float margin = __uint_as_float(__reduce_min_sync(FULL, mg));
+        const float pmax = __uint_as_float(__reduce_max_sync(FULL, pm));
         const int need = period - inper;
         const unsigned le = (lane == 31) ? FULL : ((2u << lane) - 1u);
         // lane holding the need-th accepted entry (if any): the re-fit cuts the chunk there
@@ -197,51 +261,36 @@ __device__ __forceinline__ void pipe_warp_A(const PlanarArgs& a, const float* __
         const unsigned pmask = processed >= 32 ? FULL : ((1u << processed) - 1u);
         const unsigned amask = all & pmask;
         const int r = c_spec % kPipeNC;
-        if (lane < 10) ctl.cr_snap[r][lane] = accj;
+        if (refit) ++ticket;
         if (lane == 0) {
           ctl.cr_head[r] = head;
           ctl.cr_proc[r] = processed;
           ctl.cr_amask[r] = amask;
+          ctl.cr_post[r] = refit ? ticket : 0;
+          ctl.cr_slot[r] = slot_post;
           ctl.cr_m[r] = m;
           ctl.cr_all[r] = all;
           ctl.cr_vreq[r] = n_posted;
           ctl.cr_used[r] = n_final;
           ctl.cr_inper[r] = inper;
           ctl.cr_ninl[r] = ninl;
-        }
-        if ((amask >> lane) & 1u) {  // plane_estimator_.AddPoint products, :170
-          float* st = sm.stage + lane * 11;
-          st[0] = p.x * p.x; st[1] = p.x * p.y; st[2] = p.x * p.z;
-          st[3] = p.y * p.y; st[4] = p.y * p.z; st[5] = p.z * p.z;
-          st[6] = p.x; st[7] = p.y; st[8] = p.z; st[9] = 1.0f;
-        }
-        __syncwarp();
-        if (lane < 10) {
-          // sequential fp32 sums in FIFO order; loads first (independent), adds after
-          float v[32];
-#pragma unroll
-          for (int i = 0; i < 32; ++i) v[i] = sm.stage[i * 11 + lane];
-#pragma unroll
-          for (int i = 0; i < 32; ++i)
-            if ((amask >> i) & 1u) accj += v[i];
+          ctl.cr_margin[r] = margin;
+          ctl.cr_pmax[r] = pmax;
+          if (refit) {  // plane_ = plane_estimator_.Plane(), :172-176 -- posted by S, applied in order
+            ctl.req_chunk[slot_post] = c_spec;
+            ctl.req_expect[slot_post] = ticket;
+          }
+          __threadfence_block();
+          ctl.a_spec = c_spec + 1;
         }
         const int na = __popc(amask);
         ninl += na;
         inper += na;
         head += processed;
-        if (refit) {  // plane_ = plane_estimator_.Plane(), :172-176 -- posted, applied in order later
+        if (refit) {
           inper = 0;
-          const int s = n_posted % kPipeDW;
-          if (lane < 10) ctl.req_s[s][lane] = accj;
-          ++ticket;
-          __syncwarp();
-          if (lane == 0) {
-            ctl.req_chunk[s] = c_spec;
-            ctl.req_expect[s] = ticket;
-            __threadfence_block();
-            ctl.req_ticket[s] = ticket;
-          }
           ++n_posted;
+          slot_post = (slot_post + 1 == kPipeDW) ? 0 : slot_post + 1;
         }
         ++c_spec;
         ++steps;
@@ -257,22 +306,31 @@ __device__ __forceinline__ void pipe_warp_A(const PlanarArgs& a, const float* __
       PROF_ACC(2, t2, t3);
     } else {
       PROF_CNT(4, 1);
-      if (n_posted - n_final >= kPipeDW) PROF_CNT(6, 1);
-      else if (tail_seen - head < 32) PROF_CNT(7, 1);
+      if (tail_seen - head < 32) PROF_CNT(7, 1);
     }
 #endif
     // (4) nothing to do: refresh what the other warps published; finished?
     if (!progressed) {
       const int bd = ctl.b_done;
+      const int sd = ctl.s_done;
       __threadfence_block();
       const int tp = ctl.tail_pub;
-      if (c_spec == c_ver && n_final == n_posted && bd == c_ver && head == tp) break;
+      if (c_spec == c_ver && n_final == n_posted && bd == c_ver && sd == c_spec && head == tp) break;
       tail_seen = tp;
       b_done_seen = bd;
+      s_done_seen = sd;
       PROF_T(t4);
       PROF_ACC(3, t0, t4);
     }
   }
+  // final sums (S has accumulated every chunk)
+  Estimator est;
+  est_clear(est);
+#pragma unroll
+  for (int i = 0; i < 6; ++i) est.acc[i] = ctl.cur_s[i];
+  est.csum = V3{ctl.cur_s[6], ctl.cur_s[7], ctl.cur_s[8]};
+  est.w = ctl.cur_s[9];
+  __syncwarp();
   if (lane == 0) {
     ctl.ticket = ticket;
     __threadfence_block();
@@ -283,14 +341,6 @@ __device__ __forceinline__ void pipe_warp_A(const PlanarArgs& a, const float* __
     for (int i = 0; i < 8; ++i) a.prof[(size_t)blockIdx.x * 16 + i] += prof_acc[i];
 #endif
   // CheckAndFinalize first lines, ps/planar_region.h:190-196
-  Estimator est;
-  est_clear(est);
-#pragma unroll
-  for (int i = 0; i < 6; ++i) est.acc[i] = __shfl_sync(FULL, accj, i);
-  est.csum.x = __shfl_sync(FULL, accj, 6);
-  est.csum.y = __shfl_sync(FULL, accj, 7);
-  est.csum.z = __shfl_sync(FULL, accj, 8);
-  est.w = __shfl_sync(FULL, accj, 9);
   est.plane = plane;
   est.plane.n = prev_n;
   est.centroid = centroid;
@@ -306,6 +356,77 @@ __device__ __forceinline__ void pipe_warp_A(const PlanarArgs& a, const float* __
     out->centroid[0] = est.centroid.x; out->centroid[1] = est.centroid.y; out->centroid[2] = est.centroid.z;
     for (int i = 0; i < 6; ++i) out->est[i] = est.acc[i];
     out->est[6] = est.csum.x; out->est[7] = est.csum.y; out->est[8] = est.csum.z; out->est[9] = est.w;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Warp S: PlaneEstimator::AddPoint of every inlier in FIFO order (sequential
+// fp32 sums, ps/plane_estimator.cc:55-65) for the chunk records A has written,
+// verified or not; posts the sums of a chunk that ends with a re-fit.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void pipe_warp_S(const PlanarArgs& a, const float* __restrict__ xyz,
+                                            const int* gqueue, int tag_base, const PipeSmem& sm,
+                                            PipeCtl& ctl) {
+  const int lane = threadIdx.x & 31;
+  float accj = 0.0f;  // lane j < 10 owns accumulator j: acc[0..5], csum xyz, weight
+  int c_s = 0, my_epoch = 0;
+  while (true) {
+    const int e = ctl.rb_epoch;
+    if (e != my_epoch) {  // A rolled back to chunk rb_chunk
+      __threadfence_block();
+      const int rc = ctl.rb_chunk;
+      if (c_s > rc) {
+        c_s = rc;
+        if (lane < 10) accj = ctl.cr_snap[rc % kPipeNC][lane];
+      }
+      my_epoch = e;
+      __syncwarp();
+      if (lane == 0) {
+        ctl.s_done = c_s;
+        __threadfence_block();
+        ctl.s_ack = e;
+      }
+      continue;
+    }
+    if (ctl.a_spec <= c_s) {
+      if (ctl.done) break;
+      continue;
+    }
+    __threadfence_block();
+    const int r = c_s % kPipeNC;
+    const int head = ctl.cr_head[r];
+    const unsigned amask = ctl.cr_amask[r];
+    const int post = ctl.cr_post[r];
+    const int slot = ctl.cr_slot[r];
+    if (lane < 10) ctl.cr_snap[r][lane] = accj;
+    if ((amask >> lane) & 1u) {  // plane_estimator_.AddPoint products, ps/planar_region.h:170
+      int cand;
+      V3 p;
+      pipe_read_entry(sm, gqueue, a.qcap, xyz, tag_base, head + lane, &cand, &p);
+      float* st = sm.stage + lane * 11;
+      st[0] = p.x * p.x; st[1] = p.x * p.y; st[2] = p.x * p.z;
+      st[3] = p.y * p.y; st[4] = p.y * p.z; st[5] = p.z * p.z;
+      st[6] = p.x; st[7] = p.y; st[8] = p.z; st[9] = 1.0f;
+    }
+    __syncwarp();
+    if (lane < 10) {
+      // sequential fp32 sums in FIFO order; loads first (independent), adds after
+      float v[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = sm.stage[i * 11 + lane];
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if ((amask >> i) & 1u) accj += v[i];
+      ctl.cur_s[lane] = accj;
+      if (post) ctl.req_s[slot][lane] = accj;
+    }
+    __syncwarp();
+    ++c_s;
+    if (lane == 0) {
+      __threadfence_block();
+      if (post) ctl.req_ticket[slot] = post;
+      ctl.s_done = c_s;
+    }
   }
 }
 

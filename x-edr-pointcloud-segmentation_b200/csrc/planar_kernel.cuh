@@ -45,7 +45,7 @@ __global__ void __launch_bounds__(BLOCK) planar_grow_kernel(PlanarArgs a) {
   int tag_base = 0;
   int refit_last = 0;  // warp R: newest ticket seen on its slot
   __shared__ PipeCtl s_ctl;
-  static_assert(!SMEM || (BLOCK == 384 && kPipeDW == 6), "pipeline roles: warp 0 = A, 4-7 = B, 1-3 and 9-11 = re-fit");
+  static_assert(!SMEM || (BLOCK == 384 && kPipeDW == 5), "pipeline roles: warp 0 = A, 1 = S, 4-7 = B, 2-3 and 9-11 = re-fit");
   __shared__ PipeBShared s_bsh;
   if constexpr (SMEM) {
     if (tid == 0) {
@@ -126,6 +126,11 @@ __global__ void __launch_bounds__(BLOCK) planar_grow_kernel(PlanarArgs a) {
         s_ctl.tail_pub = 1;
         s_ctl.b_done = 0;
         s_ctl.a_verified = 0;
+        s_ctl.a_spec = 0;
+        s_ctl.s_done = 0;
+        s_ctl.s_ack = 0;
+        s_ctl.rb_epoch = 0;
+        s_ctl.rb_chunk = 0;
         s_ctl.done = 0;
       }
       __syncthreads();
@@ -133,7 +138,8 @@ __global__ void __launch_bounds__(BLOCK) planar_grow_kernel(PlanarArgs a) {
       if (warp == 0) pipe_warp_A(a, xyz, nrm, gqueue, seed, tag_base, sm, s_ctl, &s_res);
       else if (warp >= 4 && warp < 8)
         pipe_group_B(a, xyz, a.labels + (size_t)f * N, gqueue, inliers, label_id, base, tag_base, sm, s_ctl, s_bsh, tid - 128);
-      else if (warp != 8) pipe_warp_R(s_ctl, warp < 4 ? warp - 1 : warp - 6, refit_last);
+      else if (warp == 1) pipe_warp_S(a, xyz, gqueue, tag_base, sm, s_ctl);
+      else if (warp != 8) pipe_warp_R(s_ctl, warp < 4 ? warp - 2 : warp - 7, refit_last);
     } else {
       if (tid < 32) planar_grow_warp(a, xyz, nrm, labels, queue, claim, inliers, seed, label_id, base, &s_res);
     }
