@@ -22,7 +22,7 @@ for mode, name in ((pcseg.SEEDS_ALL_DESCENDING, "alldesc"), (pcseg.SEEDS_PLANE_S
         pr = b.profile()
         tot = pr.sum(axis=0).astype(float)
         nch = max(b.frame_stats()[:, 6].sum(), 1) * 3
-        print(name, "A cycles/chunk: finalize %.0f verify %.0f speculate %.0f idle-iters %.0f | per chunk: idle iters %.2f rollbacks %.4f inconclusive-verify %.2f starved %.2f" % tuple(tot[:8] / nch))
+        print(name, "A cycles/chunk: finalize %.0f verify %.0f speculate %.0f idle-iters %.0f | per chunk: queue ahead %.1f rollbacks %.4f spec depth %.2f starved iters %.2f" % tuple(tot[:8] / nch))
         print(name, "B cycles/chunk: read+masktest %.0f claim %.0f enqueue+publish %.0f waiting %.0f | chunks %.2f" % tuple(tot[8:13] / nch))
         print(name, "kernel level, frame 0 per run: seed search %.2f ms, finalize %.2f ms, regions tried %d, below min inliers %d" % (pr[0, 13] / 3 / 1.965e6, pr[0, 14] / 3 / 1.965e6, pr[0, 15] // 3 // 1000000, (pr[0, 15] // 3) % 1000000))
     except Exception as e:

@@ -175,7 +175,6 @@ __device__ __forceinline__ void pipe_warp_A(const PlanarArgs& a, const float* __
           const float dmax = fmaxf(fabsf(ud), fabsf(plane.d));
           const float bound = (dn * pmax + dd) * 1.01f + 2.0e-6f * (nsum * pmax + dmax);
           if (!(bound < ctl.cr_margin[r])) {  // inconclusive (or NaN): evaluate again
-            PROF_CNT(6, 1);
             const int m = ctl.cr_m[r];
             bool acc = false;
             if (lane < m) {
@@ -236,6 +235,8 @@ __device__ __forceinline__ void pipe_warp_A(const PlanarArgs& a, const float* __
       }
       if (tail_seen - head >= 32 || (head < tail_seen && b_done_seen >= c_spec)) {
         const int m = min(32, tail_seen - head);
+        PROF_CNT(4, tail_seen - head);
+        PROF_CNT(6, c_spec - c_ver);
         bool acc = false;
         unsigned mg = 0x7f800000u, pm = 0u;  // +inf margin / zero magnitude: entry can never flip
         if (lane < m) {
@@ -305,7 +306,6 @@ __device__ __forceinline__ void pipe_warp_A(const PlanarArgs& a, const float* __
       PROF_ACC(1, t1, t2);
       PROF_ACC(2, t2, t3);
     } else {
-      PROF_CNT(4, 1);
       if (tail_seen - head < 32) PROF_CNT(7, 1);
     }
 #endif
@@ -465,20 +465,25 @@ __device__ __forceinline__ void pipe_warp_R(PipeCtl& ctl, int s, int& last) {
 
 // ---------------------------------------------------------------------------
 // Group B (4 warps, 128 threads): expansion of verified chunks -- labels,
-// inlier list, AddNeighbors.  Thread t handles ONE (entry, slot) pair of the
-// chunk, e = t >> 2, s = t & 3, so t itself is the (lane, slot) order key of
-// grow_common.cuh: a neighbour cell is enqueued by its smallest claiming t and
-// the winners are appended in t order.  The four warps meet at named barrier 1.
+// inlier list, AddNeighbors.  One pass takes up to kPipeBRec consecutive
+// verified chunk records (<= 128 contiguous queue entries); thread e handles
+// entry e and its four neighbour slots, so key = e * 4 + s is the (position,
+// slot) order of grow_common.cuh: a neighbour cell is enqueued by its smallest
+// claiming key and the winners are appended in key order.  The cost of a pass
+// is latency (barriers, shared-memory round trips), nearly independent of the
+// number of entries, so B catches up by taking more records whenever A is ahead.
+// The four warps meet at named barrier 1.
 // ---------------------------------------------------------------------------
 constexpr int kPipeBThreads = 128;
+constexpr int kPipeBRec = 4;
 
 __device__ __forceinline__ void pipe_bar_B() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
 struct PipeBShared {
   volatile int cmd;
-  volatile unsigned wb[4];     // per-warp winner ballots
+  volatile unsigned wb[4][4];  // [warp][slot] winner ballots
   volatile int unres[4];       // per-warp "some claim still probing"
-  volatile int cand[32];       // chunk cells (rejection rule)
+  volatile int cand[128];      // batch cells (rejection rule)
 };
 
 __device__ __forceinline__ void pipe_group_B(const PlanarArgs& a, const float* __restrict__ xyz, int* labels,
@@ -486,7 +491,7 @@ __device__ __forceinline__ void pipe_group_B(const PlanarArgs& a, const float* _
                                              const PipeSmem& sm, PipeCtl& ctl, PipeBShared& bs, int t) {
   const unsigned FULL = 0xffffffffu;
   const int lane = t & 31, bw = t >> 5;
-  const int e = t >> 2, s = t & 3;
+  const int e = t;
   const int rows = a.rows, cols = a.cols;
   const int R = sm.ring;
   const FastDiv fdrows = make_fastdiv(rows);
@@ -499,8 +504,9 @@ __device__ __forceinline__ void pipe_group_B(const PlanarArgs& a, const float* _
     if (t == 0) {
       int cmd;
       while (true) {
-        if (ctl.a_verified > k) { cmd = 1; break; }
-        if (pub_k < k) { cmd = 2; break; }  // idle with unpublished enqueues: flush
+        const int av = ctl.a_verified;
+        if (av > k) { cmd = min(av - k, kPipeBRec); break; }
+        if (pub_k < k) { cmd = -1; break; }  // idle with unpublished enqueues: flush
         if (ctl.done) { cmd = 0; break; }
       }
       __threadfence_block();
@@ -509,7 +515,7 @@ __device__ __forceinline__ void pipe_group_B(const PlanarArgs& a, const float* _
     pipe_bar_B();
     const int cmd = bs.cmd;
     if (cmd == 0) break;
-    if (cmd == 2) {
+    if (cmd < 0) {
       cp_async_wait<0>();
       pipe_bar_B();
       if (t == 0) {
@@ -522,14 +528,28 @@ __device__ __forceinline__ void pipe_group_B(const PlanarArgs& a, const float* _
       continue;
     }
     PROF_T(t1);
-    const int r = k % kPipeNC;
-    const int head = ctl.cr_head[r];
-    const int processed = ctl.cr_proc[r];
-    const unsigned amask = ctl.cr_amask[r];
-    const unsigned pmask = processed >= 32 ? FULL : ((1u << processed) - 1u);
-    const unsigned rejmask = ~amask & pmask;
-    const bool mine = e < processed;
-    const bool acc = (amask >> e) & 1u;
+    // the batch: records k .. k+cmd-1, entries [head, head + total)
+    const int head = ctl.cr_head[k % kPipeNC];
+    int total = 0, nacc_before = 0, nacc_total = 0;
+    bool mine = false, acc = false, any_rej = false;
+#pragma unroll
+    for (int j = 0; j < kPipeBRec; ++j) {
+      if (j < cmd) {
+        const int r = (k + j) % kPipeNC;
+        const int pj = ctl.cr_proc[r];
+        const unsigned am = ctl.cr_amask[r];
+        const unsigned pm = pj >= 32 ? FULL : ((1u << pj) - 1u);
+        any_rej = any_rej || ((~am & pm) != 0u);
+        const int q = e - total;  // index inside record j
+        if (q >= 0 && q < pj) {
+          mine = true;
+          acc = (am >> q) & 1u;
+          nacc_before = nacc_total + __popc(am & ((1u << q) - 1u));
+        }
+        total += pj;
+        nacc_total += __popc(am);
+      }
+    }
     int cand = -1;
     if (mine) {
       const int pos = head + e;
@@ -537,98 +557,138 @@ __device__ __forceinline__ void pipe_group_B(const PlanarArgs& a, const float* _
       if (((volatile int*)sm.q_tag)[slot] == tag_base + pos) cand = ((volatile int*)sm.q_cell)[slot];
       else cand = *(volatile int*)(gqueue + (pos & (a.qcap - 1)));
     }
-    // AddNeighbors, ps/planar_region.h:229-255: slot 0 (c-1,r), 1 (c,r-1), 2 (c,r+1), 3 (c+1,r)
-    int nb = -1;
+    // AddNeighbors, ps/planar_region.h:229-255: (c-1,r), (c,r-1), (c,r+1), (c+1,r)
+    int nb[4] = {-1, -1, -1, -1};
+    bool el[4] = {false, false, false, false};
     if (acc) {
+      labels[cand] = label_id;                    // :177
+      inliers[base + ninl + nacc_before] = cand;  // :169
+      // only the seed can still have its bit set when it is accepted
+      if (k == 0 && e == 0) atomicAnd(&sm.mask[cand >> 5], ~(1u << (cand & 31)));
       int row, col;
       fast_divmod(fdrows, cand, &col, &row);
-      if (s == 0) { if (col > 0) nb = cand - rows; }
-      else if (s == 1) { if (row > 0) nb = cand - 1; }
-      else if (s == 2) { if (row < rows - 1) nb = cand + 1; }
-      else { if (col < cols - 1) nb = cand + rows; }
-      if (s == 0) {
-        labels[cand] = label_id;                                                  // :177
-        inliers[base + ninl + __popc(amask & ((1u << e) - 1u))] = cand;           // :169
-        // only the seed can still have its bit set when it is accepted
-        if (k == 0) atomicAnd(&sm.mask[cand >> 5], ~(1u << (cand & 31)));
-      }
+      if (col > 0) nb[0] = cand - rows;
+      if (row > 0) nb[1] = cand - 1;
+      if (row < rows - 1) nb[2] = cand + 1;
+      if (col < cols - 1) nb[3] = cand + rows;
+#pragma unroll
+      for (int s = 0; s < 4; ++s) el[s] = nb[s] >= 0 && mask_test(sm.mask, nb[s]);
     }
-    bool el = nb >= 0 && mask_test(sm.mask, nb);
     // a cell rejected at entry q is kUnlabeled again for every later entry (:181)
-    if (rejmask) {
-      if (s == 0 && mine) bs.cand[e] = cand;
+    if (any_rej) {
+      if (mine) bs.cand[e] = cand;
       pipe_bar_B();
-      if (nb >= 0) {
-        for (unsigned rm = rejmask & ((1u << e) - 1u); rm; rm &= rm - 1)
-          el = el || (nb == bs.cand[__ffs(rm) - 1]);
+      if (acc) {
+        int off = 0;
+#pragma unroll
+        for (int j = 0; j < kPipeBRec; ++j) {
+          if (j < cmd && off < e) {
+            const int r = (k + j) % kPipeNC;
+            const int pj = ctl.cr_proc[r];
+            const unsigned pm = pj >= 32 ? FULL : ((1u << pj) - 1u);
+            unsigned rm = ~ctl.cr_amask[r] & pm;
+            const int lim = e - off;  // only entries before e
+            if (lim < 32) rm &= (1u << lim) - 1u;
+            for (; rm; rm &= rm - 1) {
+              const int cq = bs.cand[off + __ffs(rm) - 1];
+#pragma unroll
+              for (int s = 0; s < 4; ++s) el[s] = el[s] || (nb[s] == cq);
+            }
+            off += pj;
+          }
+        }
       }
     }
     PROF_T(t2);
-    // smallest key t per neighbour cell wins the enqueue
-    bool win = false, unres = el, first = true;
-    int probe = (int)(((unsigned)nb * 2654435761u) >> 21) & (kPipeHash - 1);
+    // smallest key per neighbour cell wins the enqueue
+    bool win[4] = {false, false, false, false};
+    bool unres[4] = {el[0], el[1], el[2], el[3]};
+    int probe[4];
+#pragma unroll
+    for (int s = 0; s < 4; ++s) probe[s] = (int)(((unsigned)nb[s] * 2654435761u) >> 21) & (kPipeHash - 1);
+    bool first = true;
     while (true) {
-      if (unres) atomicMin(&sm.htab[probe], ((unsigned)nb << 7) | (unsigned)t);
+#pragma unroll
+      for (int s = 0; s < 4; ++s)
+        if (unres[s]) atomicMin(&sm.htab[probe[s]], ((unsigned)nb[s] << 9) | (unsigned)(e * 4 + s));
       pipe_bar_B();
-      // every mask test of this chunk is done: rejected cells become unlabeled again
+      // every mask test of this batch is done: rejected cells become unlabeled again
       // (ordered before the winners clear their bits, after the next barrier)
-      if (first && mine && !acc && s == 0) atomicOr(&sm.mask[cand >> 5], 1u << (cand & 31));
+      if (first && mine && !acc) atomicOr(&sm.mask[cand >> 5], 1u << (cand & 31));
       first = false;
-      if (unres) {
-        const unsigned v = ((volatile unsigned*)sm.htab)[probe];
-        if ((int)(v >> 7) == nb) {
-          win = (v & 127u) == (unsigned)t;
-          unres = false;
-        } else {
-          probe = (probe + 1) & (kPipeHash - 1);
+#pragma unroll
+      for (int s = 0; s < 4; ++s) {
+        if (unres[s]) {
+          const unsigned v = ((volatile unsigned*)sm.htab)[probe[s]];
+          if ((int)(v >> 9) == nb[s]) {
+            win[s] = (v & 511u) == (unsigned)(e * 4 + s);
+            unres[s] = false;
+          } else {
+            probe[s] = (probe[s] + 1) & (kPipeHash - 1);
+          }
         }
       }
-      const unsigned wbal = __ballot_sync(FULL, win);
-      const unsigned ubal = __ballot_sync(FULL, unres);
+      const unsigned b0 = __ballot_sync(FULL, win[0]), b1 = __ballot_sync(FULL, win[1]);
+      const unsigned b2 = __ballot_sync(FULL, win[2]), b3 = __ballot_sync(FULL, win[3]);
+      const unsigned ub = __ballot_sync(FULL, unres[0] || unres[1] || unres[2] || unres[3]);
       if (lane == 0) {
-        bs.wb[bw] = wbal;
-        bs.unres[bw] = ubal != 0u;
+        bs.wb[bw][0] = b0; bs.wb[bw][1] = b1; bs.wb[bw][2] = b2; bs.wb[bw][3] = b3;
+        bs.unres[bw] = ub != 0u;
       }
       pipe_bar_B();
       if (!(bs.unres[0] | bs.unres[1] | bs.unres[2] | bs.unres[3])) break;
       pipe_bar_B();  // everyone has read the flags before they are rewritten
     }
     PROF_T(t3);
-    const unsigned w0 = bs.wb[0], w1 = bs.wb[1], w2 = bs.wb[2], w3 = bs.wb[3];
-    const int c0 = __popc(w0), c1 = __popc(w1), c2 = __popc(w2), c3 = __popc(w3);
-    const unsigned myb = bw == 0 ? w0 : (bw == 1 ? w1 : (bw == 2 ? w2 : w3));
-    const int off = (bw > 0 ? c0 : 0) + (bw > 1 ? c1 : 0) + (bw > 2 ? c2 : 0) + __popc(myb & ((1u << lane) - 1u));
-    const int new_head = head + processed;
-    if (win) {
-      sm.htab[probe] = kHashEmpty;
-      atomicAnd(&sm.mask[nb >> 5], ~(1u << (nb & 31)));  // kAlreadyInUnexaminedPointsQueue
-      const int qp = tail + off;
-      gqueue[qp & (a.qcap - 1)] = nb;
-      if (qp - new_head < R) {
-        const int sl = qp & (R - 1);
-        sm.q_tag[sl] = tag_base + qp;
-        sm.q_cell[sl] = nb;
-        const float* src = xyz + 3 * (size_t)nb;
-        cp_async4(sm.q_xyz + 3 * sl, src);
-        cp_async4(sm.q_xyz + 3 * sl + 1, src + 1);
-        cp_async4(sm.q_xyz + 3 * sl + 2, src + 2);
+    int off = 0, nwin = 0;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      const int c = __popc(bs.wb[w][0]) + __popc(bs.wb[w][1]) + __popc(bs.wb[w][2]) + __popc(bs.wb[w][3]);
+      if (w < bw) off += c;
+      nwin += c;
+    }
+    {
+      const unsigned lt = (1u << lane) - 1u;
+      off += __popc(bs.wb[bw][0] & lt) + __popc(bs.wb[bw][1] & lt) + __popc(bs.wb[bw][2] & lt) +
+             __popc(bs.wb[bw][3] & lt);
+    }
+    const int new_head = head + total;
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      if (win[s]) {
+        const int n = nb[s];
+        sm.htab[probe[s]] = kHashEmpty;
+        atomicAnd(&sm.mask[n >> 5], ~(1u << (n & 31)));  // kAlreadyInUnexaminedPointsQueue
+        const int qp = tail + off;
+        gqueue[qp & (a.qcap - 1)] = n;
+        if (qp - new_head < R) {
+          const int sl = qp & (R - 1);
+          sm.q_tag[sl] = tag_base + qp;
+          sm.q_cell[sl] = n;
+          const float* src = xyz + 3 * (size_t)n;
+          cp_async4(sm.q_xyz + 3 * sl, src);
+          cp_async4(sm.q_xyz + 3 * sl + 1, src + 1);
+          cp_async4(sm.q_xyz + 3 * sl + 2, src + 2);
+        }
+        ++off;
       }
     }
     cp_async_commit();
     const int tail_prev = tail;
-    tail += c0 + c1 + c2 + c3;
-    ninl += __popc(amask);
-    ++k;
-    // publish one chunk behind, so that the xyz copies stay off the critical path
+    const int k_prev = k;
+    tail += nwin;
+    ninl += nacc_total;
+    k += cmd;
+    // publish one pass behind, so that the xyz copies stay off the critical path
     cp_async_wait<1>();
     pipe_bar_B();
     if (t == 0) {
       __threadfence_block();
       ctl.tail_pub = tail_prev;
       __threadfence_block();
-      ctl.b_done = k - 1;
+      ctl.b_done = k_prev;
     }
-    pub_k = k - 1;
+    pub_k = k_prev;
     PROF_T(t4);
     PROF_ACC(0, t1, t2);
     PROF_ACC(1, t2, t3);
