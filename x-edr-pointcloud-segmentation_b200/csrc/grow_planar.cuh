@@ -246,19 +246,21 @@ __device__ void trace_boundary(const int* labels, int rows, int cols, int start_
   int first = -1;
   while (true) {
     // detail::FindNextBoundaryPointDirection, ps/planar_region.cc:47-65
-    int lab[8];
+    // bit i of `same` <=> neighbour i (table order) is in bounds and carries the region label
+    unsigned same = 0u;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const int nx = cx + kDx8[i], ny = cy + kDy8[i];
-      lab[i] = (nx >= 0 && nx < cols && ny >= 0 && ny < rows)
-                   ? labels[curr_idx + kDx8[i] * rows + kDy8[i]]
-                   : (region_label ^ 0x40000000);  // never equal
+      if (nx >= 0 && nx < cols && ny >= 0 && ny < rows &&
+          labels[curr_idx + kDx8[i] * rows + kDy8[i]] == region_label)
+        same |= 1u << i;
     }
+    // first direction in the order (dir+1 .. dir+8) mod 8: rotate so that bit 0 = dir+1
     int nd = -1;
-#pragma unroll
-    for (int delta = 1; delta <= 8; ++delta) {
-      const int d = (dir + delta) & 7;
-      if (nd < 0 && lab[d] == region_label) nd = d;
+    if (same) {
+      const unsigned sh = (unsigned)(dir + 1) & 7u;
+      const unsigned rot = ((same >> sh) | (same << (8u - sh))) & 0xffu;
+      nd = (int)((sh + (unsigned)__ffs(rot) - 1u) & 7u);
     }
     if (nd < 0) { err = kErrTraceCheck; break; }  // CHECK_GE(new_direction_index, 0)
     dir = (nd + 4) & 7;

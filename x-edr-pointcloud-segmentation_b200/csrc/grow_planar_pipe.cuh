@@ -44,14 +44,14 @@ struct PipeCtl {
   // B -> A
   volatile int tail_pub;    // queue entries [0, tail_pub) are complete (cell, xyz)
   volatile int b_done;      // chunks whose enqueues are all inside tail_pub
+  volatile int b_ack;       // roll-back epoch acknowledged
   // S -> A
   volatile int s_done;      // chunks accumulated
   volatile int s_ack;       // roll-back epoch acknowledged
   volatile float cur_s[10]; // sums after chunk s_done - 1
   // A -> B, S
-  volatile int a_verified;  // chunks [0, a_verified) are final             (B)
-  volatile int a_spec;      // chunk records [0, a_spec) are written         (S)
-  volatile int rb_epoch;    // bumped by A on a roll-back to chunk rb_chunk  (S)
+  volatile int a_spec;      // chunk records [0, a_spec) are written            (S, B)
+  volatile int rb_epoch;    // bumped by A on a roll-back to chunk rb_chunk     (S, B)
   volatile int rb_chunk;
   volatile int done;        // region finished: all role loops exit
   // chunk records (written by A before a_spec passes them)
@@ -68,6 +68,8 @@ struct PipeCtl {
   float ph[kPipePH][4];            // plane of version v at v % kPipePH
   // S-private per chunk: sums before the chunk
   float cr_snap[kPipeNC][10];
+  // B-private per chunk: queue tail before the chunk's enqueues (undo log)
+  int cr_tail0[kPipeNC];
   // re-fit slots
   volatile float req_s[kPipeDW][10];
   volatile int req_ticket[kPipeDW];
@@ -80,6 +82,13 @@ struct PipeCtl {
 };
 
 using PipeSmem = PlanarSmem;
+
+// Back-off of an idle role: keeps its polling off the issue slots and the shared-memory
+// pipe that the busy roles of both resident frames need.
+#ifndef PIPE_IDLE_NS
+#define PIPE_IDLE_NS 20
+#endif
+#define PIPE_IDLE() __nanosleep(PIPE_IDLE_NS)
 
 // Queue entry `pos` -> (cell, xyz); ring slot if its tag matches, else the global queue.
 __device__ __forceinline__ void pipe_read_entry(const PipeSmem& sm, const int* gqueue, int qcap,
@@ -191,10 +200,6 @@ __device__ __forceinline__ void pipe_warp_A(const PlanarArgs& a, const float* __
 #endif
         if (ok) {
           ++c_ver;
-          if (lane == 0) {
-            __threadfence_block();
-            ctl.a_verified = c_ver;
-          }
         } else {  // mis-speculation: resume from this chunk with the true plane
           PROF_CNT(5, 1);
           head = ctl.cr_head[r];
@@ -210,9 +215,11 @@ __device__ __forceinline__ void pipe_warp_A(const PlanarArgs& a, const float* __
             __threadfence_block();
             ctl.rb_epoch = epoch;
           }
-          while (ctl.s_ack != epoch) {}
+          while (ctl.s_ack != epoch || ctl.b_ack != epoch) {}
           __threadfence_block();
           s_done_seen = ctl.s_done;
+          b_done_seen = ctl.b_done;
+          tail_seen = ctl.tail_pub;
         }
         progressed = true;
       }
@@ -221,7 +228,8 @@ __device__ __forceinline__ void pipe_warp_A(const PlanarArgs& a, const float* __
     // (3) speculate on the next chunk with the newest final plane
     if (c_spec - b_done_seen >= kPipeNC) b_done_seen = ctl.b_done;
     if (c_spec - s_done_seen >= kPipeNC) s_done_seen = ctl.s_done;
-    if (c_spec - b_done_seen < kPipeNC && c_spec - s_done_seen < kPipeNC && n_posted - n_final < kPipeDW) {
+    if (c_spec - b_done_seen < kPipeNC && c_spec - s_done_seen < kPipeNC && c_spec - c_ver < kPipeNC &&
+        n_posted - n_final < kPipeDW) {
       if (head >= tail_seen) {
         tail_seen = ctl.tail_pub;
         __threadfence_block();
@@ -319,6 +327,7 @@ __device__ __forceinline__ void pipe_warp_A(const PlanarArgs& a, const float* __
       tail_seen = tp;
       b_done_seen = bd;
       s_done_seen = sd;
+      PIPE_IDLE();
       PROF_T(t4);
       PROF_ACC(3, t0, t4);
     }
@@ -390,6 +399,7 @@ __device__ __forceinline__ void pipe_warp_S(const PlanarArgs& a, const float* __
     }
     if (ctl.a_spec <= c_s) {
       if (ctl.done) break;
+      PIPE_IDLE();
       continue;
     }
     __threadfence_block();
@@ -495,7 +505,7 @@ __device__ __forceinline__ void pipe_group_B(const PlanarArgs& a, const float* _
   const int rows = a.rows, cols = a.cols;
   const int R = sm.ring;
   const FastDiv fdrows = make_fastdiv(rows);
-  int k = 0, pub_k = 0, tail = 1, ninl = 0;
+  int k = 0, pub_k = 0, tail = 1, ninl = 0, my_epoch = 0;
 #ifdef PCSEG_PROFILE
   long long prof_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 #endif
@@ -504,10 +514,12 @@ __device__ __forceinline__ void pipe_group_B(const PlanarArgs& a, const float* _
     if (t == 0) {
       int cmd;
       while (true) {
-        const int av = ctl.a_verified;
+        if (ctl.rb_epoch != my_epoch) { cmd = -2; break; }  // roll-back: undo
+        const int av = ctl.a_spec;
         if (av > k) { cmd = min(av - k, kPipeBRec); break; }
         if (pub_k < k) { cmd = -1; break; }  // idle with unpublished enqueues: flush
         if (ctl.done) { cmd = 0; break; }
+        PIPE_IDLE();
       }
       __threadfence_block();
       bs.cmd = cmd;
@@ -515,6 +527,57 @@ __device__ __forceinline__ void pipe_group_B(const PlanarArgs& a, const float* _
     pipe_bar_B();
     const int cmd = bs.cmd;
     if (cmd == 0) break;
+    if (cmd == -2) {
+      // A rolled back to chunk rb_chunk: undo the expansion of chunks k-1 .. rb_chunk in
+      // reverse order.  Per chunk the inverse of "rejected entry -> bit set, winner -> bit
+      // cleared + appended" is "appended cells -> bit set, then rejected entries -> bit
+      // cleared"; accepted entries get their label back (still queued = kUnlabeled in HBM).
+      cp_async_wait<0>();
+      __threadfence_block();
+      const int ep = ctl.rb_epoch;
+      const int rc = ctl.rb_chunk;
+      pipe_bar_B();
+      int tail_hi = tail;
+      for (int c = k - 1; c >= rc; --c) {
+        const int r = c % kPipeNC;
+        const int t0q = ctl.cr_tail0[r];
+        for (int qp = t0q + t; qp < tail_hi; qp += kPipeBThreads) {
+          const int n = *(volatile int*)(gqueue + (qp & (a.qcap - 1)));
+          atomicOr(&sm.mask[n >> 5], 1u << (n & 31));
+          // the slot must not match again if this position is re-appended while the ring is full
+          if (((volatile int*)sm.q_tag)[qp & (R - 1)] == tag_base + qp) sm.q_tag[qp & (R - 1)] = -1;
+        }
+        pipe_bar_B();
+        const int pj = ctl.cr_proc[r];
+        const unsigned am = ctl.cr_amask[r];
+        if (t < pj) {
+          const int pos = ctl.cr_head[r] + t;
+          const int slot = pos & (R - 1);
+          int cell;
+          if (((volatile int*)sm.q_tag)[slot] == tag_base + pos) cell = ((volatile int*)sm.q_cell)[slot];
+          else cell = *(volatile int*)(gqueue + (pos & (a.qcap - 1)));
+          if ((am >> t) & 1u) labels[cell] = kUnlabeled;
+          else atomicAnd(&sm.mask[cell >> 5], ~(1u << (cell & 31)));
+        }
+        pipe_bar_B();
+        ninl -= __popc(am);
+        tail_hi = t0q;
+      }
+      if (k > rc) {
+        tail = tail_hi;
+        k = rc;
+      }
+      pub_k = k;
+      my_epoch = ep;
+      if (t == 0) {
+        __threadfence_block();
+        ctl.tail_pub = tail;
+        ctl.b_done = k;
+        __threadfence_block();
+        ctl.b_ack = ep;
+      }
+      continue;
+    }
     if (cmd < 0) {
       cp_async_wait<0>();
       pipe_bar_B();
@@ -530,7 +593,7 @@ __device__ __forceinline__ void pipe_group_B(const PlanarArgs& a, const float* _
     PROF_T(t1);
     // the batch: records k .. k+cmd-1, entries [head, head + total)
     const int head = ctl.cr_head[k % kPipeNC];
-    int total = 0, nacc_before = 0, nacc_total = 0;
+    int total = 0, nacc_before = 0, nacc_total = 0, first_of = -1;
     bool mine = false, acc = false, any_rej = false;
 #pragma unroll
     for (int j = 0; j < kPipeBRec; ++j) {
@@ -541,6 +604,7 @@ __device__ __forceinline__ void pipe_group_B(const PlanarArgs& a, const float* _
         const unsigned pm = pj >= 32 ? FULL : ((1u << pj) - 1u);
         any_rej = any_rej || ((~am & pm) != 0u);
         const int q = e - total;  // index inside record j
+        if (q == 0) first_of = r;
         if (q >= 0 && q < pj) {
           mine = true;
           acc = (am >> q) & 1u;
@@ -653,6 +717,7 @@ __device__ __forceinline__ void pipe_group_B(const PlanarArgs& a, const float* _
              __popc(bs.wb[bw][3] & lt);
     }
     const int new_head = head + total;
+    if (first_of >= 0) ctl.cr_tail0[first_of] = tail + off;  // undo log: tail before this record's enqueues
 #pragma unroll
     for (int s = 0; s < 4; ++s) {
       if (win[s]) {

@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(BLOCK) planar_grow_kernel(PlanarArgs a) {
         gqueue[0] = seed;
         s_ctl.tail_pub = 1;
         s_ctl.b_done = 0;
-        s_ctl.a_verified = 0;
+        s_ctl.b_ack = 0;
         s_ctl.a_spec = 0;
         s_ctl.s_done = 0;
         s_ctl.s_ack = 0;
