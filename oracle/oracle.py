@@ -77,28 +77,65 @@ def build(force=False):
     return so
 
 
+def _bind(so):
+    L = C.CDLL(so)
+    L.oracle_polygon_area.restype = C.c_float
+    for name, rt in [("inlier_offsets", I32P), ("inlier_indices", I32P),
+                     ("label_ids", I32P), ("seed_indices", I32P),
+                     ("planes", F32P), ("centroids", F32P), ("areas", F32P),
+                     ("estimators", F32P), ("boundary_offsets", I32P),
+                     ("boundary_indices", I32P),
+                     ("discontinuous_offsets", I32P),
+                     ("discontinuous_indices", I32P), ("hull_offsets", I32P),
+                     ("hull_points", F32P), ("seed_points", F32P)]:
+        f = getattr(L, "oracle_regions_" + name)
+        f.restype = rt
+        f.argtypes = [C.c_void_p]
+    L.oracle_regions_count.argtypes = [C.c_void_p]
+    L.oracle_regions_free.argtypes = [C.c_void_p]
+    return L
+
+
+_REF = None       # oracle/_ref/libref.so: the reference's own sources against shims
+_USE_REF = False
+
+
+def ref_path():
+    return os.path.join(_HERE, "_ref", "libref.so")
+
+
+def ref_available():
+    """True when oracle/_ref/libref.so exists (built here from /root/reference by
+    `make -C oracle ref`; it travels to the GPU box as a prebuilt file)."""
+    return os.path.exists(ref_path())
+
+
+class reference:
+    """Context manager: inside it every function of this module runs the
+    REFERENCE's own code (oracle/_ref) instead of the restatement."""
+
+    def __enter__(self):
+        global _USE_REF
+        self.prev = _USE_REF
+        _USE_REF = True
+        return self
+
+    def __exit__(self, *a):
+        global _USE_REF
+        _USE_REF = self.prev
+
+
 def lib():
-    global _LIB
+    global _LIB, _REF
+    if _USE_REF:
+        if _REF is None:
+            _REF = _bind(ref_path())
+        return _REF
     if _LIB is None:
         so = os.path.join(_HERE, "liboracle.so")
         if not os.path.exists(so):
             build()
-        L = C.CDLL(so)
-        L.oracle_polygon_area.restype = C.c_float
-        for name, rt in [("inlier_offsets", I32P), ("inlier_indices", I32P),
-                         ("label_ids", I32P), ("seed_indices", I32P),
-                         ("planes", F32P), ("centroids", F32P), ("areas", F32P),
-                         ("estimators", F32P), ("boundary_offsets", I32P),
-                         ("boundary_indices", I32P),
-                         ("discontinuous_offsets", I32P),
-                         ("discontinuous_indices", I32P), ("hull_offsets", I32P),
-                         ("hull_points", F32P), ("seed_points", F32P)]:
-            f = getattr(L, "oracle_regions_" + name)
-            f.restype = rt
-            f.argtypes = [C.c_void_p]
-        L.oracle_regions_count.argtypes = [C.c_void_p]
-        L.oracle_regions_free.argtypes = [C.c_void_p]
-        _LIB = L
+        _LIB = _bind(so)
     return _LIB
 
 
