@@ -120,6 +120,24 @@ int pcseg_segment_cluster(pcseg_ctx*, const float* xyz, int rows, int cols,
 int pcseg_mean_shift_modes(pcseg_ctx*, const float* xyz, int rows, int cols,
                            const int* labels, int iterations, float* modes_out);
 
+/* Same for the seed cells [cell_begin, cell_end) only (contiguous linear-index
+ * shard; seeds are mutually independent while labels are read-only,
+ * ps/mean_shift_segmentation.h:232-260).  modes_out holds
+ * (cell_end - cell_begin) records.  Used to shard one large cloud's seeds over
+ * several GPUs (cloud + labels replicated, records all-gathered by the caller). */
+int pcseg_mean_shift_modes_range(pcseg_ctx*, const float* xyz, int rows, int cols,
+                                 const int* labels, int iterations, int cell_begin,
+                                 int cell_end, float* modes_out);
+
+/* Sort + growth phase (ps/mean_shift_segmentation.h:262-329) on mode records
+ * produced by pcseg_mean_shift_modes[_range] (rows*cols records, e.g. after an
+ * all-gather of the shards).  labels is in/out. */
+int pcseg_mean_shift_from_modes(pcseg_ctx*, const float* xyz, int rows, int cols,
+                                const float* modes,
+                                const pcseg_cluster_config* cfg,
+                                int initial_region_id_offset, int sort_mode,
+                                int* labels, pcseg_regions** out);
+
 /* Replaces ps/mean_shift_segmentation.h:207-330 SlidingMeanShift (iteration
  * phase + sort + growth).  sort_mode 0 = the reference's std::sort permutation
  * (libstdc++ introsort replayed on (intensity, seed order) keys), 1 = stable. */

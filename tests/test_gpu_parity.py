@@ -236,6 +236,54 @@ def test_mean_shift_modes_parity(ctx):
     assert np.array_equal(bits(gs[:, :6]), bits(o[:, :6]))
 
 
+def _assert_ms_equal(g_lab, g_r, o_lab, o_r):
+    assert np.array_equal(g_lab, o_lab)
+    assert_regions_equal(g_r, o_r, "cluster")
+    assert np.all(np.abs(g_r.seed_points - o_r.seed_points) <= 1e-4)  # 1e-4 of the 1 m bandwidth
+    assert np.array_equal(bits(g_r.seed_points), bits(o_r.seed_points))
+
+
+@pytest.mark.parametrize("rows,cols,pitch,blobs,h,sort_mode,min_inl", [
+    (90, 120, 0.12, 8, 1, 0, 7), (90, 120, 0.12, 8, 2, 1, 7), (200, 300, 0.05, 40, 1, 0, 7),
+    (120, 90, 0.2, 10, 3, 0, 50), (64, 64, 0.3, 6, 1, 0, 400)])
+def test_mean_shift_full_parity(ctx, rows, cols, pitch, blobs, h, sort_mode, min_inl):
+    """SlidingMeanShift end to end (iteration + sort + growth), ps/mean_shift_segmentation.h:207-330."""
+    xyz = synth.c5(rows=rows, cols=cols, n_blobs=blobs, pitch=pitch)
+    labels = np.full(rows * cols, -1, np.int32)
+    labels[np.random.default_rng(3).random(rows * cols) < 0.03] = -2  # masked cells are never seeds
+    cfg = dict(half_search_window=h, min_region_inliers=min_inl)
+    o_lab, o_r, _ = oracle.mean_shift(xyz, rows, cols, labels, cfg=oracle.default_cluster_config(**cfg),
+                                      iterations=4, id_offset=3, sort_mode=sort_mode)
+    g_lab, g_r = ctx.mean_shift(xyz, rows, cols, labels, cfg=cfg, iterations=4, id_offset=3, sort_mode=sort_mode)
+    _assert_ms_equal(g_lab, g_r, o_lab, o_r)
+
+
+def test_mean_shift_sharded_ranges_equal_full(ctx):
+    """Seed-cell shards (the multi-GPU path of C5) concatenate to the unsharded records, and
+    the growth phase on gathered records equals the one-call path."""
+    import parallel
+    rows, cols = 150, 211
+    xyz = synth.c5(rows=rows, cols=cols, n_blobs=30, pitch=0.08)
+    labels = np.full(rows * cols, -1, np.int32)
+    full = ctx.mean_shift_modes(xyz, rows, cols, labels, iterations=5)
+    for world in (2, 3, 8):
+        parts = [ctx.mean_shift_modes_range(xyz, rows, cols, labels, 5, b, e)
+                 for b, e in parallel.cell_ranges(rows * cols, world)]
+        assert np.array_equal(bits(np.concatenate(parts)), bits(full))
+    a_lab, a_r = ctx.mean_shift(xyz, rows, cols, labels, iterations=5)
+    b_lab, b_r = ctx.mean_shift_from_modes(xyz, rows, cols, full, labels)
+    _assert_ms_equal(b_lab, b_r, a_lab, a_r)
+    assert a_r.n >= 3
+
+
+def test_mean_shift_empty_and_all_labeled(ctx):
+    rows, cols = 20, 30
+    xyz = synth.c5(rows=rows, cols=cols, n_blobs=2, pitch=0.1)
+    labels = np.zeros(rows * cols, np.int32)  # nothing unlabeled: no seeds, no regions
+    g_lab, g_r = ctx.mean_shift(xyz, rows, cols, labels)
+    assert g_r.n == 0 and np.array_equal(g_lab, labels)
+
+
 def test_error_statuses(ctx):
     pts, seeds = synth.clustering_test_cloud()
     labels = np.full(100, -1, np.int32)

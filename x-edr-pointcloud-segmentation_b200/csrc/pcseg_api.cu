@@ -7,6 +7,7 @@
 #include "../../include/pcseg_b200.h"
 
 #include <algorithm>
+#include <climits>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -15,7 +16,7 @@
 
 #include "grow_cluster.cuh"
 #include "planar_kernel.cuh"
-#include "meanshift.cuh"
+#include "meanshift_grow.cuh"
 #include "normals.cuh"
 #include "seeds.cuh"
 
@@ -44,6 +45,10 @@ struct DevBuf {
     p = nullptr;
     bytes = 0;
   }
+  DevBuf() = default;
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+  ~DevBuf() { release(); }
   template <typename T>
   T* as() const { return static_cast<T*>(p); }
 };
@@ -730,12 +735,15 @@ int pcseg_seeds_plane_support(pcseg_ctx* c, const float* xyz, const float* norma
   return PCSEG_OK;
 }
 
-int pcseg_mean_shift_modes(pcseg_ctx* c, const float* xyz, int rows, int cols, const int* labels,
-                           int iterations, float* modes_out) {
+int pcseg_mean_shift_modes_range(pcseg_ctx* c, const float* xyz, int rows, int cols, const int* labels,
+                                 int iterations, int cell_begin, int cell_end, float* modes_out) {
   if (!c || !xyz || !labels || !modes_out) return PCSEG_ERR_NULL;  // CHECK_NE(labels, nullptr)
   if (rows <= 0 || cols <= 0) return PCSEG_ERR_DIMS;
-  cudaSetDevice(c->device);
   const size_t N = (size_t)rows * cols;
+  if (cell_begin < 0 || cell_end > (long long)N || cell_begin > cell_end) return PCSEG_ERR_DIMS;
+  const size_t M = (size_t)(cell_end - cell_begin);
+  if (M == 0) return PCSEG_OK;
+  cudaSetDevice(c->device);
   const void *xyz_dev, *lab_dev;
   int st;
   DevBuf sx, sl;  // transient staging (big clouds: not worth caching)
@@ -745,29 +753,163 @@ int pcseg_mean_shift_modes(pcseg_ctx* c, const float* xyz, int rows, int cols, c
   DevBuf so;
   ModeRecord* modes_dev = (ModeRecord*)modes_out;
   if (!out_dev) {
-    if (so.ensure(N * sizeof(ModeRecord)) != cudaSuccess) { sx.release(); sl.release(); return PCSEG_ERR_CUDA; }
+    if (so.ensure(M * sizeof(ModeRecord)) != cudaSuccess) { sx.release(); sl.release(); return PCSEG_ERR_CUDA; }
     modes_dev = so.as<ModeRecord>();
   }
   MeanShiftArgs a;
   a.xyz = (const float*)xyz_dev; a.labels = (const int*)lab_dev; a.rows = rows; a.cols = cols;
-  a.iterations = iterations; a.cell_begin = 0; a.cell_end = (int)N; a.modes = modes_dev;
-  meanshift_modes_kernel<<<(unsigned)((N + 255) / 256), 256, 0, c->stream>>>(a);
+  a.iterations = iterations; a.cell_begin = cell_begin; a.cell_end = cell_end; a.modes = modes_dev;
+  meanshift_modes_kernel<<<(unsigned)((M + 255) / 256), 256, 0, c->stream>>>(a);
   ++c->launches;
   cudaError_t e = cudaGetLastError();
   if (e == cudaSuccess && !out_dev)
-    e = cudaMemcpyAsync(modes_out, modes_dev, N * sizeof(ModeRecord), cudaMemcpyDeviceToHost, c->stream);
+    e = cudaMemcpyAsync(modes_out, modes_dev, M * sizeof(ModeRecord), cudaMemcpyDeviceToHost, c->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
   sx.release(); sl.release(); so.release();
   if (e != cudaSuccess) { c->last_error = cudaGetErrorString(e); return PCSEG_ERR_CUDA; }
   return PCSEG_OK;
 }
 
+int pcseg_mean_shift_modes(pcseg_ctx* c, const float* xyz, int rows, int cols, const int* labels,
+                           int iterations, float* modes_out) {
+  if (rows <= 0 || cols <= 0) return c ? PCSEG_ERR_DIMS : PCSEG_ERR_NULL;
+  return pcseg_mean_shift_modes_range(c, xyz, rows, cols, labels, iterations, 0, rows * cols, modes_out);
+}
+
+namespace {
+// Sort + growth phase on device-resident mode records (ps/mean_shift_segmentation.h:262-329).
+int mean_shift_finish(pcseg_ctx* c, const float* xyz_dev, int rows, int cols, const ModeRecord* modes_dev,
+                      const pcseg_cluster_config* cfg, int id_offset, int sort_mode, int* labels_dev,
+                      pcseg_regions** out) {
+  const size_t N = (size_t)rows * cols;
+  // (1) intensities of the valid seeds, in seed order (ascending cloud index, :219-229,267-274)
+  DevBuf d_int;
+  CU_TRY(c, d_int.ensure(N * sizeof(float)));
+  ms_intensity_kernel<<<(unsigned)((N + 255) / 256), 256, 0, c->stream>>>(modes_dev, (int)N, d_int.as<float>());
+  ++c->launches;
+  std::vector<float> h_int(N);
+  CU_TRY(c, cudaMemcpyAsync(h_int.data(), d_int.p, N * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  d_int.release();
+  // (2) the reference's own sort call on (intensity) keys, :276-280.  The permutation of an
+  // unstable sort depends only on the comparison outcomes, so sorting (cell, intensity) pairs
+  // with the same comparator reproduces the permutation of the reference's records (for the
+  // same standard library; quirk Q7).  sort_mode 1 = stable (documented patch P2).
+  std::vector<std::pair<int, double>> keys;
+  keys.reserve(N);
+  for (size_t i = 0; i < N; ++i)
+    if (h_int[i] >= 0.0f) keys.emplace_back((int)i, (double)h_int[i]);
+  auto cmp = [](const std::pair<int, double>& l, const std::pair<int, double>& r) { return l.second < r.second; };
+  if (sort_mode == 0) std::sort(keys.begin(), keys.end(), cmp);
+  else std::stable_sort(keys.begin(), keys.end(), cmp);
+  const int S = (int)keys.size();
+  pcseg_regions* res = new pcseg_regions();
+  *out = res;
+  if (S == 0) return PCSEG_OK;
+  std::vector<int> h_cells(S);
+  for (int i = 0; i < S; ++i) h_cells[i] = keys[i].first;
+  // (3) growth on the device
+  const int rcap = (int)std::min<size_t>(N / (size_t)std::max(cfg->min_region_inliers, 1) + 1, (size_t)1 << 22);
+  DevBuf d_cells, d_seeds, d_claim, d_inl, d_meta, d_out;
+  CU_TRY(c, d_cells.ensure((size_t)S * sizeof(int)));
+  CU_TRY(c, d_seeds.ensure((size_t)S * sizeof(MsSeedRec)));
+  CU_TRY(c, d_claim.ensure(N * sizeof(int)));
+  CU_TRY(c, d_inl.ensure(N * sizeof(int)));
+  CU_TRY(c, d_meta.ensure((size_t)rcap * sizeof(MsRegionMeta)));
+  CU_TRY(c, d_out.ensure(4 * sizeof(int)));
+  CU_TRY(c, cudaMemcpyAsync(d_cells.p, h_cells.data(), (size_t)S * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+  CU_TRY(c, cudaMemsetAsync(d_out.p, 0, 4 * sizeof(int), c->stream));
+  ms_gather_kernel<<<(unsigned)((S + 255) / 256), 256, 0, c->stream>>>(modes_dev, d_cells.as<int>(), S, rows,
+                                                                        d_seeds.as<MsSeedRec>());
+  fill_int_kernel<<<(unsigned)std::min<size_t>((N + 255) / 256, 65535), 256, 0, c->stream>>>(d_claim.as<int>(), N, INT_MAX);
+  MsGrowArgs g;
+  g.xyz = xyz_dev; g.labels = labels_dev; g.claim = d_claim.as<int>(); g.seeds = d_seeds.as<MsSeedRec>();
+  g.n_seeds = S; g.rows = rows; g.cols = cols; g.half_window = cfg->half_search_window;
+  g.min_inliers = cfg->min_region_inliers; g.id_offset = id_offset; g.inliers = d_inl.as<int>();
+  g.meta = d_meta.as<MsRegionMeta>(); g.rcap = rcap; g.out = d_out.as<int>();
+  ms_grow_kernel<<<1, kMsGrowBlock, 0, c->stream>>>(g);
+  c->launches += 3;
+  CU_TRY(c, cudaGetLastError());
+  int h_out[4];
+  CU_TRY(c, cudaMemcpyAsync(h_out, d_out.p, sizeof(h_out), cudaMemcpyDeviceToHost, c->stream));
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  const int R = h_out[0], total = h_out[2];
+  std::vector<MsRegionMeta> meta(R);
+  res->inlier_indices.resize(total);
+  if (R > 0) CU_TRY(c, cudaMemcpyAsync(meta.data(), d_meta.p, (size_t)R * sizeof(MsRegionMeta), cudaMemcpyDeviceToHost, c->stream));
+  if (total > 0) CU_TRY(c, cudaMemcpyAsync(res->inlier_indices.data(), d_inl.p, (size_t)total * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  for (int r = 0; r < R; ++r) {
+    res->inlier_offsets.push_back(meta[r].inlier_begin + meta[r].inlier_count);
+    res->label_ids.push_back(meta[r].label_id);
+    res->seed_points.insert(res->seed_points.end(), meta[r].seed, meta[r].seed + 3);
+  }
+  d_cells.release(); d_seeds.release(); d_claim.release(); d_inl.release(); d_meta.release(); d_out.release();
+  if (h_out[1]) { c->last_error = "mean-shift region table overflow"; return PCSEG_ERR_CAPACITY; }
+  return PCSEG_OK;
+}
+}  // namespace
+
+int pcseg_mean_shift_from_modes(pcseg_ctx* c, const float* xyz, int rows, int cols, const float* modes,
+                                const pcseg_cluster_config* cfg, int id_offset, int sort_mode, int* labels,
+                                pcseg_regions** out) {
+  if (!c || !xyz || !modes || !cfg || !labels || !out) return PCSEG_ERR_NULL;
+  if (rows <= 0 || cols <= 0) return PCSEG_ERR_DIMS;
+  int st = check_cluster_cfg(cfg);
+  if (st) return st;
+  cudaSetDevice(c->device);
+  const size_t N = (size_t)rows * cols;
+  DevBuf sx, sl, sm;
+  const void *xyz_dev, *modes_dev;
+  if ((st = to_device(c, xyz, N * 3 * sizeof(float), &sx, &xyz_dev))) return st;
+  if ((st = to_device(c, modes, N * sizeof(ModeRecord), &sm, &modes_dev))) { sx.release(); return st; }
+  int* lab_dev = labels;
+  if (!is_device_ptr(labels)) {
+    const void* tmp;
+    if ((st = to_device(c, labels, N * sizeof(int), &sl, &tmp))) { sx.release(); sm.release(); return st; }
+    lab_dev = (int*)sl.p;
+  }
+  st = mean_shift_finish(c, (const float*)xyz_dev, rows, cols, (const ModeRecord*)modes_dev, cfg, id_offset,
+                         sort_mode, lab_dev, out);
+  if (st == PCSEG_OK && lab_dev != labels) {
+    st = from_device(c, labels, lab_dev, N * sizeof(int));
+    if (st == PCSEG_OK && cudaStreamSynchronize(c->stream) != cudaSuccess) st = PCSEG_ERR_CUDA;
+  }
+  sx.release(); sl.release(); sm.release();
+  return st;
+}
+
 int pcseg_mean_shift(pcseg_ctx* c, const float* xyz, int rows, int cols, const pcseg_cluster_config* cfg,
                      int iterations, int id_offset, int sort_mode, int* labels, pcseg_regions** out) {
-  (void)xyz; (void)rows; (void)cols; (void)cfg; (void)iterations; (void)id_offset; (void)sort_mode;
-  if (!c || !labels || !out) return PCSEG_ERR_NULL;
-  c->last_error = "mean-shift sort+growth phase (SURVEY 8f-2) not built yet; use pcseg_mean_shift_modes";
-  return PCSEG_ERR_UNSUPPORTED;
+  if (!c || !xyz || !cfg || !labels || !out) return PCSEG_ERR_NULL;  // CHECK_NE(labels/regions, nullptr), :212-213
+  if (rows <= 0 || cols <= 0) return PCSEG_ERR_DIMS;
+  int st = check_cluster_cfg(cfg);
+  if (st) return st;
+  cudaSetDevice(c->device);
+  const size_t N = (size_t)rows * cols;
+  DevBuf sx, sl, sm;
+  const void* xyz_dev;
+  if ((st = to_device(c, xyz, N * 3 * sizeof(float), &sx, &xyz_dev))) return st;
+  int* lab_dev = labels;
+  if (!is_device_ptr(labels)) {
+    const void* tmp;
+    if ((st = to_device(c, labels, N * sizeof(int), &sl, &tmp))) { sx.release(); return st; }
+    lab_dev = (int*)sl.p;
+  }
+  if (sm.ensure(N * sizeof(ModeRecord)) != cudaSuccess) { sx.release(); sl.release(); return PCSEG_ERR_CUDA; }
+  MeanShiftArgs a;
+  a.xyz = (const float*)xyz_dev; a.labels = lab_dev; a.rows = rows; a.cols = cols;
+  a.iterations = iterations; a.cell_begin = 0; a.cell_end = (int)N; a.modes = sm.as<ModeRecord>();
+  meanshift_modes_kernel<<<(unsigned)((N + 255) / 256), 256, 0, c->stream>>>(a);
+  ++c->launches;
+  st = mean_shift_finish(c, (const float*)xyz_dev, rows, cols, sm.as<ModeRecord>(), cfg, id_offset, sort_mode,
+                         lab_dev, out);
+  if (st == PCSEG_OK && lab_dev != labels) {
+    st = from_device(c, labels, lab_dev, N * sizeof(int));
+    if (st == PCSEG_OK && cudaStreamSynchronize(c->stream) != cudaSuccess) st = PCSEG_ERR_CUDA;
+  }
+  sx.release(); sl.release(); sm.release();
+  return st;
 }
 
 // ---- batch pipeline --------------------------------------------------------

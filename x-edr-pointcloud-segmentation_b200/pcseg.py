@@ -59,7 +59,8 @@ EXPORTS = """pcseg_default_normals_params pcseg_default_planar_config
 pcseg_default_cluster_config pcseg_create pcseg_destroy pcseg_status_string
 pcseg_last_error pcseg_launch_count pcseg_stream pcseg_prepare_unlabeled_labels
 pcseg_normals_organized pcseg_segment_planar pcseg_segment_cluster
-pcseg_mean_shift_modes pcseg_mean_shift pcseg_seeds_plane_support
+pcseg_mean_shift_modes pcseg_mean_shift_modes_range pcseg_mean_shift_from_modes
+pcseg_mean_shift pcseg_seeds_plane_support
 pcseg_batch_create pcseg_batch_destroy pcseg_batch_run pcseg_batch_frame_stats
 pcseg_batch_regions pcseg_batch_stage_times pcseg_batch_profile pcseg_batch_device_labels pcseg_batch_device_normals
 pcseg_regions_count pcseg_regions_inlier_offsets pcseg_regions_inlier_indices
@@ -140,6 +141,8 @@ def _collect(L, handle, kind):
         r.disc_indices = arr("discontinuous_indices", int(r.disc_offsets[-1]), np.int32)
         r.hull_offsets = arr("hull_offsets", n + 1, np.int32)
         r.hull_points = arr("hull_points", 3 * int(r.hull_offsets[-1]), np.float32).reshape(-1, 3)
+    if kind == "meanshift":
+        r.seed_points = arr("seed_points", 3 * n, np.float32).reshape(n, 3)
     r.inliers = [r.inlier_indices[r.inlier_offsets[i]:r.inlier_offsets[i + 1]] for i in range(n)]
     return r
 
@@ -273,6 +276,39 @@ class Context:
         self._check(self.L.pcseg_mean_shift_modes(self.h, _addr(xyz), rows, cols,
                                                   _addr(labels), iterations, _addr(out)))
         return out.reshape(-1, 8)
+
+    def mean_shift_modes_range(self, xyz, rows, cols, labels, iterations, cell_begin, cell_end):
+        """Mode records of the seed cells [cell_begin, cell_end) (one shard)."""
+        xyz = _f32(xyz).reshape(-1)
+        labels = _i32(labels).reshape(-1)
+        out = np.zeros((cell_end - cell_begin) * 8, np.float32)
+        self._check(self.L.pcseg_mean_shift_modes_range(self.h, _addr(xyz), rows, cols, _addr(labels),
+                                                        iterations, cell_begin, cell_end, _addr(out)))
+        return out.reshape(-1, 8)
+
+    def mean_shift_from_modes(self, xyz, rows, cols, modes, labels, cfg=None, id_offset=0, sort_mode=0):
+        xyz = _f32(xyz).reshape(-1)
+        modes = _f32(modes).reshape(-1)
+        labels = _i32(labels).reshape(-1).copy()
+        c = cfg if isinstance(cfg, ClusterConfig) else cluster_config(**(cfg or {}))
+        h = C.c_void_p()
+        self._check(self.L.pcseg_mean_shift_from_modes(self.h, _addr(xyz), rows, cols, _addr(modes), C.byref(c),
+                                                       id_offset, sort_mode, _addr(labels), C.byref(h)))
+        r = _collect(self.L, h, "meanshift")
+        self.L.pcseg_regions_free(h)
+        return labels, r
+
+    def mean_shift(self, xyz, rows, cols, labels, cfg=None, iterations=5, id_offset=0, sort_mode=0):
+        """SlidingMeanShift (ps/mean_shift_segmentation.h:207-330): labels out, regions."""
+        xyz = _f32(xyz).reshape(-1)
+        labels = _i32(labels).reshape(-1).copy()
+        c = cfg if isinstance(cfg, ClusterConfig) else cluster_config(**(cfg or {}))
+        h = C.c_void_p()
+        self._check(self.L.pcseg_mean_shift(self.h, _addr(xyz), rows, cols, C.byref(c), iterations,
+                                            id_offset, sort_mode, _addr(labels), C.byref(h)))
+        r = _collect(self.L, h, "meanshift")
+        self.L.pcseg_regions_free(h)
+        return labels, r
 
     def seeds_plane_support(self, xyz, normals, rows, cols, neighborhood_size=9,
                             max_plane_distance=0.05, min_support=12):
