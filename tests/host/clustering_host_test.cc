@@ -1,0 +1,125 @@
+// C++ parity test through the host-side mirror (pcseg_host.h) of the reference API.
+// Reads like ps/clustering_test.cc:115-151 (known-answer test of
+// SegmentRegions<ClusterRegion>): 10x10 column-major cloud, seeds stored reversed so
+// that they are consumed in ascending index order, default config, id offset 1; then the
+// same scene through SegmentRegions<PlanarRegion> / ComputeNormalsOrganized /
+// SlidingMeanShift as smoke checks of the remaining entry points.
+#include <cmath>
+#include <cstdio>
+#include <vector>
+
+#include "pcseg_host.h"
+
+using mobility::b200::CloudRef;
+using mobility::b200::Float3;
+
+namespace {
+constexpr int kRows = 10, kCols = 10;
+
+// Scene of SURVEY.md Appendix C.1 (restated from the reference test's description).
+std::vector<Float3> PointCloudData() {
+  std::vector<Float3> p(kRows * kCols);
+  for (int c = 0; c < kCols; ++c) {
+    for (int r = 0; r < kRows; ++r) {
+      Float3 v;
+      if (c < 4) {
+        if (r < 4) v = {0.05f * c + 2, 0.05f * r + 2, 2};
+        else if (r > 4) v = {0.05f * c, 0.05f * r + 2, 0};
+        else v = {0.05f * c, 0.05f * r + 2, 1};
+      } else if (c == 4) {
+        v = {0.1f * c, 0, 0.1f * r};
+      } else if (r + c == 9 || r + c == 10) {
+        v = {0.05f * c + 5, -0.05f * r - 2, 2 - 0.05f * r};
+      } else if (r == 8 && c == 8) {
+        v = {0.05f * c + 2, -0.05f * r - 2, 4};
+      } else if ((r == 6 || r == 7) && c == 8) {
+        v = {6, 8, 2};
+      } else {
+        v = {0.05f * c + 2, -0.05f * r - 2, 2 - 0.05f * r};
+      }
+      p[c * kRows + r] = v;
+    }
+  }
+  return p;
+}
+
+const int kExpected[kRows][kCols] = {  // ps/clustering_test.cc:127-137, [row][col]
+    {1, 1, 1, 1, 3, 4, 4, 4, 4, 5},   {1, 1, 1, 1, 3, 4, 4, 4, 5, 5},   {1, 1, 1, 1, 3, 4, 4, 5, 5, 6},
+    {1, 1, 1, 1, 3, 4, 5, 5, 6, 6},   {-1, -1, -1, -1, 3, 5, 5, 6, 6, 6}, {2, 2, 2, 2, 3, 5, 6, 6, 6, 6},
+    {2, 2, 2, 2, 3, 6, 6, 6, -1, 6},  {2, 2, 2, 2, 3, 6, 6, 6, -1, 6},  {2, 2, 2, 2, 3, 6, 6, 6, -1, 6},
+    {2, 2, 2, 2, 3, 6, 6, 6, 6, 6}};
+
+int g_failures = 0;
+#define EXPECT(c)                                                   \
+  do {                                                              \
+    if (!(c)) {                                                     \
+      std::printf("FAILED %s:%d: %s\n", __FILE__, __LINE__, #c);    \
+      ++g_failures;                                                 \
+    }                                                               \
+  } while (0)
+}  // namespace
+
+int main() {
+  mobility::b200::Context ctx(0);
+  std::vector<Float3> data = PointCloudData();
+  CloudRef<Float3> points(data.data(), kRows, kCols);
+  std::vector<int> seeds(kRows * kCols);
+  for (int i = 0; i < kRows * kCols; ++i) seeds[kRows * kCols - 1 - i] = i;
+
+  // --- ps/clustering_test.cc:115-151 ---
+  std::vector<int> label_store = mobility::PrepareUnlabeledLabels(ctx, points);
+  CloudRef<int> labels(label_store.data(), kRows, kCols);
+  std::vector<mobility::ClusterRegion> regions;
+  mobility::SegmentRegions(ctx, points, seeds, mobility::ClusterRegionConfig(), &regions, &labels, 1);
+  for (int r = 0; r < kRows; ++r)
+    for (int c = 0; c < kCols; ++c) EXPECT(label_store[labels.LinearizeIndex(r, c)] == kExpected[r][c]);
+  const size_t sizes[] = {16, 20, 10, 10, 10, 27};
+  EXPECT(regions.size() == 6);
+  for (size_t i = 0; i < regions.size() && i < 6; ++i) {
+    EXPECT(regions[i].inlier_indices().size() == sizes[i]);
+    EXPECT(regions[i].label_id() == (int)i + 1);
+  }
+
+  // --- normals + planes on a tilted 64x64 plane with a step ---
+  const int R = 64, C = 64;
+  std::vector<Float3> plane(R * C), normals(R * C);
+  for (int c = 0; c < C; ++c)
+    for (int r = 0; r < R; ++r)
+      plane[c * R + r] = {0.03f * c, 0.03f * r, (c < 32 ? 2.0f : 2.6f) + 0.002f * r};
+  CloudRef<Float3> pc(plane.data(), R, C), nc(normals.data(), R, C);
+  const double sensor[3] = {0, 0, 0};
+  mobility::ComputeNormalsParams np;
+  np.min_neighbor_distance = 0.02f;
+  mobility::ComputeNormalsOrganized(ctx, sensor, pc, &nc, np);
+  int finite = 0;
+  for (const Float3& n : normals) finite += std::isfinite(n.x) ? 1 : 0;
+  EXPECT(finite > R * C / 2);
+  EXPECT(normals[10 * R + 10].z < -0.99f);  // oriented towards the sensor at the origin
+  std::vector<int> lab2 = mobility::PrepareUnlabeledLabels(ctx, pc);
+  CloudRef<int> labels2(lab2.data(), R, C);
+  std::vector<int> seeds2 = mobility::FindSeedPointsFromPlaneSupport(ctx, pc, nc);
+  EXPECT(!seeds2.empty());
+  std::vector<mobility::PlanarRegion> planes;
+  mobility::PlanarRegion::InputData<CloudRef<Float3>, CloudRef<Float3>> in{{0, 0, 0, 1}, pc, nc};
+  mobility::SegmentRegions(ctx, in, seeds2, mobility::PlanarRegionConfig(), &planes, &labels2, 0);
+  EXPECT(planes.size() == 2);
+  for (const auto& p : planes) {
+    EXPECT(p.inlier_indices().size() > 1500);
+    EXPECT(std::fabs(std::fabs(p.plane()[2]) - 1.0f) < 1e-2f);
+    EXPECT(p.area() > 1.0f);
+    EXPECT(!p.boundary_indices().empty());
+    EXPECT(p.projected_boundary_points().size() >= 3);
+  }
+
+  // --- SlidingMeanShift on the same sheet (labels reset) ---
+  std::vector<int> lab3 = mobility::PrepareUnlabeledLabels(ctx, pc);
+  CloudRef<int> labels3(lab3.data(), R, C);
+  std::vector<mobility::ClusterRegion> ms;
+  mobility::SlidingMeanShift(ctx, pc, mobility::ClusterRegionConfig(), 3, 0, &labels3, &ms);
+  EXPECT(!ms.empty());
+  for (const auto& m : ms) EXPECT(m.Seed().has_value() && m.inlier_indices().size() >= 7);
+
+  if (g_failures == 0) std::printf("PASS clustering_host_test: %zu clusters, %zu planes, %zu mean-shift regions\n",
+                                   regions.size(), planes.size(), ms.size());
+  return g_failures == 0 ? 0 : 1;
+}

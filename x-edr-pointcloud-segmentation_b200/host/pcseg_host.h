@@ -83,6 +83,8 @@ inline const float* XyzData(const CloudT& c) {
 
 }  // namespace b200
 
+struct RegionAccess;
+
 // ps/algorithms.h:313-322
 struct ComputeNormalsParams {
   float min_neighbor_distance = 0.1f;
@@ -143,9 +145,6 @@ class PlanarRegion {
   const std::vector<b200::Float3>& projected_boundary_points() const { return hull_; }
 
  private:
-  template <typename R, typename I, typename C>
-  friend void SegmentRegions(b200::Context&, const I&, const std::vector<int>&, const C&, std::vector<R>*,
-                             b200::CloudRef<int>, int);
   friend struct RegionAccess;
   int label_id_ = 0, seed_point_index_ = 0;
   b200::Float3 centroid_{0, 0, 0};
@@ -176,3 +175,161 @@ class ClusterRegion {
   std::vector<int> inlier_indices_;
   std::optional<b200::Float3> seed_;
 };
+
+// Fills the region objects from a C-ABI result handle.
+struct RegionAccess {
+  static void Fill(const pcseg_regions* r, std::vector<PlanarRegion>* out) {
+    const int n = pcseg_regions_count(r);
+    const int* io = pcseg_regions_inlier_offsets(r);
+    const int* ii = pcseg_regions_inlier_indices(r);
+    const int* bo = pcseg_regions_boundary_offsets(r);
+    const int* bi = pcseg_regions_boundary_indices(r);
+    const int* dof = pcseg_regions_discontinuous_offsets(r);
+    const int* di = pcseg_regions_discontinuous_indices(r);
+    const int* ho = pcseg_regions_hull_offsets(r);
+    const float* hp = pcseg_regions_hull_points(r);
+    out->clear();  // regions->clear(), ps/segmentation.h:248
+    out->resize(n);
+    for (int k = 0; k < n; ++k) {
+      PlanarRegion& p = (*out)[k];
+      p.label_id_ = pcseg_regions_label_ids(r)[k];
+      p.seed_point_index_ = pcseg_regions_seed_indices(r)[k];
+      const float* c = pcseg_regions_centroids(r) + 3 * k;
+      p.centroid_ = {c[0], c[1], c[2]};
+      for (int j = 0; j < 4; ++j) p.plane_[j] = pcseg_regions_planes(r)[4 * k + j];
+      for (int j = 0; j < 10; ++j) p.estimator_[j] = pcseg_regions_estimators(r)[10 * k + j];
+      p.area_ = pcseg_regions_areas(r)[k];
+      p.inlier_indices_.assign(ii + io[k], ii + io[k + 1]);
+      p.boundary_indices_.assign(bi + bo[k], bi + bo[k + 1]);
+      p.discontinuous_.assign(di + dof[k], di + dof[k + 1]);
+      for (int j = ho[k]; j < ho[k + 1]; ++j) p.hull_.push_back({hp[3 * j], hp[3 * j + 1], hp[3 * j + 2]});
+    }
+  }
+  static void Fill(const pcseg_regions* r, std::vector<ClusterRegion>* out, bool with_seed) {
+    const int n = pcseg_regions_count(r);
+    const int* io = pcseg_regions_inlier_offsets(r);
+    const int* ii = pcseg_regions_inlier_indices(r);
+    out->clear();
+    out->resize(n);
+    for (int k = 0; k < n; ++k) {
+      ClusterRegion& c = (*out)[k];
+      c.label_id_ = pcseg_regions_label_ids(r)[k];
+      c.inlier_indices_.assign(ii + io[k], ii + io[k + 1]);
+      if (with_seed) {
+        const float* s = pcseg_regions_seed_points(r) + 3 * k;
+        c.seed_ = b200::Float3{s[0], s[1], s[2]};
+      }
+    }
+  }
+};
+
+// ps/algorithms.h:329-375 (both overloads).  Only the translation of
+// point_cloud_pose_sensor is read by the reference (:355).
+template <typename PointsT, typename NormalsT>
+void ComputeNormalsOrganized(b200::Context& ctx, const double sensor_translation[3], const PointsT& points,
+                             NormalsT* normals, const std::pair<int, int>& row_range,
+                             const std::pair<int, int>& col_range,
+                             const ComputeNormalsParams& params = ComputeNormalsParams()) {
+  pcseg_normals_params p{params.min_neighbor_distance, params.max_neighbor_distance,
+                         params.include_diagonal_neighbors ? 1 : 0, params.min_num_support_neighbors};
+  b200::CheckOk(ctx.get(),
+                pcseg_normals_organized(ctx.get(), b200::XyzData(points), points.Rows(), points.Cols(),
+                                        sensor_translation, &p, row_range.first, row_range.second,
+                                        col_range.first, col_range.second,
+                                        const_cast<float*>(b200::XyzData(*normals)), nullptr),
+                "ComputeNormalsOrganized");
+}
+template <typename PointsT, typename NormalsT>
+void ComputeNormalsOrganized(b200::Context& ctx, const double sensor_translation[3], const PointsT& points,
+                             NormalsT* normals, const ComputeNormalsParams& params = ComputeNormalsParams()) {
+  ComputeNormalsOrganized(ctx, sensor_translation, points, normals, {0, points.Rows()}, {0, points.Cols()}, params);
+}
+
+// ps/segmentation.cc:21-26
+template <typename PointsT>
+std::vector<int> PrepareUnlabeledLabels(b200::Context& ctx, const PointsT& point_cloud) {
+  std::vector<int> labels(static_cast<size_t>(point_cloud.Rows()) * point_cloud.Cols());
+  b200::CheckOk(ctx.get(), pcseg_prepare_unlabeled_labels(ctx.get(), labels.data(), (int)labels.size()),
+                "PrepareUnlabeledLabels");
+  return labels;
+}
+
+// ps/segmentation.h:190-230
+template <typename PointsT, typename NormalsT>
+std::vector<int> FindSeedPointsFromPlaneSupport(b200::Context& ctx, const PointsT& points, const NormalsT& normals,
+                                                int neighborhood_size = 9, float max_plane_distance = 0.05f,
+                                                int min_num_support_points = 12) {
+  if (points.Cols() != normals.Cols() || points.Rows() != normals.Rows()) b200::CheckOk(ctx.get(), PCSEG_ERR_DIMS, "FindSeedPointsFromPlaneSupport");
+  std::vector<int> seeds(static_cast<size_t>(points.Rows()) * points.Cols());
+  int n = 0;
+  b200::CheckOk(ctx.get(),
+                pcseg_seeds_plane_support(ctx.get(), b200::XyzData(points), b200::XyzData(normals), points.Rows(),
+                                          points.Cols(), neighborhood_size, max_plane_distance,
+                                          min_num_support_points, seeds.data(), (int)seeds.size(), &n),
+                "FindSeedPointsFromPlaneSupport");
+  seeds.resize(n);
+  return seeds;
+}
+
+// ps/segmentation.h:239-292 with RegionT = PlanarRegion<>.  labels: Cloud<int>-like, in/out.
+template <typename PointsT, typename NormalsT, typename LabelsT>
+void SegmentRegions(b200::Context& ctx, const PlanarRegion::InputData<PointsT, NormalsT>& input,
+                    const std::vector<int>& seed_point_indices, const PlanarRegionConfig& region_config,
+                    std::vector<PlanarRegion>* regions, LabelsT* labels, int initial_id_offset = 0) {
+  if (!regions || !labels) b200::CheckOk(ctx.get(), PCSEG_ERR_NULL, "SegmentRegions<PlanarRegion>");  // CHECK(regions)
+  // CheckInputDataAndLabels, ps/planar_region.h:257-268
+  if (input.points.Cols() != input.normals.Cols() || input.points.Rows() != input.normals.Rows() ||
+      input.points.Cols() != labels->Cols() || input.points.Rows() != labels->Rows())
+    b200::CheckOk(ctx.get(), PCSEG_ERR_DIMS, "SegmentRegions<PlanarRegion>");
+  const pcseg_planar_config cfg = PlanarRegion::ApplyDefaultConfigValues(region_config);
+  pcseg_regions* r = nullptr;
+  b200::CheckOk(ctx.get(),
+                pcseg_segment_planar(ctx.get(), b200::XyzData(input.points), b200::XyzData(input.normals),
+                                     input.points.Rows(), input.points.Cols(), input.robot_q_xyzw,
+                                     seed_point_indices.data(), (int)seed_point_indices.size(), &cfg,
+                                     initial_id_offset, labels->Data(), &r),
+                "SegmentRegions<PlanarRegion>");
+  RegionAccess::Fill(r, regions);
+  pcseg_regions_free(r);
+}
+
+// ps/segmentation.h:239-292 with RegionT = ClusterRegion<> (InputData = the point cloud).
+template <typename PointsT, typename LabelsT>
+void SegmentRegions(b200::Context& ctx, const PointsT& points, const std::vector<int>& seed_point_indices,
+                    const ClusterRegionConfig& region_config, std::vector<ClusterRegion>* regions, LabelsT* labels,
+                    int initial_id_offset = 0) {
+  if (!regions || !labels) b200::CheckOk(ctx.get(), PCSEG_ERR_NULL, "SegmentRegions<ClusterRegion>");
+  if (points.Cols() != labels->Cols() || points.Rows() != labels->Rows())  // ps/cluster_region.h:152-159
+    b200::CheckOk(ctx.get(), PCSEG_ERR_DIMS, "SegmentRegions<ClusterRegion>");
+  const pcseg_cluster_config cfg = ClusterRegion::ApplyDefaultConfigValues(region_config);
+  pcseg_regions* r = nullptr;
+  b200::CheckOk(ctx.get(),
+                pcseg_segment_cluster(ctx.get(), b200::XyzData(points), points.Rows(), points.Cols(),
+                                      seed_point_indices.data(), (int)seed_point_indices.size(), &cfg,
+                                      initial_id_offset, labels->Data(), &r),
+                "SegmentRegions<ClusterRegion>");
+  RegionAccess::Fill(r, regions, false);
+  pcseg_regions_free(r);
+}
+
+// ps/mean_shift_segmentation.h:207-211.  The sort of :276-280 is std::sort of this toolchain's
+// standard library, as in the reference (quirk Q7).
+template <typename PointsT, typename LabelsT>
+void SlidingMeanShift(b200::Context& ctx, const PointsT& point_cloud, const ClusterRegionConfig& config,
+                      int iterations, int initial_region_id_offset, LabelsT* labels,
+                      std::vector<ClusterRegion>* regions) {
+  if (!regions || !labels) b200::CheckOk(ctx.get(), PCSEG_ERR_NULL, "SlidingMeanShift");  // CHECK_NE(.., nullptr)
+  if (point_cloud.Cols() != labels->Cols() || point_cloud.Rows() != labels->Rows())
+    b200::CheckOk(ctx.get(), PCSEG_ERR_DIMS, "SlidingMeanShift");
+  const pcseg_cluster_config cfg = ClusterRegion::ApplyDefaultConfigValues(config);
+  pcseg_regions* r = nullptr;
+  b200::CheckOk(ctx.get(),
+                pcseg_mean_shift(ctx.get(), b200::XyzData(point_cloud), point_cloud.Rows(), point_cloud.Cols(), &cfg,
+                                 iterations, initial_region_id_offset, 0, labels->Data(), &r),
+                "SlidingMeanShift");
+  RegionAccess::Fill(r, regions, true);
+  pcseg_regions_free(r);
+}
+
+}  // namespace mobility
+#endif  // PCSEG_B200_HOST_H_
