@@ -285,16 +285,20 @@ def main():
     stage_ms = {k: v / args.steps for k, v in stage_acc.items()}
     peak, peak_kind = measured_peak_gbs()
     dom = max(("planar", "normals", "cluster"), key=lambda k: stage_ms[k])
+    fused = stage_ms["cluster"] < 0.05   # cluster stage runs inside planar_grow_kernel (per-frame fusion)
     alg_bytes = {"normals": 24.0 * F * N_PTS,            # 12 B read + 12 B write per point
                  "planar": 24.0 * F * N_PTS,             # point + label rd/wr + inlier index per point entering
                  "cluster": 24.0 * float((F * N_PTS) - int(stats[:, 2].sum()))}
+    if fused:
+        alg_bytes["planar"] += alg_bytes["cluster"]
     roof = {}
-    for k in ("normals", "planar", "cluster"):
+    for k in ("normals", "planar") if fused else ("normals", "planar", "cluster"):
         ach = alg_bytes[k] / (stage_ms[k] * 1e-3) / 1e9 if stage_ms[k] > 0 else 0.0
         roof[k] = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                    "traffic": None, "kernel_ms": stage_ms[k], "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)"}
     roofline = dict(roof[dom])
-    roofline["kernel"] = {"planar": "planar_grow_kernel", "normals": "normals_kernel", "cluster": "cluster_grow_kernel"}[dom]
+    roofline["kernel"] = {"planar": "planar_grow_kernel" + (" (planar + fused cluster growth)" if fused else ""),
+                          "normals": "normals_kernel", "cluster": "cluster_grow_kernel"}[dom]
     roofline["note"] = ("latency-bound serial FIFO chain (one re-fit per 30 inliers), not bandwidth-bound; "
                         "see DESIGN.md and profiles/")
 

@@ -33,9 +33,12 @@ struct ClusterArgs {
   FrameStats* stats;  // [F]
 };
 
+// All cluster regions of frame f, grown by the calling CTA (every thread of the
+// CTA must call).  Used by cluster_grow_kernel and, fused behind a frame's planar
+// stage, by planar_grow_kernel (a frame's stages are sequential, different
+// frames are independent: fusing removes the batch-wide barrier between them).
 template <int BLOCK>
-__global__ void __launch_bounds__(BLOCK) cluster_grow_kernel(ClusterArgs a) {
-  const int f = blockIdx.x;
+__device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, int id_offset, int* s_warp) {
   const int tid = threadIdx.x;
   const int rows = a.rows, cols = a.cols;
   const int N = rows * cols;
@@ -46,11 +49,8 @@ __global__ void __launch_bounds__(BLOCK) cluster_grow_kernel(ClusterArgs a) {
   volatile int* vclaim = claim;
   int* inliers = a.inliers + (size_t)f * N;
   ClusterMeta* meta = a.meta + (size_t)f * a.rcap;
-  const int id_offset = a.id_offset_from_planar ? a.stats[f].n_planar : a.id_offset;
   const int h = a.half_window;
   const int side = 2 * h + 1;
-
-  __shared__ int s_warp[BLOCK / 32 + 1];
 
   int seed_pos = a.n_seeds;  // seeds are consumed back to front
   int nreg = 0, inl_total = 0, err = 0, steps = 0;
@@ -114,24 +114,51 @@ __global__ void __launch_bounds__(BLOCK) cluster_grow_kernel(ClusterArgs a) {
         }
       }
       __syncthreads();
-      // AddNeighbors, ps/cluster_region.h:122-150: delta_col outer, delta_row inner
+      // AddNeighbors, ps/cluster_region.h:122-150: delta_col outer, delta_row inner.
+      // All label probes of an entry are issued before the first one is used (one memory
+      // round trip instead of one per neighbour); same for the claim read-back below.
       unsigned long long el = 0ull;
       const int row = cand % rows, col = cand / rows;
       if (acc) {
-        int s = 0;
-        for (int dc = -h; dc <= h; ++dc) {
-          for (int dr = -h; dr <= h; ++dr) {
-            if (dc == 0 && dr == 0) continue;
-            const int cc = col + dc, rc = row + dr;
-            if (cc >= 0 && cc < cols && rc >= 0 && rc < rows) {
-              const int n = cc * rows + rc;
-              const int L = labels[n];
-              if (L == kUnlabeled || (L <= kRejBase && (kRejBase - L) < tid)) {
-                el |= 1ull << s;
-                atomicMin(claim + n, tid * 64 + s);
+        if (h == 1) {
+          int L[8], nn[8];
+#pragma unroll
+          for (int s = 0; s < 8; ++s) {
+            const int cell = s + (s >= 4 ? 1 : 0);
+            const int cc = col + cell / 3 - 1, rc = row + cell % 3 - 1;
+            const bool in = cc >= 0 && cc < cols && rc >= 0 && rc < rows;
+            nn[s] = in ? cc * rows + rc : -1;
+            L[s] = in ? labels[nn[s]] : 0;
+          }
+#pragma unroll
+          for (int s = 0; s < 8; ++s) {
+            if (nn[s] >= 0 && (L[s] == kUnlabeled || (L[s] <= kRejBase && (kRejBase - L[s]) < tid))) {
+              el |= 1ull << s;
+              atomicMin(claim + nn[s], tid * 64 + s);
+            }
+          }
+        } else {
+          int s = 0;
+          for (int dc = -h; dc <= h; ++dc) {
+            int L[7];
+#pragma unroll
+            for (int j = 0; j < 7; ++j) {
+              const int dr = j - h;
+              const int cc = col + dc, rc = row + dr;
+              const bool in = j < side && !(dc == 0 && dr == 0) && cc >= 0 && cc < cols && rc >= 0 && rc < rows;
+              L[j] = in ? labels[cc * rows + rc] : 0;
+            }
+#pragma unroll
+            for (int j = 0; j < 7; ++j) {
+              const int dr = j - h;
+              if (j < side && !(dc == 0 && dr == 0)) {
+                if (L[j] == kUnlabeled || (L[j] <= kRejBase && (kRejBase - L[j]) < tid)) {
+                  el |= 1ull << s;
+                  atomicMin(claim + (col + dc) * rows + (row + dr), tid * 64 + s);
+                }
+                ++s;
               }
             }
-            ++s;
           }
         }
       }
@@ -139,14 +166,27 @@ __global__ void __launch_bounds__(BLOCK) cluster_grow_kernel(ClusterArgs a) {
       if (mine && !acc) labels[cand] = kUnlabeled;  // ps/cluster_region.h:105
       unsigned long long win = 0ull;
       if (acc) {
-        unsigned long long e = el;
-        while (e) {
-          const int s = __ffsll((long long)e) - 1;
-          e &= e - 1;
-          const int cell = s + (s >= (side * side) / 2 ? 1 : 0);  // skip the centre
-          const int dc = cell / side - h, dr = cell % side - h;
-          const int n = (col + dc) * rows + (row + dr);
-          if (vclaim[n] == tid * 64 + s) win |= 1ull << s;
+        if (h == 1) {
+          int cv[8];
+#pragma unroll
+          for (int s = 0; s < 8; ++s) {
+            const int cell = s + (s >= 4 ? 1 : 0);
+            const int n = (col + cell / 3 - 1) * rows + (row + cell % 3 - 1);
+            cv[s] = ((el >> s) & 1ull) ? vclaim[n] : -1;
+          }
+#pragma unroll
+          for (int s = 0; s < 8; ++s)
+            if (cv[s] == tid * 64 + s) win |= 1ull << s;
+        } else {
+          unsigned long long e = el;
+          while (e) {
+            const int s = __ffsll((long long)e) - 1;
+            e &= e - 1;
+            const int cell = s + (s >= (side * side) / 2 ? 1 : 0);  // skip the centre
+            const int dc = cell / side - h, dr = cell % side - h;
+            const int n = (col + dc) * rows + (row + dr);
+            if (vclaim[n] == tid * 64 + s) win |= 1ull << s;
+          }
         }
       }
       int nwin;
@@ -199,6 +239,13 @@ __global__ void __launch_bounds__(BLOCK) cluster_grow_kernel(ClusterArgs a) {
     a.stats[f].error_flags |= err;
     a.stats[f].grow_steps += steps;
   }
+}
+
+template <int BLOCK>
+__global__ void __launch_bounds__(BLOCK) cluster_grow_kernel(ClusterArgs a) {
+  __shared__ int s_warp[BLOCK / 32 + 1];
+  const int f = blockIdx.x;
+  cluster_grow_frame<BLOCK>(a, f, a.id_offset_from_planar ? a.stats[f].n_planar : a.id_offset, s_warp);
 }
 
 }  // namespace pcseg

@@ -33,7 +33,7 @@ struct PlanarArgs {
   float disc_min_range, disc_max_range, disc_angle, disc_z_diff, disc_z_ratio;
   float qx, qy, qz, qw;
   int id_offset;
-  int* queue;            // [F][qcap]
+  int* queue;            // [F][2*qcap] (first qcap ints used; stride shared with the cluster stage)
   int qcap;
   int* claim;            // [F][N]
   int* inliers;          // [F][N]

@@ -43,7 +43,41 @@ __device__ __forceinline__ bool in_range(V3 c, V3 p, float min2, float max2) {
   return d2 >= min2 && d2 <= max2;
 }
 
+// One axis walk of FindNormalSupportNeighbors (ps/algorithms.h:137-205): the first k in
+// [0, count) whose point q[k * stride3 .. +2] is finite with min2 <= |c - p|^2 <= max2,
+// or -1.  The walk dominates the kernel (about 25 steps per direction at the default
+// min_neighbor_distance on a 640x480 depth frame), so it is written for instruction count
+// and memory-level parallelism: four candidates are loaded and evaluated per trip (the loads
+// of a trip do not depend on each other) and the first eligible one is taken, which is
+// exactly the reference's sequential first match.
+// CHK = false drops the explicit allFinite() test: a non-finite candidate gives d2 = NaN or
+// +Inf, which fails `d2 >= min2 && d2 <= max2` whenever max2 is finite (the caller
+// instantiates CHK = true otherwise), so the outcome is identical.
+template <bool CHK>
+__device__ __forceinline__ bool walk_hit(const float* __restrict__ q, V3 c, float min2, float max2) {
+  const V3 p{__ldg(q), __ldg(q + 1), __ldg(q + 2)};
+  if (CHK && !vfinite(p)) return false;
+  const float d2 = vsqn(vsub(c, p));
+  return d2 >= min2 && d2 <= max2;
+}
+template <bool CHK>
+__device__ __forceinline__ int walk_first(const float* __restrict__ q, long stride3, int count, V3 c,
+                                          float min2, float max2) {
+  int k = 0;
+  for (; k + 4 <= count; k += 4, q += 4 * stride3) {
+    const bool e0 = walk_hit<CHK>(q, c, min2, max2);
+    const bool e1 = walk_hit<CHK>(q + stride3, c, min2, max2);
+    const bool e2 = walk_hit<CHK>(q + 2 * stride3, c, min2, max2);
+    const bool e3 = walk_hit<CHK>(q + 3 * stride3, c, min2, max2);
+    if (e0 | e1 | e2 | e3) return k + (e0 ? 0 : e1 ? 1 : e2 ? 2 : 3);
+  }
+  for (; k < count; ++k, q += stride3)
+    if (walk_hit<CHK>(q, c, min2, max2)) return k;
+  return -1;
+}
+
 // Returns the number of support indices (centre included), fills idx[<=9].
+template <bool CHK>
 __device__ __forceinline__ int find_support(const float* __restrict__ xyz, int rows, int cols,
                                             int row, int col, V3 center, float min2, float max2,
                                             bool diag, int idx[9]) {
@@ -53,34 +87,27 @@ __device__ __forceinline__ int find_support(const float* __restrict__ xyz, int r
   int min_col = max(col - 1, 0);
   int max_col = min(col + 1, cols - 1);
   const int ci = col * rows + row;
+  const float* qc = xyz + 3 * (size_t)ci;
   idx[n++] = ci;
   // upper neighbour: index -= 1
   {
-    int index = ci - 1;
-    for (int r = row - 1; r >= 0; --r, --index) {
-      if (in_range(center, ld3(xyz, index), min2, max2)) { idx[n++] = index; min_row = r; break; }
-    }
+    const int k = walk_first<CHK>(qc - 3, -3, row, center, min2, max2);
+    if (k >= 0) { idx[n++] = ci - 1 - k; min_row = row - 1 - k; }
   }
   // left neighbour: index -= rows
   {
-    int index = ci - rows;
-    for (int c = col - 1; c >= 0; --c, index -= rows) {
-      if (in_range(center, ld3(xyz, index), min2, max2)) { idx[n++] = index; min_col = c; break; }
-    }
+    const int k = walk_first<CHK>(qc - 3 * (long)rows, -3 * (long)rows, col, center, min2, max2);
+    if (k >= 0) { idx[n++] = ci - (1 + k) * rows; min_col = col - 1 - k; }
   }
   // lower neighbour
   {
-    int index = ci + 1;
-    for (int r = row + 1; r < rows; ++r, ++index) {
-      if (in_range(center, ld3(xyz, index), min2, max2)) { idx[n++] = index; max_row = r; break; }
-    }
+    const int k = walk_first<CHK>(qc + 3, 3, rows - 1 - row, center, min2, max2);
+    if (k >= 0) { idx[n++] = ci + 1 + k; max_row = row + 1 + k; }
   }
   // right neighbour
   {
-    int index = ci + rows;
-    for (int c = col + 1; c < cols; ++c, index += rows) {
-      if (in_range(center, ld3(xyz, index), min2, max2)) { idx[n++] = index; max_col = c; break; }
-    }
+    const int k = walk_first<CHK>(qc + 3 * (long)rows, 3 * (long)rows, cols - 1 - col, center, min2, max2);
+    if (k >= 0) { idx[n++] = ci + (1 + k) * rows; max_col = col + 1 + k; }
   }
   if (!diag) return n;
   if (min_col != col) {
@@ -102,6 +129,7 @@ __device__ __forceinline__ void store_nan3(float* normals, float* curvature, int
   if (curvature) curvature[i] = kNaN;
 }
 
+template <bool CHK>
 __global__ void __launch_bounds__(256) normals_kernel(NormalsArgs a) {
   const int nr = a.r1 - a.r0;
   const int nc = a.c1 - a.c0;
@@ -119,7 +147,7 @@ __global__ void __launch_bounds__(256) normals_kernel(NormalsArgs a) {
   int idx[9];
   int n = 0;
   if (vfinite(point))
-    n = find_support(xyz, a.rows, a.cols, row, col, point, a.min2, a.max2, a.diag != 0, idx);
+    n = find_support<CHK>(xyz, a.rows, a.cols, row, col, point, a.min2, a.max2, a.diag != 0, idx);
   if (n == 0 || n < a.min_support) {
     store_nan3(normals, curvature, ci);
     return;
@@ -162,7 +190,7 @@ __device__ int normals_chain(const NormalsArgs& a, const float* xyz, float* norm
       int idx[9];
       int n = 0;
       if (vfinite(point))
-        n = find_support(xyz, a.rows, a.cols, row, col, point, a.min2, a.max2, a.diag != 0, idx);
+        n = find_support<true>(xyz, a.rows, a.cols, row, col, point, a.min2, a.max2, a.diag != 0, idx);
       if (n == 0 || n < a.min_support) {
         store_nan3(normals, curvature, ci);
         continue;

@@ -62,6 +62,10 @@ struct pcseg_ctx {
   long long launches = 0;
   pcseg_batch* scratch = nullptr;  // cached single-frame workspace
   DevBuf tmp_a, tmp_b;
+  // host<->device copies of the batched pipeline run on their own streams so that they
+  // overlap the kernels (chunked H2D under the normals stage, normals D2H under growth)
+  cudaStream_t copy_in = nullptr, copy_out = nullptr;
+  std::vector<cudaEvent_t> chunk_ev;  // 2 per chunk: H2D done, normals done
 };
 
 struct pcseg_regions {
@@ -197,38 +201,66 @@ int batch_alloc(pcseg_batch* b) {
 // ===========================================================================
 namespace {
 
+// Frames [f0, f0 + nf) of the batch (nf < 0: all of them).
 int run_normals(pcseg_batch* b, const float* xyz_dev, float* normals_dev, float* curvature_dev,
-                const pcseg_normals_params* p, const double sensor_t[3], int r0, int r1, int c0, int c1) {
+                const pcseg_normals_params* p, const double sensor_t[3], int r0, int r1, int c0, int c1,
+                int f0 = 0, int nf = -1) {
   pcseg_ctx* c = b->ctx;
   if (r1 <= r0 || c1 <= c0) return PCSEG_OK;
+  if (nf < 0) nf = b->n_frames - f0;
+  if (nf <= 0) return PCSEG_OK;
   NormalsArgs a;
-  a.xyz = xyz_dev;
-  a.normals = normals_dev;
-  a.curvature = curvature_dev;
-  a.rows = b->rows; a.cols = b->cols; a.n_frames = b->n_frames;
+  a.xyz = xyz_dev + (size_t)f0 * b->N * 3;
+  a.normals = normals_dev + (size_t)f0 * b->N * 3;
+  a.curvature = curvature_dev ? curvature_dev + (size_t)f0 * b->N : nullptr;
+  a.rows = b->rows; a.cols = b->cols; a.n_frames = nf;
   a.r0 = r0; a.r1 = r1; a.c0 = c0; a.c1 = c1;
   a.min2 = p->min_neighbor_distance * p->min_neighbor_distance;  // ps/algorithms.h:111-114
   a.max2 = p->max_neighbor_distance * p->max_neighbor_distance;
   a.diag = p->include_diagonal_neighbors;
   a.min_support = p->min_num_support_neighbors;
   a.sx = (float)sensor_t[0]; a.sy = (float)sensor_t[1]; a.sz = (float)sensor_t[2];
-  a.inv_list = b->inv_list.as<int>();
-  a.inv_count = b->inv_count.as<int>();
+  a.inv_list = b->inv_list.as<int>() + (size_t)f0 * kInvCap;
+  a.inv_count = b->inv_count.as<int>() + f0;
   a.inv_cap = kInvCap;
-  CU_TRY(c, cudaMemsetAsync(a.inv_count, 0, b->n_frames * sizeof(int), c->stream));
+  CU_TRY(c, cudaMemsetAsync(a.inv_count, 0, nf * sizeof(int), c->stream));
   const int work = (r1 - r0) * (c1 - c0);
-  dim3 grid((work + 255) / 256, b->n_frames);
-  normals_kernel<<<grid, 256, 0, c->stream>>>(a);
-  normals_fixup_kernel<<<b->n_frames, 256, 0, c->stream>>>(a);
+  dim3 grid((work + 255) / 256, nf);
+  if (a.max2 <= FLT_MAX) normals_kernel<false><<<grid, 256, 0, c->stream>>>(a);
+  else normals_kernel<true><<<grid, 256, 0, c->stream>>>(a);  // max distance inf/NaN: explicit allFinite() test
+  normals_fixup_kernel<<<nf, 256, 0, c->stream>>>(a);
   c->launches += 2;
   CU_TRY(c, cudaGetLastError());
   return PCSEG_OK;
 }
 
+int make_cluster_args(pcseg_batch* b, const float* xyz_dev, const int* seeds_dev, int n_seeds,
+                      const pcseg_cluster_config* cfg, int id_offset, int offset_from_planar, ClusterArgs* out) {
+  pcseg_ctx* c = b->ctx;
+  b->rcap_cluster = (int)(b->N / (size_t)cfg->min_region_inliers) + 1;
+  CU_TRY(c, b->meta_cluster.ensure((size_t)b->n_frames * b->rcap_cluster * sizeof(ClusterMeta)));
+  ClusterArgs a;
+  a.xyz = xyz_dev; a.labels = b->labels.as<int>();
+  a.rows = b->rows; a.cols = b->cols;
+  a.seeds = seeds_dev; a.n_seeds = seeds_dev ? n_seeds : (int)b->N;
+  a.min_inliers = cfg->min_region_inliers; a.sq_thr = cfg->squared_distance_threshold;
+  a.half_window = cfg->half_search_window;
+  a.id_offset = id_offset; a.id_offset_from_planar = offset_from_planar;
+  a.queue = b->queue.as<int>(); a.qcap = b->qcap;
+  a.claim = b->claim.as<int>(); a.inliers = b->inl_cluster.as<int>();
+  a.meta = b->meta_cluster.as<ClusterMeta>(); a.rcap = b->rcap_cluster;
+  a.stats = b->stats.as<FrameStats>();
+  *out = a;
+  return PCSEG_OK;
+}
+
+// fuse_cluster (nullable): cluster stage to run behind each frame's planar stage in the same
+// CTA; *fused tells the caller whether that happened (shared-memory fast path only).
 int run_planar(pcseg_batch* b, const float* xyz_dev, const float* normals_dev, const int* seeds_dev,
                int n_seeds, int seeds_stride, const int* n_seeds_dev, const pcseg_planar_config* cfg,
-               const float q[4], int id_offset) {
+               const float q[4], int id_offset, const ClusterArgs* fuse_cluster = nullptr, bool* fused = nullptr) {
   pcseg_ctx* c = b->ctx;
+  if (fused) *fused = false;
   PlanarArgs a;
   a.xyz = xyz_dev; a.normals = normals_dev; a.labels = b->labels.as<int>();
   a.rows = b->rows; a.cols = b->cols;
@@ -252,7 +284,7 @@ int run_planar(pcseg_batch* b, const float* xyz_dev, const float* normals_dev, c
   const size_t smem_fixed = 32 * 11 * sizeof(float) + kHashSize * sizeof(unsigned);
   size_t smem = (size_t)a.mask_words * 4 + (size_t)a.ring * 20 + smem_fixed;
   cudaFuncAttributes fattr;
-  CU_TRY(c, cudaFuncGetAttributes(&fattr, planar_grow_kernel<kPipeBlock, true>));
+  CU_TRY(c, cudaFuncGetAttributes(&fattr, planar_grow_kernel<kPipeBlock, true, false>));
   const size_t smem_static = fattr.sharedSizeBytes;
   // two frames per SM when they fit (228 KB per SM, 1 KB reserved per CTA), else one
   const size_t smem_two = (228 * 1024) / 2 - 1024 - smem_static;
@@ -263,10 +295,16 @@ int run_planar(pcseg_batch* b, const float* xyz_dev, const float* normals_dev, c
     if (smem > smem_two && (size_t)a.mask_words * 4 + 1024 * 20 + smem_fixed <= smem_two) a.ring = 1024;
     smem = (size_t)a.mask_words * 4 + (size_t)a.ring * 20 + smem_fixed;
     while (smem > smem_max) { a.ring /= 2; smem = (size_t)a.mask_words * 4 + (size_t)a.ring * 20 + smem_fixed; }
-    CU_TRY(c, cudaFuncSetAttribute(planar_grow_kernel<kPipeBlock, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    planar_grow_kernel<kPipeBlock, true><<<b->n_frames, kPipeBlock, smem, c->stream>>>(a);
+    if (fuse_cluster && getenv("PCSEG_FUSE")) {  // opt-in: measured slower (the extra code thrashes the instruction cache)
+      CU_TRY(c, cudaFuncSetAttribute(planar_grow_kernel<kPipeBlock, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      planar_grow_kernel<kPipeBlock, true, true><<<b->n_frames, kPipeBlock, smem, c->stream>>>(a, *fuse_cluster);
+      if (fused) *fused = true;
+    } else {
+      CU_TRY(c, cudaFuncSetAttribute(planar_grow_kernel<kPipeBlock, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      planar_grow_kernel<kPipeBlock, true, false><<<b->n_frames, kPipeBlock, smem, c->stream>>>(a, ClusterArgs{});
+    }
   } else {
-    planar_grow_kernel<kGrowBlock, false><<<b->n_frames, kGrowBlock, 0, c->stream>>>(a);
+    planar_grow_kernel<kGrowBlock, false, false><<<b->n_frames, kGrowBlock, 0, c->stream>>>(a, ClusterArgs{});
   }
   ++c->launches;
   CU_TRY(c, cudaGetLastError());
@@ -276,19 +314,9 @@ int run_planar(pcseg_batch* b, const float* xyz_dev, const float* normals_dev, c
 int run_cluster(pcseg_batch* b, const float* xyz_dev, const int* seeds_dev, int n_seeds,
                 const pcseg_cluster_config* cfg, int id_offset, int offset_from_planar) {
   pcseg_ctx* c = b->ctx;
-  b->rcap_cluster = (int)(b->N / (size_t)cfg->min_region_inliers) + 1;
-  CU_TRY(c, b->meta_cluster.ensure((size_t)b->n_frames * b->rcap_cluster * sizeof(ClusterMeta)));
   ClusterArgs a;
-  a.xyz = xyz_dev; a.labels = b->labels.as<int>();
-  a.rows = b->rows; a.cols = b->cols;
-  a.seeds = seeds_dev; a.n_seeds = seeds_dev ? n_seeds : (int)b->N;
-  a.min_inliers = cfg->min_region_inliers; a.sq_thr = cfg->squared_distance_threshold;
-  a.half_window = cfg->half_search_window;
-  a.id_offset = id_offset; a.id_offset_from_planar = offset_from_planar;
-  a.queue = b->queue.as<int>(); a.qcap = b->qcap;
-  a.claim = b->claim.as<int>(); a.inliers = b->inl_cluster.as<int>();
-  a.meta = b->meta_cluster.as<ClusterMeta>(); a.rcap = b->rcap_cluster;
-  a.stats = b->stats.as<FrameStats>();
+  int st = make_cluster_args(b, xyz_dev, seeds_dev, n_seeds, cfg, id_offset, offset_from_planar, &a);
+  if (st) return st;
   cluster_grow_kernel<kGrowBlock><<<b->n_frames, kGrowBlock, 0, c->stream>>>(a);
   ++c->launches;
   CU_TRY(c, cudaGetLastError());
@@ -519,7 +547,9 @@ int pcseg_create(int device, pcseg_ctx** out) {
   if (cudaSetDevice(device) != cudaSuccess) return PCSEG_ERR_CUDA;
   pcseg_ctx* c = new pcseg_ctx();
   c->device = device;
-  if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+  if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&c->copy_in, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&c->copy_out, cudaStreamNonBlocking) != cudaSuccess) {
     delete c;
     return PCSEG_ERR_CUDA;
   }
@@ -533,6 +563,9 @@ void pcseg_destroy(pcseg_ctx* c) {
   if (c->scratch) pcseg_batch_destroy(c->scratch);
   c->tmp_a.release();
   c->tmp_b.release();
+  for (cudaEvent_t e : c->chunk_ev) cudaEventDestroy(e);
+  if (c->copy_in) cudaStreamDestroy(c->copy_in);
+  if (c->copy_out) cudaStreamDestroy(c->copy_out);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -949,21 +982,53 @@ int pcseg_batch_run(pcseg_batch* b, const float* xyz, const pcseg_pipeline_param
   if (p->run_cluster_stage && (st = check_cluster_cfg(&p->cluster))) return st;
   cudaSetDevice(c->device);
   const size_t F = b->n_frames, N = b->N;
-  const void* xyz_dev;
-  if ((st = to_device(c, xyz, F * N * 3 * sizeof(float), &b->xyz, &xyz_dev))) return st;
-  b->xyz_dev = (const float*)xyz_dev;
+  const bool xyz_host = !is_device_ptr(xyz);
+  const bool nrm_host = normals_out && !is_device_ptr(normals_out);
+  if (xyz_host) CU_TRY(c, b->xyz.ensure(F * N * 3 * sizeof(float)));
+  b->xyz_dev = xyz_host ? b->xyz.as<float>() : xyz;
   float* nrm_dev;
-  if (normals_out && is_device_ptr(normals_out)) nrm_dev = normals_out;
+  if (normals_out && !nrm_host) nrm_dev = normals_out;
   else {
     CU_TRY(c, b->normals.ensure(F * N * 3 * sizeof(float)));
     nrm_dev = b->normals.as<float>();
   }
   b->normals_dev = nrm_dev;
   cudaEventRecord(b->ev[0], c->stream);
-  if ((st = run_normals(b, b->xyz_dev, nrm_dev, nullptr, &p->normals, p->sensor_translation, 0, b->rows, 0, b->cols))) return st;
+  if (!xyz_host && !nrm_host) {
+    if ((st = run_normals(b, b->xyz_dev, nrm_dev, nullptr, &p->normals, p->sensor_translation, 0, b->rows, 0, b->cols))) return st;
+  } else {
+    // Host buffers: chunks of frames; chunk k's H2D (copy_in stream) overlaps the normals
+    // kernel of chunk k-1, and its normals D2H (copy_out stream) overlaps everything after.
+    const size_t chunk_frames = std::max<size_t>(1, std::min<size_t>(F, (size_t)(96u << 20) / (N * 12) ));
+    const size_t n_chunks = (F + chunk_frames - 1) / chunk_frames;
+    while (c->chunk_ev.size() < 2 * n_chunks + 1) {
+      cudaEvent_t e;
+      CU_TRY(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+      c->chunk_ev.push_back(e);
+    }
+    // the copy streams start after everything already queued on the main stream
+    cudaEvent_t start = c->chunk_ev[2 * n_chunks];
+    CU_TRY(c, cudaEventRecord(start, c->stream));
+    CU_TRY(c, cudaStreamWaitEvent(c->copy_in, start, 0));
+    CU_TRY(c, cudaStreamWaitEvent(c->copy_out, start, 0));
+    for (size_t k = 0; k < n_chunks; ++k) {
+      const size_t f0 = k * chunk_frames, nf = std::min(chunk_frames, F - f0);
+      const size_t off = f0 * N * 3, cnt = nf * N * 3 * sizeof(float);
+      if (xyz_host) {
+        CU_TRY(c, cudaMemcpyAsync(b->xyz.as<float>() + off, xyz + off, cnt, cudaMemcpyHostToDevice, c->copy_in));
+        CU_TRY(c, cudaEventRecord(c->chunk_ev[2 * k], c->copy_in));
+        CU_TRY(c, cudaStreamWaitEvent(c->stream, c->chunk_ev[2 * k], 0));
+      }
+      if ((st = run_normals(b, b->xyz_dev, nrm_dev, nullptr, &p->normals, p->sensor_translation, 0, b->rows, 0,
+                            b->cols, (int)f0, (int)nf))) return st;
+      if (nrm_host) {
+        CU_TRY(c, cudaEventRecord(c->chunk_ev[2 * k + 1], c->stream));
+        CU_TRY(c, cudaStreamWaitEvent(c->copy_out, c->chunk_ev[2 * k + 1], 0));
+        CU_TRY(c, cudaMemcpyAsync(normals_out + off, nrm_dev + off, cnt, cudaMemcpyDeviceToHost, c->copy_out));
+      }
+    }
+  }
   cudaEventRecord(b->ev[1], c->stream);
-  if (normals_out && !is_device_ptr(normals_out) &&
-      (st = from_device(c, normals_out, nrm_dev, F * N * 3 * sizeof(float)))) return st;
   if ((st = fill_int(c, b->labels.as<int>(), F * N, kUnlabeled))) return st;  // PrepareUnlabeledLabels
   CU_TRY(c, cudaMemsetAsync(b->stats.p, 0, F * sizeof(FrameStats), c->stream));
   const int* seeds_dev = nullptr;
@@ -980,17 +1045,21 @@ int pcseg_batch_run(pcseg_batch* b, const float* xyz, const pcseg_pipeline_param
     n_seeds = p->n_planar_seeds;
   }
   cudaEventRecord(b->ev[2], c->stream);
+  bool fused = false;
   if (!(p->planar_seed_mode == PCSEG_SEEDS_EXPLICIT && n_seeds == 0)) {
+    ClusterArgs ca;
+    if (p->run_cluster_stage && (st = make_cluster_args(b, b->xyz_dev, nullptr, (int)N, &p->cluster, 0, 1, &ca))) return st;
     if ((st = run_planar(b, b->xyz_dev, nrm_dev, seeds_dev, n_seeds, stride, n_seeds_dev, &p->planar,
-                         p->robot_q_xyzw, 0))) return st;
+                         p->robot_q_xyzw, 0, p->run_cluster_stage ? &ca : nullptr, &fused))) return st;
   }
   cudaEventRecord(b->ev[3], c->stream);
-  if (p->run_cluster_stage) {
+  if (p->run_cluster_stage && !fused) {
     if ((st = run_cluster(b, b->xyz_dev, nullptr, (int)N, &p->cluster, 0, 1))) return st;
   }
   cudaEventRecord(b->ev[4], c->stream);
   if (labels_out && (st = from_device(c, labels_out, b->labels.p, F * N * sizeof(int)))) return st;
   CU_TRY(c, cudaStreamSynchronize(c->stream));
+  if (nrm_host) CU_TRY(c, cudaStreamSynchronize(c->copy_out));
   return PCSEG_OK;
 }
 

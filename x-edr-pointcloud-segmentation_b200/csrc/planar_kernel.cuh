@@ -4,6 +4,7 @@
 #include "grow_planar.cuh"
 #include "grow_planar_smem.cuh"
 #include "grow_planar_pipe.cuh"
+#include "grow_cluster.cuh"
 
 namespace pcseg {
 
@@ -11,8 +12,11 @@ namespace pcseg {
 //               shared memory (planar_grow_warp_smem); needs
 //               mask_words*4 + ring*20 + 32*11*4 + kHashSize*4 bytes.
 // SMEM = false: everything through L2 (planar_grow_warp); any cloud size.
-template <int BLOCK, bool SMEM>
-__global__ void __launch_bounds__(BLOCK) planar_grow_kernel(PlanarArgs a) {
+// FUSE = true : the frame's CTA goes on with SegmentRegions<ClusterRegion<>> (seeds all
+//               descending or ca.seeds, id offset = the frame's plane count) as soon as its
+//               own planar stage is done, instead of waiting for the slowest frame of the batch.
+template <int BLOCK, bool SMEM, bool FUSE>
+__global__ void __launch_bounds__(BLOCK, SMEM ? 2 : 1) planar_grow_kernel(PlanarArgs a, ClusterArgs ca) {
   extern __shared__ __align__(16) unsigned char dyn_smem[];
   const int f = blockIdx.x;
   const int tid = threadIdx.x;
@@ -21,7 +25,7 @@ __global__ void __launch_bounds__(BLOCK) planar_grow_kernel(PlanarArgs a) {
   const float* __restrict__ xyz = a.xyz + (size_t)f * N * 3;
   const float* __restrict__ nrm = a.normals + (size_t)f * N * 3;
   volatile int* labels = a.labels + (size_t)f * N;
-  volatile int* queue = a.queue + (size_t)f * a.qcap;
+  volatile int* queue = a.queue + (size_t)f * a.qcap * 2;  // per-frame stride shared with the cluster stage ([qcap][2])
   int* claim = a.claim + (size_t)f * N;
   int* inliers = a.inliers + (size_t)f * N;
   int* boundary = a.boundary + (size_t)f * a.bcap;
@@ -81,6 +85,7 @@ __global__ void __launch_bounds__(BLOCK) planar_grow_kernel(PlanarArgs a) {
 
 #ifdef PCSEG_PROFILE
   long long kp_seed = 0, kp_fin = 0, kp_regions = 0, kp_tiny = 0;
+  const long long kp_start = clock64();
 #endif
   while (true) {
     PROF_T(k0);
@@ -116,7 +121,7 @@ __global__ void __launch_bounds__(BLOCK) planar_grow_kernel(PlanarArgs a) {
     const int base = inl_total;
 
     if constexpr (SMEM) {
-      int* gqueue = a.queue + (size_t)f * a.qcap;
+      int* gqueue = a.queue + (size_t)f * a.qcap * 2;
       if (tid == 0) {
         const V3 sp = ld3(xyz, seed);
         sm.q_tag[0] = tag_base;
@@ -308,8 +313,10 @@ __global__ void __launch_bounds__(BLOCK) planar_grow_kernel(PlanarArgs a) {
   if (tid == 0 && a.prof) {
     a.prof[(size_t)f * 16 + 13] += kp_seed;
     a.prof[(size_t)f * 16 + 14] += kp_fin;
-    a.prof[(size_t)f * 16 + 15] += kp_regions * 1000000 + kp_tiny;
+    a.prof[(size_t)f * 16 + 15] = clock64() - kp_start;  // planar stage of this frame, cycles
+    (void)kp_regions; (void)kp_tiny;
   }
+  const long long kp_planar_end = clock64();
 #endif
   if (tid == 0) {
     a.stats[f].n_planar = nreg;
@@ -318,6 +325,13 @@ __global__ void __launch_bounds__(BLOCK) planar_grow_kernel(PlanarArgs a) {
     a.stats[f].error_flags |= err;
     a.stats[f].grow_steps += steps;
     a.stats[f].refits += refits;
+  }
+  if constexpr (FUSE) {
+    __syncthreads();  // the frame's labels (written by this CTA) are final
+    cluster_grow_frame<BLOCK>(ca, f, nreg, s_warp);
+#ifdef PCSEG_PROFILE
+    if (tid == 0 && a.prof) a.prof[(size_t)f * 16 + 7] = clock64() - kp_planar_end;  // fused cluster stage, cycles
+#endif
   }
 }
 
