@@ -53,14 +53,25 @@ def gen_frames(indices):
         return np.stack(pool.map(_gen_frame, list(indices), chunksize=1))
 
 
-def _cpu_pipeline(xyz):
-    """The reference algorithm on the CPU for one frame (oracle port)."""
+def cpu_kind():
+    """"reference": oracle/_ref/libref.so (the reference's own .h/.cc compiled in place against
+    shim headers, built where /root/reference exists and shipped prebuilt); else the "port"."""
     import oracle
-    nrm = oracle.normals_organized(xyz, ROWS, COLS)
-    seeds = np.arange(N_PTS - 1, -1, -1, dtype=np.int32)
-    labels = np.full(N_PTS, -1, np.int32)
-    lab, regs = oracle.segment_planar(xyz, nrm, ROWS, COLS, seeds, labels)
-    lab2, cl = oracle.segment_cluster(xyz, ROWS, COLS, seeds, lab, id_offset=regs.n)
+    return "reference" if oracle.ref_available() else "port"
+
+
+def _cpu_pipeline(xyz):
+    """The reference's CPU path for one frame: ComputeNormalsOrganized ->
+    SegmentRegions<PlanarRegion> -> SegmentRegions<ClusterRegion> (oracle/_ref when built,
+    else the oracle port)."""
+    import contextlib
+    import oracle
+    with (oracle.reference() if oracle.ref_available() else contextlib.nullcontext()):
+        nrm = oracle.normals_organized(xyz, ROWS, COLS)
+        seeds = np.arange(N_PTS - 1, -1, -1, dtype=np.int32)
+        labels = np.full(N_PTS, -1, np.int32)
+        lab, regs = oracle.segment_planar(xyz, nrm, ROWS, COLS, seeds, labels)
+        lab2, cl = oracle.segment_cluster(xyz, ROWS, COLS, seeds, lab, id_offset=regs.n)
     return lab2, regs.n, cl.n
 
 
@@ -136,7 +147,7 @@ def run_reference(args, rank, world):
     import multiprocessing as mp
     cores = os.cpu_count() or 1
     sample = min(FRAMES_PER_GPU, 4 * cores)
-    kind = "port"  # oracle/_ref (reference sources against shims) validates the port in tests/
+    kind = cpu_kind()
     global _FRAMES
     _FRAMES = gen_frames(list(range(sample)))
     with mp.get_context("fork").Pool(cores) as pool:
@@ -328,8 +339,8 @@ def main():
                 "outputs": "normals + labels to pinned host memory", "ok": e2e_ok},
         "gpu_launches": int(launches),
         "roofline": roofline, "roofline_all": roof,
-        "cpu_baseline": {"value": cpu_value, "unit": UNIT, "cores": 1, "kind": "port",
-                         "sample": "%d frames of the same batch, oracle port single-threaded, %.1f s" % (ns, cpu_s)},
+        "cpu_baseline": {"value": cpu_value, "unit": UNIT, "cores": 1, "kind": cpu_kind(),
+                         "sample": "%d frames of the same batch, single-threaded (the reference's native mode), %.1f s" % (ns, cpu_s)},
         "parity": {"frames_checked_vs_oracle": ns, "frames_with_label_mismatch": mismatched_frames},
         "clocks": clocks, "host_cores": os.cpu_count(),
     }
