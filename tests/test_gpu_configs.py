@@ -1,0 +1,107 @@
+"""BASELINE.json's configs C3, C4 and C5 at FULL size, CUDA path (C ABI) against the CPU
+oracle on the same seeded synthetic inputs.  C1 is test_gpu_parity.py::
+test_c1_full_pipeline_parity; C2 is checked frame by frame below and inside bench.py.
+Labels / inlier index sets / boundaries bit-exact; planes, centroids within 1e-5 relative;
+mean-shift modes within 1e-4 of the bandwidth (north_star)."""
+import numpy as np
+import pytest
+
+import oracle
+import pcseg
+import synth
+from test_gpu_parity import assert_regions_equal, assert_same_float, bits
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = pcseg.Context(0)
+    yield c
+    c.close()
+
+
+def test_c3_1280x720_indoor_full(ctx):
+    """C3: 1280x720 organized cloud, >= 25 planes; normals (+ curvature channel) -> planes
+    (plane-support seeds and all-descending seeds) -> clusters."""
+    rows, cols = 720, 1280
+    xyz = synth.c3(rows, cols)
+    g_n, g_curv = ctx.normals_organized(xyz, rows, cols, want_curvature=True)
+    o_n, o_curv = oracle.normals_organized(xyz, rows, cols, want_curvature=True)
+    assert_same_float(g_n, o_n, "normals")
+    assert_same_float(g_curv, o_curv, "curvature")
+    labels = np.full(rows * cols, -1, np.int32)
+    for seeds_g, seeds_o in (
+            (ctx.seeds_plane_support(xyz, g_n, rows, cols), oracle.seeds_plane_support(xyz, o_n, rows, cols)),
+            (np.arange(rows * cols - 1, -1, -1, dtype=np.int32),) * 2):
+        assert np.array_equal(seeds_g, seeds_o)
+        o_lab, o_r = oracle.segment_planar(xyz, o_n, rows, cols, seeds_o, labels)
+        g_lab, g_r = ctx.segment_planar(xyz, g_n, rows, cols, seeds_g, labels)
+        assert np.array_equal(g_lab, o_lab)
+        assert_regions_equal(g_r, o_r, "planar")
+        assert g_r.n >= 25
+    alld = np.arange(rows * cols - 1, -1, -1, dtype=np.int32)
+    o_lab2, o_c = oracle.segment_cluster(xyz, rows, cols, alld, o_lab, id_offset=o_r.n)
+    g_lab2, g_c = ctx.segment_cluster(xyz, rows, cols, alld, g_lab, id_offset=g_r.n)
+    assert np.array_equal(g_lab2, o_lab2)
+    assert_regions_equal(g_c, o_c, "cluster")
+
+
+def test_c4_lidar_2m_points_full(ctx):
+    """C4 (reference-parity variant): 128 x 16384 organized lidar sweep = 2 097 152 points,
+    ground pre-masked, Euclidean clustering with h = 2 (fewer objects than SURVEY.md's 200 so
+    that the CPU scene generator stays within seconds; the cloud size is the full one)."""
+    rows, cols = 128, 16384
+    xyz, labels = synth.c4(rows=rows, cols=cols, n_objects=24)
+    assert xyz.shape[0] == 2097152
+    seeds = np.arange(rows * cols - 1, -1, -1, dtype=np.int32)
+    cfg = dict(squared_distance_threshold=0.25, half_search_window=2, min_region_inliers=10)
+    o_lab, o_r = oracle.segment_cluster(xyz, rows, cols, seeds, labels, cfg=oracle.default_cluster_config(**cfg))
+    g_lab, g_r = ctx.segment_cluster(xyz, rows, cols, seeds, labels, cfg=cfg)
+    assert o_r.n > 5
+    assert np.array_equal(g_lab, o_lab)
+    assert_regions_equal(g_r, o_r, "cluster")
+
+
+def test_c5_meanshift_10m_points_full(ctx):
+    """C5: SlidingMeanShift of a 2500 x 4000 = 10 M point cloud, 5 iterations; also the
+    8-way seed-cell sharding of the iteration phase (the multi-GPU partition) against the
+    unsharded records."""
+    rows, cols = 2500, 4000
+    xyz = synth.c5(rows, cols)
+    labels = np.full(rows * cols, -1, np.int32)
+    o_lab, o_r, o_modes = oracle.mean_shift(xyz, rows, cols, labels, iterations=5)
+    g_lab, g_r = ctx.mean_shift(xyz, rows, cols, labels, iterations=5)
+    assert np.array_equal(g_lab, o_lab)
+    assert_regions_equal(g_r, o_r, "cluster")
+    assert np.all(np.abs(g_r.seed_points - o_r.seed_points) <= 1e-4)  # 1e-4 of the 1 m bandwidth
+    full = ctx.mean_shift_modes(xyz, rows, cols, labels, iterations=5)
+    seed_cells = o_modes[:, 7].astype(np.int64)
+    assert np.array_equal(np.nonzero(full[:, 7] == 1.0)[0], seed_cells)
+    assert np.all(np.abs(full[seed_cells][:, :5] - o_modes[:, :5]) <= 1e-4)
+    n = rows * cols
+    parts = [ctx.mean_shift_modes_range(xyz, rows, cols, labels, 5, n * k // 8, n * (k + 1) // 8) for k in range(8)]
+    assert np.array_equal(bits(np.concatenate(parts)), bits(full))
+
+
+def test_c2_batch_frames_vs_oracle(ctx):
+    """C2: frames of the 256-frame batch through the batched pipeline (pcseg_batch_run, host
+    buffers) against the per-frame CPU pipeline; frame ids spread over the batch."""
+    rows, cols = 480, 640
+    ids = [0, 37, 101, 133, 200, 255]
+    frames = np.stack([synth.c2_frame(i, 256, rows, cols) for i in ids])
+    b = pcseg.Batch(ctx, len(ids), rows, cols)
+    nrm = np.empty((len(ids), rows * cols, 3), np.float32)
+    lab = np.empty((len(ids), rows * cols), np.int32)
+    b.run(frames, pcseg.pipeline_params(seed_mode=pcseg.SEEDS_ALL_DESCENDING, run_cluster=True),
+          normals_out=nrm, labels_out=lab)
+    seeds = np.arange(rows * cols - 1, -1, -1, dtype=np.int32)
+    for k in range(len(ids)):
+        o_n = oracle.normals_organized(frames[k], rows, cols)
+        assert_same_float(nrm[k], o_n, "normals of frame %d" % ids[k])
+        o_lab, o_r = oracle.segment_planar(frames[k], o_n, rows, cols, seeds, np.full(rows * cols, -1, np.int32))
+        o_lab2, o_c = oracle.segment_cluster(frames[k], rows, cols, seeds, o_lab, id_offset=o_r.n)
+        assert np.array_equal(lab[k], o_lab2), "labels of frame %d" % ids[k]
+        assert_regions_equal(b.regions(k, "planar"), o_r, "planar")
+        assert_regions_equal(b.regions(k, "cluster"), o_c, "cluster")
+    b.close()
