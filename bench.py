@@ -183,6 +183,9 @@ def main():
     ap.add_argument("--frames", type=int, default=FRAMES_PER_GPU)
     ap.add_argument("--cpu-sample", type=int, default=16)
     ap.add_argument("--seed-mode", default="alldesc", choices=["alldesc", "planesupport"])
+    ap.add_argument("--depth", type=int, default=4, choices=[1, 2, 3, 4],
+                    help="batch workspaces in flight per GPU (2: pcseg_batch_submit/wait, the copies and the "
+                         "normals stage of one batch overlap the growth stages of the other; 1: synchronous)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -212,10 +215,14 @@ def main():
     out_labels = torch.empty((F, N_PTS), dtype=torch.int32).pin_memory()
 
     ctx = pcseg.Context(local_rank)
-    batch = pcseg.Batch(ctx, F, ROWS, COLS)
+    D = args.depth
+    batches = [pcseg.Batch(ctx, F, ROWS, COLS) for _ in range(D)]
+    batch = batches[0]
+    out_normals = [out_normals] + [torch.empty((F, N_PTS, 3), dtype=torch.float32).pin_memory() for _ in range(D - 1)]
+    out_labels = [out_labels] + [torch.empty((F, N_PTS), dtype=torch.int32).pin_memory() for _ in range(D - 1)]
     mode = pcseg.SEEDS_ALL_DESCENDING if args.seed_mode == "alldesc" else pcseg.SEEDS_PLANE_SUPPORT
     params = pcseg.pipeline_params(seed_mode=mode, run_cluster=True)
-    stream = torch.cuda.ExternalStream(ctx.stream)
+    stream = torch.cuda.ExternalStream(batch.stream)
 
     def barrier():
         if world > 1:
@@ -229,15 +236,37 @@ def main():
             return float(t.item())
         return x
 
-    def timed(fn, steps):
-        """K steps bracketed by barrier+sync, device time via CUDA events on the
-        library's stream; also the host wall clock."""
+    stage_acc = {"normals": 0.0, "seeds": 0.0, "planar": 0.0, "cluster": 0.0}
+
+    def run_steps(steps, submit, collect=False):
+        """`steps` passes of the pipeline, step i on workspace i % D; a workspace is waited for
+        (and its stage timers read) before it is reused, and all are drained at the end."""
+        busy = [False] * D
+        for i in range(steps):
+            j = i % D
+            if busy[j]:
+                batches[j].wait()
+                if collect:
+                    for k, v in batches[j].stage_times().items():
+                        stage_acc[k] += v
+            submit(j)
+            busy[j] = True
+        for j in range(D):
+            if busy[j]:
+                batches[j].wait()
+                if collect:
+                    for k, v in batches[j].stage_times().items():
+                        stage_acc[k] += v
+
+    def timed(submit, steps, collect=False):
+        """K steps bracketed by barrier+sync; device time between two CUDA events on the first
+        workspace's stream (idle at both records, so they bracket the whole region); also the
+        host wall clock."""
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
         e0.record(stream)
-        for _ in range(steps):
-            fn()
+        run_steps(steps, submit, collect)
         e1.record(stream)
         e1.synchronize()
         wall = (time.perf_counter() - t0) * 1e3
@@ -245,21 +274,13 @@ def main():
         return max_over_ranks(e0.elapsed_time(e1)), max_over_ranks(wall)
 
     # ---- device-resident arm (value) ----
-    run_dev = lambda: batch.run(dev_xyz.data_ptr(), params)
-    for _ in range(args.warmup):
-        run_dev()
+    submit_dev = lambda j: batches[j].submit(dev_xyz.data_ptr(), params)
+    run_steps(args.warmup, submit_dev)
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
     l0 = ctx.launches
-    stage_acc = {"normals": 0.0, "seeds": 0.0, "planar": 0.0, "cluster": 0.0}
-
-    def run_dev_acc():
-        run_dev()
-        for k, v in batch.stage_times().items():
-            stage_acc[k] += v
-
-    dev_ms, dev_wall = timed(run_dev_acc, args.steps)
+    dev_ms, dev_wall = timed(submit_dev, args.steps, collect=True)
     launches = ctx.launches - l0
     clocks = sampler.stop() if rank == 0 else None
     stats = batch.frame_stats()
@@ -269,14 +290,24 @@ def main():
 
     # ---- end-to-end arm (host buffers through the C ABI) ----
     host_np = host.numpy()
-    on_np, ol_np = out_normals.numpy(), out_labels.numpy()
-    run_e2e = lambda: batch.run(host_np, params, normals_out=on_np, labels_out=ol_np)
-    for _ in range(2):
-        run_e2e()
-    e2e_ms, e2e_wall = timed(run_e2e, args.steps)
+    on_np = [t.numpy() for t in out_normals]
+    ol_np = [t.numpy() for t in out_labels]
+    submit_e2e = lambda j: batches[j].submit(host_np, params, normals_out=on_np[j], labels_out=ol_np[j])
+    run_steps(2, submit_e2e)
+    e2e_ms, e2e_wall = timed(submit_e2e, args.steps)
     e2e_ms_step = max(e2e_ms, e2e_wall) / args.steps
     e2e_value = total_pts / (e2e_ms_step * 1e-3) / 1e6
     e2e_ok = int(stats[:, 5].max()) == 0
+    ol_np = ol_np[0]
+
+    # ---- one batch alone, synchronous: its latency (all frames submitted up front) ----
+    sync_ms = []
+    for it in range(3):
+        t0 = time.perf_counter()
+        batch.run(dev_xyz.data_ptr(), params)
+        sync_ms.append((time.perf_counter() - t0) * 1e3)
+    batch_latency_ms = statistics.median(sync_ms)
+    stage_ms_sync = batch.stage_times()   # one batch alone: no other workspace's kernels beside it
 
     # ---- single frame latency ----
     b1 = pcseg.Batch(ctx, 1, ROWS, COLS)
@@ -292,8 +323,11 @@ def main():
             dist.destroy_process_group()
         return
 
-    # ---- roofline of the dominant kernel (live stage timings) ----
-    stage_ms = {k: v / args.steps for k, v in stage_acc.items()}
+    # ---- roofline of the dominant kernel.  Kernel durations are the CUDA-event stage timings of
+    # one batch run ALONE (synchronous pass above): in the timed region D workspaces overlap, so a
+    # stage's elapsed time there (stage_ms) also contains the other workspaces' kernels. ----
+    stage_ms_overlapped = {k: v / args.steps for k, v in stage_acc.items()}
+    stage_ms = stage_ms_sync
     peak, peak_kind = measured_peak_gbs()
     dom = max(("planar", "normals", "cluster"), key=lambda k: stage_ms[k])
     fused = stage_ms["cluster"] < 0.05   # cluster stage runs inside planar_grow_kernel (per-frame fusion)
@@ -310,8 +344,9 @@ def main():
     roofline = dict(roof[dom])
     roofline["kernel"] = {"planar": "planar_grow_kernel" + (" (planar + fused cluster growth)" if fused else ""),
                           "normals": "normals_kernel", "cluster": "cluster_grow_kernel"}[dom]
-    roofline["note"] = ("latency-bound serial FIFO chain (one re-fit per 30 inliers), not bandwidth-bound; "
-                        "see DESIGN.md and profiles/")
+    roofline["note"] = ("kernel_ms: one batch alone (CUDA events on its stream); latency-bound serial FIFO chain "
+                        "(one re-fit per 30 inliers) whose top stall is instruction fetch, not bandwidth-bound; "
+                        "see DESIGN.md section 8 and profiles/")
 
     # ---- CPU baseline: oracle port, single thread, bounded sample ----
     ns = min(args.cpu_sample, F)
@@ -330,9 +365,10 @@ def main():
         "config": {"workload": "C2: batch of %d 640x480 organized depth frames per GPU, normals+planes+clusters, "
                                "planar seeds %s, frame-wise sharding" % (F, args.seed_mode),
                    "frames_per_gpu": F, "rows": ROWS, "cols": COLS, "points_per_step": total_pts,
-                   "l2": "inputs larger than L2 (%.0f MB of points per GPU per step)" % (F * N_PTS * 12 / 1e6)},
-        "p50_frame_ms": ms_per_step, "latency_ms_single_frame": statistics.median(lat),
-        "stage_ms": stage_ms,
+                   "l2": "inputs larger than L2 (%.0f MB of points per GPU per step)" % (F * N_PTS * 12 / 1e6),
+                   "workspaces_in_flight": D},
+        "p50_frame_ms": batch_latency_ms, "latency_ms_single_frame": statistics.median(lat),
+        "stage_ms": stage_ms, "stage_ms_in_timed_region_overlapped": stage_ms_overlapped,
         "regions_per_frame": {"planar": float(stats[:, 0].mean()), "cluster": float(stats[:, 1].mean())},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(F * N_PTS * 12) * world,
                 "d2h_bytes_per_step": int(F * N_PTS * 16) * world, "ms_per_step": e2e_ms_step,
@@ -345,7 +381,8 @@ def main():
         "clocks": clocks, "host_cores": os.cpu_count(),
     }
     print(json.dumps(line), flush=True)
-    batch.close()
+    for b in batches:
+        b.close()
     ctx.close()
     if world > 1:
         dist.destroy_process_group()

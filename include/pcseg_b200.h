@@ -181,6 +181,18 @@ void pcseg_batch_destroy(pcseg_batch*);
 int pcseg_batch_run(pcseg_batch*, const float* xyz,
                     const pcseg_pipeline_params* params, float* normals_out,
                     int* labels_out);
+/* Asynchronous form of pcseg_batch_run: submit enqueues the whole pipeline (copies included)
+ * on the workspace's own streams and returns; wait blocks until its results are complete.
+ * Two workspaces of one context used alternately overlap the host copies of one batch with
+ * the kernels of the other (a caller's frame stream: bench.py's e2e arm).  The buffers passed
+ * to submit must stay valid (and pinned, for real overlap) until wait returns; submitting to
+ * a workspace that is still in flight waits for it first. */
+int pcseg_batch_submit(pcseg_batch*, const float* xyz,
+                       const pcseg_pipeline_params* params, float* normals_out,
+                       int* labels_out);
+int pcseg_batch_wait(pcseg_batch*);
+/* The CUDA stream (cudaStream_t as void*) the workspace's kernels are launched on. */
+void* pcseg_batch_stream(const pcseg_batch*);
 /* Per-frame counters after a run: {n_planar, n_cluster, planar_inliers,
  * cluster_inliers, boundary_len, error_flags, grow_steps, refits}. */
 int pcseg_batch_frame_stats(pcseg_batch*, int* stats8_per_frame);

@@ -1,0 +1,84 @@
+"""Secondary timings (not the bench line): configs C3, C4, C5 at full size on one GPU, device
+time with CUDA events around the C-ABI calls (inputs resident in HBM), and the CPU oracle
+(single thread) beside them.  Prints one JSON object."""
+import json, os, sys, time
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "x-edr-pointcloud-segmentation_b200"))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+import numpy as np
+import torch
+import oracle, pcseg, synth
+
+ctx = pcseg.Context(0)
+stream = torch.cuda.ExternalStream(ctx.stream)
+
+
+def gpu_ms(fn, reps=5):
+    fn(); fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record(stream)
+    for _ in range(reps):
+        fn()
+    e1.record(stream)
+    e1.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+def cpu_ms(fn):
+    t = time.perf_counter(); fn(); return (time.perf_counter() - t) * 1e3
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+out = {}
+# ---- C3 ----
+rows, cols = 720, 1280
+xyz = synth.c3(rows, cols); N = rows * cols
+d_xyz = dev(xyz); d_n = torch.empty((N, 3), dtype=torch.float32, device="cuda")
+seeds = np.arange(N - 1, -1, -1, dtype=np.int32)
+import ctypes as C
+L = ctx.L
+VP = C.c_void_p
+np_ = pcseg.normals_params()
+st3 = (C.c_double * 3)(0.0, 0.0, 0.0)
+t_n = gpu_ms(lambda: ctx._check(L.pcseg_normals_organized(ctx.h, VP(d_xyz.data_ptr()), rows, cols, st3, C.byref(np_),
+                                                          0, rows, 0, cols, VP(d_n.data_ptr()), None)))
+nrm = d_n.cpu().numpy()
+labels = np.full(N, -1, np.int32)
+# growth stages through the numpy API (host buffers: the copies are < 1 ms of these times)
+t_p = gpu_ms(lambda: ctx.segment_planar(xyz, nrm, rows, cols, seeds, labels), reps=3)
+g_lab, g_r = ctx.segment_planar(xyz, nrm, rows, cols, seeds, labels)
+t_c = gpu_ms(lambda: ctx.segment_cluster(xyz, rows, cols, seeds, g_lab, id_offset=g_r.n), reps=3)
+c_n = cpu_ms(lambda: oracle.normals_organized(xyz, rows, cols))
+c_p = cpu_ms(lambda: oracle.segment_planar(xyz, nrm, rows, cols, seeds, labels))
+c_c = cpu_ms(lambda: oracle.segment_cluster(xyz, rows, cols, seeds, g_lab, id_offset=g_r.n))
+out["C3_1280x720"] = {"points": N, "planes": int(g_r.n), "gpu_ms": {"normals": t_n, "planar": t_p, "cluster": t_c},
+                      "cpu_port_ms": {"normals": c_n, "planar": c_p, "cluster": c_c},
+                      "gpu_Mpts_s": N / (t_n + t_p + t_c) / 1e3, "cpu_Mpts_s": N / (c_n + c_p + c_c) / 1e3,
+                      "normals_GBs": 24.0 * N / t_n / 1e6}
+# ---- C4 ----
+rows, cols = 128, 16384
+xyz, labels = synth.c4(rows=rows, cols=cols, n_objects=24); N = rows * cols
+d_xyz = dev(xyz); seeds = np.arange(N - 1, -1, -1, dtype=np.int32)
+cfg = dict(squared_distance_threshold=0.25, half_search_window=2, min_region_inliers=10)
+t_c = gpu_ms(lambda: ctx.segment_cluster(xyz, rows, cols, seeds, labels, cfg=cfg), reps=3)
+c_c = cpu_ms(lambda: oracle.segment_cluster(xyz, rows, cols, seeds, labels, cfg=oracle.default_cluster_config(**cfg)))
+out["C4_lidar_2M"] = {"points": N, "gpu_ms": {"cluster": t_c}, "cpu_port_ms": {"cluster": c_c},
+                      "gpu_Mpts_s": N / t_c / 1e3, "cpu_Mpts_s": N / c_c / 1e3}
+# ---- C5 ----
+rows, cols = 2500, 4000
+xyz = synth.c5(rows, cols); N = rows * cols
+d_xyz = dev(xyz); labels = np.full(N, -1, np.int32); d_lab = dev(labels)
+d_modes = torch.empty((N, 8), dtype=torch.float32, device="cuda")
+t_m = gpu_ms(lambda: ctx._check(L.pcseg_mean_shift_modes(ctx.h, VP(d_xyz.data_ptr()), rows, cols, VP(d_lab.data_ptr()), 5,
+                                                         VP(d_modes.data_ptr()))))
+t_full = gpu_ms(lambda: ctx.mean_shift(xyz, rows, cols, labels, iterations=5), reps=2)
+c_full = cpu_ms(lambda: oracle.mean_shift(xyz, rows, cols, labels, iterations=5))
+n_seeds = int((~np.isnan(xyz[:, 0])).sum())
+out["C5_meanshift_10M"] = {"points": N, "seeds": n_seeds, "gpu_ms": {"modes_kernel": t_m, "sliding_mean_shift_total": t_full},
+                           "cpu_port_ms": {"sliding_mean_shift_total": c_full},
+                           "modes_Gseeds_s": n_seeds / t_m / 1e6, "modes_GBs_algorithmic": 44.0 * n_seeds / t_m / 1e6,
+                           "speedup_total": c_full / t_full}
+print(json.dumps(out))

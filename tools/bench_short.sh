@@ -1,7 +1,7 @@
 #!/bin/bash
 # usage: tools/bench_short.sh <tag> [env assignments...]; prints the key fields of a 5-step bench
 tag=$1; shift
-env "$@" python bench.py --steps 5 > gpurun_out/b_$tag.log 2>&1
+env "$@" python bench.py --steps 6 $BENCH_ARGS > gpurun_out/b_$tag.log 2>&1
 python - <<PY
 import json
 try:

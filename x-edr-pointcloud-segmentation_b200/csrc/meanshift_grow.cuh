@@ -19,7 +19,9 @@
 //       winners are appended in key order -- exactly the order in which the
 //       sequential loop would have labelled them (labels are written at once,
 //       there is no "in queue" state, quirk Q15);
-//     * < min_region_inliers: labels reset to kUnlabeled (:323-327).
+//     * < min_region_inliers: labels reset to kUnlabeled (:323-327);
+//     * modes whose first step would find nothing (they sit on an area labelled by an earlier
+//       region) are no-ops and are filtered out per batch of 1024, in parallel.
 #pragma once
 #include "meanshift.cuh"
 
@@ -92,6 +94,28 @@ __global__ void __launch_bounds__(kMsGrowBlock) ms_grow_kernel(MsGrowArgs a) {
         const V3 d{me.mx - s[0], me.my - s[1], me.mz - s[2]};
         if ((double)vsqn(d) < 1.0) alive = false;     // kSquaredCentroidDistanceThreshold, :316-318
       }
+    }
+    // A mode whose FIRST queue step (the window of its centre cell, :172-199) finds no cell that
+    // is unlabeled, not NaN and within 1 m^2 of the mode grows an empty region: rejected, labels
+    // untouched, nothing suppressed -- a no-op.  Labels only move kUnlabeled -> label between now
+    // and the mode's turn (a rejected region restores what it took), so "empty now" implies
+    // "empty then" and such modes are dropped here, in parallel.  Without this every mode that
+    // lands on an already labelled area costs a serial CTA-wide round (millions on C5).
+    if (alive) {
+      const V3 mm{me.mx, me.my, me.mz};
+      const int crow = me.centre % rows, ccol = me.centre / rows;
+      bool any = false;
+      for (int s = 0; s < WW && !any; ++s) {
+        const int rc = crow + s % W - a.half_window, cc = ccol + s / W - a.half_window;
+        if (cc >= 0 && cc < cols && rc >= 0 && rc < rows) {
+          const int n = cc * rows + rc;
+          if (a.labels[n] == kUnlabeled) {
+            const V3 p = ld3(a.xyz, n);
+            if (!vhasnan(p) && !((double)vsqn(vsub(p, mm)) > 1.0)) any = true;
+          }
+        }
+      }
+      if (!any) alive = false;
     }
     while (true) {
       // first surviving mode of the batch

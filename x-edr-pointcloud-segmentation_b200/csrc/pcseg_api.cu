@@ -93,6 +93,11 @@ struct pcseg_batch {
   const float* xyz_dev = nullptr;      // where this run's points live on the device
   const float* normals_dev = nullptr;  // where this run's normals live on the device
   bool claim_ready = false;
+  // Workspaces made by pcseg_batch_create own a stream set, so that two of them on one context
+  // overlap (pcseg_batch_submit / pcseg_batch_wait: the copies of one run under the kernels of
+  // the other).  The context's cached single-frame workspace has none and uses the context's.
+  cudaStream_t own_stream = nullptr, own_copy_in = nullptr, own_copy_out = nullptr;
+  bool in_flight = false, wait_copy_out = false;
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   DevBuf prof;
 };
@@ -955,6 +960,12 @@ int pcseg_batch_create(pcseg_ctx* c, int n_frames, int rows, int cols, pcseg_bat
   int st = batch_alloc(b);
   if (st) { pcseg_batch_destroy(b); return st; }
   for (auto& e : b->ev) cudaEventCreate(&e);
+  if (cudaStreamCreateWithFlags(&b->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&b->own_copy_in, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&b->own_copy_out, cudaStreamNonBlocking) != cudaSuccess) {
+    pcseg_batch_destroy(b);
+    return PCSEG_ERR_CUDA;
+  }
   *out = b;
   return PCSEG_OK;
 }
@@ -963,6 +974,8 @@ void pcseg_batch_destroy(pcseg_batch* b) {
   if (!b) return;
   cudaSetDevice(b->ctx->device);
   cudaStreamSynchronize(b->ctx->stream);
+  for (cudaStream_t s : {b->own_stream, b->own_copy_in, b->own_copy_out})
+    if (s) { cudaStreamSynchronize(s); cudaStreamDestroy(s); }
   DevBuf* all[] = {&b->xyz, &b->normals, &b->labels, &b->queue, &b->claim, &b->inl_planar, &b->inl_cluster,
                    &b->boundary, &b->bflags, &b->meta_planar, &b->meta_cluster, &b->stats, &b->inv_list,
                    &b->inv_count, &b->seeds, &b->n_seeds};
@@ -972,9 +985,55 @@ void pcseg_batch_destroy(pcseg_batch* b) {
   delete b;
 }
 
+namespace {
+// Routes everything a run enqueues to the workspace's own streams (calls on one context are
+// serialised by the caller, so swapping the context's current streams is safe).
+struct StreamScope {
+  pcseg_ctx* c;
+  cudaStream_t s, ci, co;
+  StreamScope(pcseg_ctx* ctx, pcseg_batch* b) : c(ctx), s(ctx->stream), ci(ctx->copy_in), co(ctx->copy_out) {
+    if (b->own_stream) { c->stream = b->own_stream; c->copy_in = b->own_copy_in; c->copy_out = b->own_copy_out; }
+  }
+  ~StreamScope() { c->stream = s; c->copy_in = ci; c->copy_out = co; }
+};
+int batch_enqueue(pcseg_batch* b, const float* xyz, const pcseg_pipeline_params* p, float* normals_out,
+                  int* labels_out);
+}  // namespace
+
+int pcseg_batch_submit(pcseg_batch* b, const float* xyz, const pcseg_pipeline_params* p, float* normals_out,
+                       int* labels_out) {
+  if (!b || !xyz || !p) return PCSEG_ERR_NULL;
+  if (b->in_flight) {
+    int st = pcseg_batch_wait(b);
+    if (st) return st;
+  }
+  StreamScope scope(b->ctx, b);
+  int st = batch_enqueue(b, xyz, p, normals_out, labels_out);
+  if (st == PCSEG_OK) b->in_flight = true;
+  return st;
+}
+
+int pcseg_batch_wait(pcseg_batch* b) {
+  if (!b) return PCSEG_ERR_NULL;
+  pcseg_ctx* c = b->ctx;
+  cudaSetDevice(c->device);
+  if (!b->in_flight) return PCSEG_OK;
+  b->in_flight = false;
+  CU_TRY(c, cudaStreamSynchronize(b->own_stream ? b->own_stream : c->stream));
+  if (b->wait_copy_out) CU_TRY(c, cudaStreamSynchronize(b->own_copy_out ? b->own_copy_out : c->copy_out));
+  return PCSEG_OK;
+}
+
 int pcseg_batch_run(pcseg_batch* b, const float* xyz, const pcseg_pipeline_params* p, float* normals_out,
                     int* labels_out) {
-  if (!b || !xyz || !p) return PCSEG_ERR_NULL;
+  int st = pcseg_batch_submit(b, xyz, p, normals_out, labels_out);
+  if (st) return st;
+  return pcseg_batch_wait(b);
+}
+
+namespace {
+int batch_enqueue(pcseg_batch* b, const float* xyz, const pcseg_pipeline_params* p, float* normals_out,
+                  int* labels_out) {
   pcseg_ctx* c = b->ctx;
   if (b->rows <= 1) return PCSEG_ERR_DIMS;
   int st = check_planar_cfg(&p->planar);
@@ -1058,15 +1117,16 @@ int pcseg_batch_run(pcseg_batch* b, const float* xyz, const pcseg_pipeline_param
   }
   cudaEventRecord(b->ev[4], c->stream);
   if (labels_out && (st = from_device(c, labels_out, b->labels.p, F * N * sizeof(int)))) return st;
-  CU_TRY(c, cudaStreamSynchronize(c->stream));
-  if (nrm_host) CU_TRY(c, cudaStreamSynchronize(c->copy_out));
+  b->wait_copy_out = nrm_host;
   return PCSEG_OK;
 }
+}  // namespace
 
 int pcseg_batch_frame_stats(pcseg_batch* b, int* stats8) {
   if (!b || !stats8) return PCSEG_ERR_NULL;
   pcseg_ctx* c = b->ctx;
   cudaSetDevice(c->device);
+  if (int w = pcseg_batch_wait(b)) return w;
   static_assert(sizeof(FrameStats) == 8 * sizeof(int), "stats layout");
   CU_TRY(c, cudaMemcpyAsync(stats8, b->stats.p, (size_t)b->n_frames * sizeof(FrameStats), cudaMemcpyDeviceToHost, c->stream));
   CU_TRY(c, cudaStreamSynchronize(c->stream));
@@ -1077,6 +1137,7 @@ int pcseg_batch_regions(pcseg_batch* b, int frame, int kind, pcseg_regions** out
   if (!b || !out) return PCSEG_ERR_NULL;
   if (frame < 0 || frame >= b->n_frames) return PCSEG_ERR_DIMS;
   cudaSetDevice(b->ctx->device);
+  if (int w = pcseg_batch_wait(b)) return w;
   pcseg_regions* r = new pcseg_regions();
   int st = kind == 0 ? collect_planar(b, frame, r) : collect_cluster(b, frame, r);
   if (st) { delete r; return st; }
@@ -1088,6 +1149,7 @@ int pcseg_batch_stage_times(pcseg_batch* b, float* ms4) {
   if (!b || !ms4) return PCSEG_ERR_NULL;
   pcseg_ctx* c = b->ctx;
   cudaSetDevice(c->device);
+  if (int w = pcseg_batch_wait(b)) return w;
   CU_TRY(c, cudaEventSynchronize(b->ev[4]));
   // normals (+fix-up) | label init + seed finder | planar growth | cluster growth
   for (int i = 0; i < 4; ++i) CU_TRY(c, cudaEventElapsedTime(ms4 + i, b->ev[i], b->ev[i + 1]));
@@ -1103,6 +1165,7 @@ int pcseg_batch_profile(pcseg_batch* b, long long* out16_per_frame) {
   return PCSEG_OK;
 }
 
+void* pcseg_batch_stream(const pcseg_batch* b) { return b ? (void*)(b->own_stream ? b->own_stream : b->ctx->stream) : nullptr; }
 int* pcseg_batch_device_labels(pcseg_batch* b) { return b ? b->labels.as<int>() : nullptr; }
 float* pcseg_batch_device_normals(pcseg_batch* b) { return b ? const_cast<float*>(b->normals_dev) : nullptr; }
 

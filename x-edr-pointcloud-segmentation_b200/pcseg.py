@@ -93,6 +93,9 @@ def lib():
         L.pcseg_launch_count.argtypes = [C.c_void_p]
         L.pcseg_stream.restype = C.c_void_p
         L.pcseg_stream.argtypes = [C.c_void_p]
+        L.pcseg_batch_stream.restype = C.c_void_p
+        L.pcseg_batch_stream.argtypes = [C.c_void_p]
+        L.pcseg_batch_wait.argtypes = [C.c_void_p]
         L.pcseg_destroy.argtypes = [C.c_void_p]
         L.pcseg_batch_destroy.argtypes = [C.c_void_p]
         L.pcseg_batch_device_labels.restype = C.c_void_p
@@ -341,6 +344,22 @@ class Batch:
             self.h, _addr(xyz), C.byref(params),
             _addr(normals_out) if normals_out is not None else None,
             _addr(labels_out) if labels_out is not None else None))
+
+    def submit(self, xyz, params, normals_out=None, labels_out=None):
+        """Asynchronous run (pcseg_batch_submit); the buffers must stay alive until wait()."""
+        self._keep = (xyz, params, normals_out, labels_out)
+        self.ctx._check(self.ctx.L.pcseg_batch_submit(
+            self.h, _addr(xyz), C.byref(params),
+            _addr(normals_out) if normals_out is not None else None,
+            _addr(labels_out) if labels_out is not None else None))
+
+    def wait(self):
+        self.ctx._check(self.ctx.L.pcseg_batch_wait(self.h))
+        self._keep = None
+
+    @property
+    def stream(self):
+        return self.ctx.L.pcseg_batch_stream(self.h)
 
     def frame_stats(self):
         out = np.zeros((self.n_frames, 8), np.int32)
