@@ -61,7 +61,7 @@ pcseg_last_error pcseg_launch_count pcseg_stream pcseg_prepare_unlabeled_labels
 pcseg_normals_organized pcseg_segment_planar pcseg_segment_cluster
 pcseg_mean_shift_modes pcseg_mean_shift_modes_range pcseg_mean_shift_from_modes
 pcseg_mean_shift pcseg_seeds_plane_support
-pcseg_batch_create pcseg_batch_destroy pcseg_batch_run pcseg_batch_frame_stats
+pcseg_batch_create pcseg_batch_destroy pcseg_batch_run pcseg_batch_submit pcseg_batch_wait pcseg_batch_stream pcseg_batch_frame_stats
 pcseg_batch_regions pcseg_batch_stage_times pcseg_batch_profile pcseg_batch_device_labels pcseg_batch_device_normals
 pcseg_regions_count pcseg_regions_inlier_offsets pcseg_regions_inlier_indices
 pcseg_regions_label_ids pcseg_regions_seed_indices pcseg_regions_planes
