@@ -105,3 +105,42 @@ def test_c2_batch_frames_vs_oracle(ctx):
         assert_regions_equal(b.regions(k, "planar"), o_r, "planar")
         assert_regions_equal(b.regions(k, "cluster"), o_c, "cluster")
     b.close()
+
+
+def test_async_workspaces_equal_synchronous(ctx):
+    """pcseg_batch_submit / pcseg_batch_wait on two workspaces in flight give the results of
+    pcseg_batch_run, for host buffers and for device-resident input."""
+    import torch
+    rows, cols, F = 120, 160, 5
+    sets = [np.stack([synth.depth_frame(rows, cols, seed=100 * s + i, yaw_deg=3.0 * i) for i in range(F)])
+            for s in range(3)]
+    params = pcseg.pipeline_params(normals=pcseg.normals_params(min_neighbor_distance=0.05),
+                                   seed_mode=pcseg.SEEDS_PLANE_SUPPORT, run_cluster=True)
+    ref = pcseg.Batch(ctx, F, rows, cols)
+    want = []
+    for x in sets:
+        n = np.empty((F, rows * cols, 3), np.float32); l = np.empty((F, rows * cols), np.int32)
+        ref.run(x, params, normals_out=n, labels_out=l)
+        want.append((n, l, ref.frame_stats()[:, :5].copy()))
+    ws = [pcseg.Batch(ctx, F, rows, cols) for _ in range(2)]
+    got = [None] * 3
+    outs = [(np.empty((F, rows * cols, 3), np.float32), np.empty((F, rows * cols), np.int32)) for _ in range(3)]
+    pinned = [torch.from_numpy(x).pin_memory().numpy() for x in sets]
+    for i in range(3):
+        ws[i % 2].submit(pinned[i], params, normals_out=outs[i][0], labels_out=outs[i][1])  # waits if in flight
+        if i == 0:
+            continue
+    for w in ws:
+        w.wait()
+    for i in range(3):
+        assert np.array_equal(bits(outs[i][0]), bits(want[i][0])), i
+        assert np.array_equal(outs[i][1], want[i][1]), i
+    # device-resident input, no host outputs: results stay in the workspace
+    d = torch.from_numpy(sets[2]).cuda()
+    ws[0].submit(d.data_ptr(), params)
+    ws[1].submit(d.data_ptr(), params)
+    for w in ws:
+        assert np.array_equal(w.frame_stats()[:, :5], want[2][2])   # frame_stats waits
+        assert_regions_equal(w.regions(F - 1, "planar"), ref.regions(F - 1, "planar"), "planar")
+    for w in ws + [ref]:
+        w.close()

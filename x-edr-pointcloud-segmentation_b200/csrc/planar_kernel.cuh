@@ -15,8 +15,13 @@ namespace pcseg {
 // FUSE = true : the frame's CTA goes on with SegmentRegions<ClusterRegion<>> (seeds all
 //               descending or ca.seeds, id offset = the frame's plane count) as soon as its
 //               own planar stage is done, instead of waiting for the slowest frame of the batch.
+#ifdef PLANAR_MAXNREG
+#define PLANAR_REG_ATTR __maxnreg__(PLANAR_MAXNREG)
+#else
+#define PLANAR_REG_ATTR __launch_bounds__(BLOCK, SMEM ? 2 : 1)
+#endif
 template <int BLOCK, bool SMEM, bool FUSE>
-__global__ void __launch_bounds__(BLOCK, SMEM ? 2 : 1) planar_grow_kernel(PlanarArgs a, ClusterArgs ca) {
+__global__ void PLANAR_REG_ATTR planar_grow_kernel(PlanarArgs a, ClusterArgs ca) {
   extern __shared__ __align__(16) unsigned char dyn_smem[];
   const int f = blockIdx.x;
   const int tid = threadIdx.x;
