@@ -35,7 +35,15 @@
 
 namespace pcseg {
 
-constexpr int kPipeDW = 5;    // re-fit warps / slots: warps 2, 3, 9, 10, 11 of the 12-warp CTA
+// CTA of the fast path: warp 0 = A, 1 = S, 4-7 = B, re-fit warps 2, 3 and 8 .. (kPipeWarps - 1).
+// Fewer warps leave registers on the SM for the kernels of other batches to run beside two
+// resident frames; the default is the measured optimum on the C2 batch.
+#ifndef PCSEG_PIPE_WARPS
+#define PCSEG_PIPE_WARPS 11
+#endif
+constexpr int kPipeWarps = PCSEG_PIPE_WARPS;
+constexpr int kPipeDW = kPipeWarps == 12 ? 5 : kPipeWarps - 6;  // re-fit warps / slots (12 warps: warp 8 idles)
+static_assert(kPipeWarps >= 9 && kPipeWarps <= 12, "A + S + 4 B + 3..5 re-fit warps");
 constexpr int kPipeNC = 16;   // chunk records in flight
 constexpr int kPipePH = 8;    // plane history (> kPipeDW)
 constexpr int kPipeHash = kHashSize;

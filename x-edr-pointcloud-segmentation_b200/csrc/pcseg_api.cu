@@ -25,7 +25,11 @@ using namespace pcseg;
 namespace {
 
 constexpr int kGrowBlock = 256;
-constexpr int kPipeBlock = 384;  // planar fast path: 12 warps (grow_planar_pipe.cuh)
+#ifndef PCSEG_CLUSTER_BLOCK
+#define PCSEG_CLUSTER_BLOCK 512
+#endif
+constexpr int kClusterBlock = PCSEG_CLUSTER_BLOCK;  // queue entries evaluated per step of cluster growth
+constexpr int kPipeBlock = 32 * kPipeWarps;  // planar fast path (grow_planar_pipe.cuh)
 constexpr int kInvCap = 4096;
 
 struct DevBuf {
@@ -322,7 +326,7 @@ int run_cluster(pcseg_batch* b, const float* xyz_dev, const int* seeds_dev, int 
   ClusterArgs a;
   int st = make_cluster_args(b, xyz_dev, seeds_dev, n_seeds, cfg, id_offset, offset_from_planar, &a);
   if (st) return st;
-  cluster_grow_kernel<kGrowBlock><<<b->n_frames, kGrowBlock, 0, c->stream>>>(a);
+  cluster_grow_kernel<kClusterBlock><<<b->n_frames, kClusterBlock, 0, c->stream>>>(a);
   ++c->launches;
   CU_TRY(c, cudaGetLastError());
   return PCSEG_OK;

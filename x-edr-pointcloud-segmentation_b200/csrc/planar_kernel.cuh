@@ -18,7 +18,7 @@ namespace pcseg {
 #ifdef PLANAR_MAXNREG
 #define PLANAR_REG_ATTR __maxnreg__(PLANAR_MAXNREG)
 #else
-#define PLANAR_REG_ATTR __launch_bounds__(BLOCK, SMEM ? 2 : 1)
+#define PLANAR_REG_ATTR __launch_bounds__(SMEM ? 384 : BLOCK, SMEM ? 2 : 1)  // register budget of the 12-warp CTA (<= 85) for every warp count
 #endif
 template <int BLOCK, bool SMEM, bool FUSE>
 __global__ void PLANAR_REG_ATTR planar_grow_kernel(PlanarArgs a, ClusterArgs ca) {
@@ -54,7 +54,7 @@ __global__ void PLANAR_REG_ATTR planar_grow_kernel(PlanarArgs a, ClusterArgs ca)
   int tag_base = 0;
   int refit_last = 0;  // warp R: newest ticket seen on its slot
   __shared__ PipeCtl s_ctl;
-  static_assert(!SMEM || (BLOCK == 384 && kPipeDW == 5), "pipeline roles: warp 0 = A, 1 = S, 4-7 = B, 2-3 and 9-11 = re-fit");
+  static_assert(!SMEM || BLOCK == 32 * kPipeWarps, "pipeline roles: warp 0 = A, 1 = S, 4-7 = B, 2-3 and 8.. = re-fit");
   __shared__ PipeBShared s_bsh;
   if constexpr (SMEM) {
     if (tid == 0) {
@@ -149,7 +149,8 @@ __global__ void PLANAR_REG_ATTR planar_grow_kernel(PlanarArgs a, ClusterArgs ca)
       else if (warp >= 4 && warp < 8)
         pipe_group_B(a, xyz, a.labels + (size_t)f * N, gqueue, inliers, label_id, base, tag_base, sm, s_ctl, s_bsh, tid - 128);
       else if (warp == 1) pipe_warp_S(a, xyz, gqueue, tag_base, sm, s_ctl);
-      else if (warp != 8) pipe_warp_R(s_ctl, warp < 4 ? warp - 2 : warp - 7, refit_last);
+      else if (kPipeWarps == 12) { if (warp != 8) pipe_warp_R(s_ctl, warp < 4 ? warp - 2 : warp - 7, refit_last); }
+      else pipe_warp_R(s_ctl, warp < 4 ? warp - 2 : warp - 6, refit_last);
     } else {
       if (tid < 32) planar_grow_warp(a, xyz, nrm, labels, queue, claim, inliers, seed, label_id, base, &s_res);
     }
@@ -203,8 +204,8 @@ __global__ void PLANAR_REG_ATTR planar_grow_kernel(PlanarArgs a, ClusterArgs ca)
       }
       s_ax[tid] = ax; s_ay[tid] = ay; s_bx[tid] = bx; s_by[tid] = by;
       __syncthreads();
-      for (int s = BLOCK / 2; s > 0; s >>= 1) {
-        if (tid < s) {
+      for (int s = 256; s > 0; s >>= 1) {  // BLOCK <= 512, any multiple of 32
+        if (tid < s && tid + s < BLOCK) {
           if (s_ax[tid + s] < s_ax[tid] || (s_ax[tid + s] == s_ax[tid] && s_ay[tid + s] < s_ay[tid])) {
             s_ax[tid] = s_ax[tid + s]; s_ay[tid] = s_ay[tid + s];
           }
