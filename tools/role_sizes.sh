@@ -18,7 +18,7 @@ for line in open('/tmp/pcseg_sizes/ni.sass'):
     if m and sec:
         if not m.group(1).startswith('.L'): lab=m.group(1)
         continue
-    if sec and 'planar_grow_kernelILi384ELb1ELb0' in sec and re.match(r'\s+/\*[0-9a-f]{4,}\*/',line):
+    if sec and ('planar_grow_kernelILi' in sec and 'ELb1ELb0' in sec) and re.match(r'\s+/\*[0-9a-f]{4,}\*/',line):
         sizes[lab]=sizes.get(lab,0)+16
 for k,v in sorted(sizes.items(), key=lambda x:-x[1])[:9]: print("%6.1f KB  %s"%(v/1024,k.split('$')[-1][:60]))
 PY

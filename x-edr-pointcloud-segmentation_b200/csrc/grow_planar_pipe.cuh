@@ -361,7 +361,7 @@ __device__ __forceinline__ void pipe_warp_A(const PlanarArgs& a, const float* __
   est.plane = plane;
   est.plane.n = prev_n;
   est.centroid = centroid;
-  if (ninl >= a.min_inliers && inper != 0) est_compute(est);
+  if (ninl >= a.min_inliers && inper != 0) est_compute<true>(est);
   else if (n_final == 0) est.plane = Plane{prev_n, 0.0f};
   if (lane == 0) {
     out->ninl = ninl;
@@ -468,7 +468,7 @@ __device__ __forceinline__ void pipe_warp_R(PipeCtl& ctl, int s, int& last) {
     for (int i = 0; i < 10; ++i) S[i] = ctl.req_s[s][i];
     __threadfence_block();
     if (ctl.req_ticket[s] != t) continue;  // re-posted while reading
-    const RawFit r = est_raw(S, V3{S[6], S[7], S[8]}, S[9]);
+    const RawFit r = est_raw<true>(S, V3{S[6], S[7], S[8]}, S[9]);
     if (lane == 0) {
       ctl.res_v[s][0] = r.centroid.x; ctl.res_v[s][1] = r.centroid.y; ctl.res_v[s][2] = r.centroid.z;
       ctl.res_v[s][3] = r.ev.x; ctl.res_v[s][4] = r.ev.y; ctl.res_v[s][5] = r.ev.z;
