@@ -39,8 +39,9 @@ UNIT = "Mpoints/s"
 
 
 def _gen_frame(i):
+    """Frame id i = replica * 256 + k: frame k of the C2 sweep with the replica's noise seeds."""
     import synth
-    return synth.c2_frame(i, FRAMES_PER_GPU, ROWS, COLS)
+    return synth.c2_frame(i % FRAMES_PER_GPU, FRAMES_PER_GPU, ROWS, COLS, replica=i // FRAMES_PER_GPU)
 
 
 def gen_frames(indices):
@@ -207,8 +208,9 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     F = args.frames
-    # frame ids are disjoint across ranks (frame-wise sharding: frame i -> GPU i mod G)
-    ids = [(rank + world * k) % (FRAMES_PER_GPU * 8) for k in range(F)]
+    # frame-wise sharding, weak scaling: every rank segments its own 256-frame C2 batch (the same
+    # camera sweep, rank-specific noise seeds), no data-path collective
+    ids = [rank * FRAMES_PER_GPU + k for k in range(F)]
     host = torch.from_numpy(gen_frames(ids)).pin_memory()           # [F, N, 3] pinned
     dev_xyz = host.to("cuda", non_blocking=False)
     out_normals = torch.empty((F, N_PTS, 3), dtype=torch.float32).pin_memory()

@@ -94,12 +94,15 @@ def c1(rows=480, cols=640):
     return depth_frame(rows, cols, seed=1234)
 
 
-def c2_frame(i, n_frames=256, rows=480, cols=640):
-    """Frame i of the C2 batch."""
+def c2_frame(i, n_frames=256, rows=480, cols=640, replica=0):
+    """Frame i of the C2 batch.  replica > 0: the same camera sweep and box
+    jitter with other noise / dropout seeds (the batches of the other GPUs in a weak-scaling
+    run: same workload per GPU, different data)."""
     jit = np.random.default_rng(99).uniform(-0.2, 0.2, size=(n_frames, 3, 2))
+    i = i % n_frames
     yaw = -20.0 + 40.0 * i / max(n_frames - 1, 1)
-    return depth_frame(rows, cols, seed=1234 + 2 * i, yaw_deg=yaw,
-                       box_jitter=jit[i % n_frames])
+    return depth_frame(rows, cols, seed=1234 + 2 * i + 100000 * replica, yaw_deg=yaw,
+                       box_jitter=jit[i])
 
 
 def c2_batch(n_frames=256, rows=480, cols=640, distinct=None):
