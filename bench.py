@@ -180,7 +180,7 @@ def run_reference(args, rank, world):
         return
     import multiprocessing as mp
     cores = os.cpu_count() or 1
-    sample = min(FRAMES_PER_GPU, 4 * cores)
+    sample = min(FRAMES_PER_GPU, int(os.environ.get("PCSEG_BENCH_REF_SAMPLE", 4 * cores)))  # frames per step
     kind = cpu_kind()
     global _FRAMES
     _FRAMES = gen_frames(list(range(sample)))
