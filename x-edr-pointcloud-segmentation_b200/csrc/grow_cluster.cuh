@@ -138,25 +138,25 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
             }
           }
         } else {
-          int s = 0;
-          for (int dc = -h; dc <= h; ++dc) {
-            int L[7];
+          // window slots in groups of kG: the label probes of a group are in flight together
+          constexpr int kG = 12;
+          const int nslots = side * side - 1;
+          for (int s0 = 0; s0 < nslots; s0 += kG) {
+            int L[kG], nn[kG];
 #pragma unroll
-            for (int j = 0; j < 7; ++j) {
-              const int dr = j - h;
-              const int cc = col + dc, rc = row + dr;
-              const bool in = j < side && !(dc == 0 && dr == 0) && cc >= 0 && cc < cols && rc >= 0 && rc < rows;
-              L[j] = in ? labels[cc * rows + rc] : 0;
+            for (int k = 0; k < kG; ++k) {
+              const int sl = s0 + k;
+              const int cell = sl + (sl >= (side * side) / 2 ? 1 : 0);  // skip the centre
+              const int cc = col + cell / side - h, rc = row + cell % side - h;
+              const bool in = sl < nslots && cc >= 0 && cc < cols && rc >= 0 && rc < rows;
+              nn[k] = in ? cc * rows + rc : -1;
+              L[k] = in ? labels[nn[k]] : 0;
             }
 #pragma unroll
-            for (int j = 0; j < 7; ++j) {
-              const int dr = j - h;
-              if (j < side && !(dc == 0 && dr == 0)) {
-                if (L[j] == kUnlabeled || (L[j] <= kRejBase && (kRejBase - L[j]) < tid)) {
-                  el |= 1ull << s;
-                  atomicMin(claim + (col + dc) * rows + (row + dr), tid * 64 + s);
-                }
-                ++s;
+            for (int k = 0; k < kG; ++k) {
+              if (nn[k] >= 0 && (L[k] == kUnlabeled || (L[k] <= kRejBase && (kRejBase - L[k]) < tid))) {
+                el |= 1ull << (s0 + k);
+                atomicMin(claim + nn[k], tid * 64 + s0 + k);
               }
             }
           }
@@ -179,13 +179,27 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
             if (cv[s] == tid * 64 + s) win |= 1ull << s;
         } else {
           unsigned long long e = el;
-          while (e) {
-            const int s = __ffsll((long long)e) - 1;
-            e &= e - 1;
-            const int cell = s + (s >= (side * side) / 2 ? 1 : 0);  // skip the centre
-            const int dc = cell / side - h, dr = cell % side - h;
-            const int n = (col + dc) * rows + (row + dr);
-            if (vclaim[n] == tid * 64 + s) win |= 1ull << s;
+          while (e) {  // claim read-back, 8 claimed slots per round trip
+            int ss[8], cv[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              ss[k] = -1;
+              if (e) {
+                ss[k] = __ffsll((long long)e) - 1;
+                e &= e - 1;
+              }
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              cv[k] = -1;
+              if (ss[k] >= 0) {
+                const int cell = ss[k] + (ss[k] >= (side * side) / 2 ? 1 : 0);  // skip the centre
+                cv[k] = vclaim[(col + cell / side - h) * rows + (row + cell % side - h)];
+              }
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+              if (ss[k] >= 0 && cv[k] == tid * 64 + ss[k]) win |= 1ull << ss[k];
           }
         }
       }
