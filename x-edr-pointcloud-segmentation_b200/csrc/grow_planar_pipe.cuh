@@ -14,17 +14,22 @@
 //                bit can differ (plane change x point magnitude < the chunk's
 //                distance margin, fp32 error included) or else re-evaluates the
 //                chunk; identical accept bits => identical chunk, the chunk is
-//                VERIFIED (else A rolls back to it).  Only verified chunks are
-//                expanded, so nothing speculative ever reaches memory.
+//                VERIFIED, else A rolls S and B back to it (stop-the-world: epoch
+//                counter, acknowledged by both) and resumes with the true plane.
 //   warp 1  "S"  adds the moments of the chunks' inliers in FIFO order
-//                (sequential fp32) and posts the sums of every re-fit.
-//   warps 4-7 "B" expand verified chunks in order, one (entry, slot) pair per
-//                thread: labels, inlier list, neighbour tests against the 1-bit
-//                mask, min-key claims, ordered enqueue with cp.async prefetch of
-//                the xyz into the ring.
-//   5 warps  "R" each owns one re-fit slot: est_raw (centroid, covariance,
-//                eigen-solve) of posted sums.  The only part of ComputePlane
-//                that depends on the previous plane (eigenvector sign,
+//                (sequential fp32) and posts the sums of every re-fit; keeps a
+//                snapshot of the sums per chunk record for the roll-back.
+//   warps 4-7 "B" expand the chunks A has written, verified or not, up to four
+//                records (128 queue entries) per pass, one entry with its four
+//                neighbour slots per thread: labels, inlier list, neighbour tests
+//                against the 1-bit mask, min-key claims, ordered enqueue with
+//                cp.async prefetch of the xyz into the ring.  The queue tail before
+//                each record's enqueues is the undo log of a roll-back (appended
+//                cells get their mask bit back, rejected entries lose theirs,
+//                accepted entries become kUnlabeled again).
+//   kPipeDW warps "R" (2, 3 and 8 ..): each owns one re-fit slot: est_raw (centroid,
+//                covariance, eigen-solve) of posted sums.  The only part of
+//                ComputePlane that depends on the previous plane (eigenvector sign,
 //                ps/plane_estimator.cc:208-216) is applied by A in order.
 //
 // Chunking is invisible to the semantics (the FIFO is popped entry by entry in
