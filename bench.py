@@ -220,7 +220,16 @@ def main():
     ap.add_argument("--depth", type=int, default=4, choices=[1, 2, 3, 4],
                     help="batch workspaces in flight per GPU (2: pcseg_batch_submit/wait, the copies and the "
                          "normals stage of one batch overlap the growth stages of the other; 1: synchronous)")
+    ap.add_argument("--secondary", action="store_true",
+                    help="instead of the bench line: one-frame timings of configs C3, C4, C5 with the CPU "
+                         "checker timed beside them (tools/bench_configs.py)")
     args = ap.parse_args()
+    if args.secondary:
+        import runpy
+        import oracle
+        runpy.run_path(os.path.join(ROOT, "tools", "bench_configs.py"), init_globals={"CPU_BASELINE_MODULE": oracle},
+                       run_name="__main__")
+        return
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
     rank = int(os.environ.get("RANK", "0"))

@@ -1,13 +1,15 @@
 """Secondary timings (not the bench line): configs C3, C4, C5 at full size on one GPU, device
-time with CUDA events around the C-ABI calls (inputs resident in HBM), and the CPU oracle
-(single thread) beside them.  Prints one JSON object."""
+time with CUDA events around the C-ABI calls.  Run through `python bench.py --secondary`, which
+passes the CPU checker in for the cpu_baseline columns (this file itself never touches oracle/);
+run directly it reports the GPU side only.  Prints one JSON object."""
 import json, os, sys, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "x-edr-pointcloud-segmentation_b200"))
-sys.path.insert(0, os.path.join(ROOT, "oracle"))
 import numpy as np
 import torch
-import oracle, pcseg, synth
+import pcseg, synth
+
+cpu_ref = globals().get("CPU_BASELINE_MODULE")  # injected by bench.py --secondary
 
 ctx = pcseg.Context(0)
 stream = torch.cuda.ExternalStream(ctx.stream)
@@ -51,9 +53,10 @@ labels = np.full(N, -1, np.int32)
 t_p = gpu_ms(lambda: ctx.segment_planar(xyz, nrm, rows, cols, seeds, labels), reps=3)
 g_lab, g_r = ctx.segment_planar(xyz, nrm, rows, cols, seeds, labels)
 t_c = gpu_ms(lambda: ctx.segment_cluster(xyz, rows, cols, seeds, g_lab, id_offset=g_r.n), reps=3)
-c_n = cpu_ms(lambda: oracle.normals_organized(xyz, rows, cols))
-c_p = cpu_ms(lambda: oracle.segment_planar(xyz, nrm, rows, cols, seeds, labels))
-c_c = cpu_ms(lambda: oracle.segment_cluster(xyz, rows, cols, seeds, g_lab, id_offset=g_r.n))
+NA = float("nan")
+c_n = cpu_ms(lambda: cpu_ref.normals_organized(xyz, rows, cols)) if cpu_ref else NA
+c_p = cpu_ms(lambda: cpu_ref.segment_planar(xyz, nrm, rows, cols, seeds, labels)) if cpu_ref else NA
+c_c = cpu_ms(lambda: cpu_ref.segment_cluster(xyz, rows, cols, seeds, g_lab, id_offset=g_r.n)) if cpu_ref else NA
 out["C3_1280x720"] = {"points": N, "planes": int(g_r.n), "gpu_ms": {"normals": t_n, "planar": t_p, "cluster": t_c},
                       "cpu_port_ms": {"normals": c_n, "planar": c_p, "cluster": c_c},
                       "gpu_Mpts_s": N / (t_n + t_p + t_c) / 1e3, "cpu_Mpts_s": N / (c_n + c_p + c_c) / 1e3,
@@ -64,7 +67,7 @@ xyz, labels = synth.c4(rows=rows, cols=cols, n_objects=24); N = rows * cols
 d_xyz = dev(xyz); seeds = np.arange(N - 1, -1, -1, dtype=np.int32)
 cfg = dict(squared_distance_threshold=0.25, half_search_window=2, min_region_inliers=10)
 t_c = gpu_ms(lambda: ctx.segment_cluster(xyz, rows, cols, seeds, labels, cfg=cfg), reps=3)
-c_c = cpu_ms(lambda: oracle.segment_cluster(xyz, rows, cols, seeds, labels, cfg=oracle.default_cluster_config(**cfg)))
+c_c = cpu_ms(lambda: cpu_ref.segment_cluster(xyz, rows, cols, seeds, labels, cfg=cpu_ref.default_cluster_config(**cfg))) if cpu_ref else NA
 out["C4_lidar_2M"] = {"points": N, "gpu_ms": {"cluster": t_c}, "cpu_port_ms": {"cluster": c_c},
                       "gpu_Mpts_s": N / t_c / 1e3, "cpu_Mpts_s": N / c_c / 1e3}
 # ---- C5 ----
@@ -75,7 +78,7 @@ d_modes = torch.empty((N, 8), dtype=torch.float32, device="cuda")
 t_m = gpu_ms(lambda: ctx._check(L.pcseg_mean_shift_modes(ctx.h, VP(d_xyz.data_ptr()), rows, cols, VP(d_lab.data_ptr()), 5,
                                                          VP(d_modes.data_ptr()))))
 t_full = gpu_ms(lambda: ctx.mean_shift(xyz, rows, cols, labels, iterations=5), reps=2)
-c_full = cpu_ms(lambda: oracle.mean_shift(xyz, rows, cols, labels, iterations=5))
+c_full = cpu_ms(lambda: cpu_ref.mean_shift(xyz, rows, cols, labels, iterations=5)) if cpu_ref else NA
 n_seeds = int((~np.isnan(xyz[:, 0])).sum())
 out["C5_meanshift_10M"] = {"points": N, "seeds": n_seeds, "gpu_ms": {"modes_kernel": t_m, "sliding_mean_shift_total": t_full},
                            "cpu_port_ms": {"sliding_mean_shift_total": c_full},
