@@ -21,6 +21,11 @@ host_test: tests/host/clustering_host_test
 tests/host/clustering_host_test: tests/host/clustering_host_test.cc $(PKG)/host/pcseg_host.h include/pcseg_b200.h $(PKG)/libpcseg_b200.so
 	$(CXX) -std=c++17 -O2 -Wall -Iinclude -I$(PKG)/host -o $@ $< -L$(PKG) -lpcseg_b200 -Wl,-rpath,'$$ORIGIN/../../$(PKG)'
 
+# diagnostics build with the per-role cycle counters (tools/probe_prof.py loads it through PCSEG_LIB)
+prof: build/libpcseg_prof.so
+build/libpcseg_prof.so: $(CSRC)/pcseg_api.cu $(wildcard $(CSRC)/*.cuh) include/pcseg_b200.h
+	mkdir -p build && $(NVCC) $(NVFLAGS) -DPCSEG_PROFILE -o $@ $(CSRC)/pcseg_api.cu
+
 clean:
 	rm -f $(PKG)/libpcseg_b200.so; $(MAKE) -C oracle clean
-.PHONY: all lib oracle clean host_test
+.PHONY: all lib oracle clean host_test prof

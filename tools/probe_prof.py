@@ -1,4 +1,4 @@
-"""GPU probe (PCSEG_PROFILE build): per-role cycle breakdown of planar growth."""
+"""GPU probe (PCSEG_PROFILE build, `make prof`): per-role cycle breakdown of planar growth."""
 import os, sys, json
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 os.environ["PCSEG_LIB"] = os.path.join(ROOT, "build", "libpcseg_prof.so")
