@@ -37,7 +37,9 @@ struct ClusterArgs {
 // CTA must call).  Used by cluster_grow_kernel and, fused behind a frame's planar
 // stage, by planar_grow_kernel (a frame's stages are sequential, different
 // frames are independent: fusing removes the batch-wide barrier between them).
-template <int BLOCK>
+// H1 = true: instantiation for half_search_window == 1 (the default; 8 neighbours, lean register
+// allocation so that two CTAs share an SM); H1 = false: any window up to h = 3.
+template <int BLOCK, bool H1>
 __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, int id_offset, int* s_warp) {
   const int tid = threadIdx.x;
   const int rows = a.rows, cols = a.cols;
@@ -49,7 +51,7 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
   volatile int* vclaim = claim;
   int* inliers = a.inliers + (size_t)f * N;
   ClusterMeta* meta = a.meta + (size_t)f * a.rcap;
-  const int h = a.half_window;
+  const int h = H1 ? 1 : a.half_window;
   const int side = 2 * h + 1;
 
   int seed_pos = a.n_seeds;  // seeds are consumed back to front
@@ -120,7 +122,7 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
       unsigned long long el = 0ull;
       const int row = cand % rows, col = cand / rows;
       if (acc) {
-        if (h == 1) {
+        if (H1) {
           int L[8], nn[8];
 #pragma unroll
           for (int s = 0; s < 8; ++s) {
@@ -166,7 +168,7 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
       if (mine && !acc) labels[cand] = kUnlabeled;  // ps/cluster_region.h:105
       unsigned long long win = 0ull;
       if (acc) {
-        if (h == 1) {
+        if (H1) {
           int cv[8];
 #pragma unroll
           for (int s = 0; s < 8; ++s) {
@@ -255,11 +257,11 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
   }
 }
 
-template <int BLOCK>
-__global__ void __launch_bounds__(BLOCK) cluster_grow_kernel(ClusterArgs a) {
+template <int BLOCK, bool H1>
+__global__ void __launch_bounds__(BLOCK, H1 ? 2 : 1) cluster_grow_kernel(ClusterArgs a) {
   __shared__ int s_warp[BLOCK / 32 + 1];
   const int f = blockIdx.x;
-  cluster_grow_frame<BLOCK>(a, f, a.id_offset_from_planar ? a.stats[f].n_planar : a.id_offset, s_warp);
+  cluster_grow_frame<BLOCK, H1>(a, f, a.id_offset_from_planar ? a.stats[f].n_planar : a.id_offset, s_warp);
 }
 
 }  // namespace pcseg

@@ -326,7 +326,8 @@ int run_cluster(pcseg_batch* b, const float* xyz_dev, const int* seeds_dev, int 
   ClusterArgs a;
   int st = make_cluster_args(b, xyz_dev, seeds_dev, n_seeds, cfg, id_offset, offset_from_planar, &a);
   if (st) return st;
-  cluster_grow_kernel<kClusterBlock><<<b->n_frames, kClusterBlock, 0, c->stream>>>(a);
+  if (a.half_window == 1) cluster_grow_kernel<kClusterBlock, true><<<b->n_frames, kClusterBlock, 0, c->stream>>>(a);
+  else cluster_grow_kernel<kClusterBlock, false><<<b->n_frames, kClusterBlock, 0, c->stream>>>(a);
   ++c->launches;
   CU_TRY(c, cudaGetLastError());
   return PCSEG_OK;

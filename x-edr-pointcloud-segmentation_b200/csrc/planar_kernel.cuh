@@ -334,7 +334,8 @@ __global__ void PLANAR_REG_ATTR planar_grow_kernel(PlanarArgs a, ClusterArgs ca)
   }
   if constexpr (FUSE) {
     __syncthreads();  // the frame's labels (written by this CTA) are final
-    cluster_grow_frame<BLOCK>(ca, f, nreg, s_warp);
+    if (ca.half_window == 1) cluster_grow_frame<BLOCK, true>(ca, f, nreg, s_warp);
+    else cluster_grow_frame<BLOCK, false>(ca, f, nreg, s_warp);
 #ifdef PCSEG_PROFILE
     if (tid == 0 && a.prof) a.prof[(size_t)f * 16 + 7] = clock64() - kp_planar_end;  // fused cluster stage, cycles
 #endif
