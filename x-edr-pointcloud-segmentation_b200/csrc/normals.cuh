@@ -132,8 +132,12 @@ __device__ __forceinline__ void store_nan3(float* normals, float* curvature, int
 #ifndef NORMALS_MIN_BLOCKS
 #define NORMALS_MIN_BLOCKS 6  // 40 registers: measured 10.0 -> 9.0 ms on the C2 batch (more warps to cover the walk loads)
 #endif
+#ifndef NORMALS_BLOCK
+#define NORMALS_BLOCK 128  // small CTAs: one fits beside two resident planar-growth CTAs (9 K registers left)
+#endif
+constexpr int kNormalsBlock = NORMALS_BLOCK;
 template <bool CHK>
-__global__ void __launch_bounds__(256, NORMALS_MIN_BLOCKS) normals_kernel(NormalsArgs a) {
+__global__ void __launch_bounds__(kNormalsBlock, NORMALS_MIN_BLOCKS * 256 / kNormalsBlock) normals_kernel(NormalsArgs a) {
   const int nr = a.r1 - a.r0;
   const int nc = a.c1 - a.c0;
   const int t = blockIdx.x * blockDim.x + threadIdx.x;

@@ -234,9 +234,9 @@ int run_normals(pcseg_batch* b, const float* xyz_dev, float* normals_dev, float*
   a.inv_cap = kInvCap;
   CU_TRY(c, cudaMemsetAsync(a.inv_count, 0, nf * sizeof(int), c->stream));
   const int work = (r1 - r0) * (c1 - c0);
-  dim3 grid((work + 255) / 256, nf);
-  if (a.max2 <= FLT_MAX) normals_kernel<false><<<grid, 256, 0, c->stream>>>(a);
-  else normals_kernel<true><<<grid, 256, 0, c->stream>>>(a);  // max distance inf/NaN: explicit allFinite() test
+  dim3 grid((work + kNormalsBlock - 1) / kNormalsBlock, nf);
+  if (a.max2 <= FLT_MAX) normals_kernel<false><<<grid, kNormalsBlock, 0, c->stream>>>(a);
+  else normals_kernel<true><<<grid, kNormalsBlock, 0, c->stream>>>(a);  // max distance inf/NaN: explicit allFinite() test
   normals_fixup_kernel<<<nf, 256, 0, c->stream>>>(a);
   c->launches += 2;
   CU_TRY(c, cudaGetLastError());
