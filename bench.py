@@ -263,8 +263,17 @@ def main():
     D = args.depth
     batches = [pcseg.Batch(ctx, F, ROWS, COLS) for _ in range(D)]
     batch = batches[0]
-    out_normals = [out_normals] + [torch.empty((F, N_PTS, 3), dtype=torch.float32).pin_memory() for _ in range(D - 1)]
-    out_labels = [out_labels] + [torch.empty((F, N_PTS), dtype=torch.int32).pin_memory() for _ in range(D - 1)]
+    out_normals, out_labels = [out_normals], [out_labels]
+    try:  # one pinned output set per workspace; a host that cannot pin that much runs with fewer in flight
+        for _ in range(D - 1):
+            out_normals.append(torch.empty((F, N_PTS, 3), dtype=torch.float32).pin_memory())
+            out_labels.append(torch.empty((F, N_PTS), dtype=torch.int32).pin_memory())
+    except RuntimeError:
+        D = min(len(out_normals), len(out_labels))
+        out_normals, out_labels = out_normals[:D], out_labels[:D]
+        for b in batches[D:]:
+            b.close()
+        batches = batches[:D]
     mode = pcseg.SEEDS_ALL_DESCENDING if args.seed_mode == "alldesc" else pcseg.SEEDS_PLANE_SUPPORT
     params = pcseg.pipeline_params(seed_mode=mode, run_cluster=True)
     stream = torch.cuda.ExternalStream(batch.stream)
