@@ -210,6 +210,86 @@ int pcseg_batch_regions(pcseg_batch*, int frame, int kind, pcseg_regions** out);
 int* pcseg_batch_device_labels(pcseg_batch*);
 float* pcseg_batch_device_normals(pcseg_batch*);
 
+/* ---- Batched region results: everything a PlanarRegion / ClusterRegion holds
+ * (ps/planar_region.h:427-450, ps/cluster_region.h:161-168) for ALL frames of a
+ * batch, packed on the device (one pass) and copied with one transfer per array.
+ * With want_inlier_xyz / want_boundary_xyz the gathers of
+ * CreatePlanarDetectedObjectProto (ps/detected_objects.cc:21-48: inlier xyz in
+ * inlier order, discontinuous boundary index -> position in that list) and
+ * CreateClusterDetectedObjectProto (ps/detected_objects.h:62-74) run on the
+ * device too.  Region r of the batch: frame-major, region order within a frame =
+ * the order SegmentRegions pushed them (ps/segmentation.h:278). ---- */
+typedef struct {
+  int frame, label_id, seed_index;
+  int inlier_begin, inlier_count;        /* into planar_inlier_indices / planar_inlier_xyz */
+  int boundary_begin, boundary_count;    /* into boundary_indices / boundary_xyz / boundary_discontinuous */
+  int discontinuous_begin, discontinuous_count; /* into discontinuous_indices / discontinuous_positions */
+  int hull_begin, hull_count;            /* into hull_points (projected_boundary_points_) */
+  float plane[4];                        /* normal xyz, offset */
+  float centroid[3];
+  float area;
+  float estimator[10];                   /* PlaneEstimator: 6 second moments, sum xyz, weight */
+} pcseg_planar_record;
+
+typedef struct {
+  int frame, label_id;
+  int inlier_begin, inlier_count;        /* into cluster_inlier_indices / cluster_inlier_xyz */
+  /* extension outputs (no reference field): centroid = sum of the inlier points / count, lane-strided
+   * double sums; axis-aligned extent */
+  float centroid[3];
+  float bbox_min[3], bbox_max[3];
+} pcseg_cluster_record;
+
+typedef struct {
+  /* in: which optional gathers to run */
+  int want_inlier_xyz;    /* planar_inlier_xyz, cluster_inlier_xyz */
+  int want_boundary_xyz;  /* boundary_xyz */
+  int want_hull;          /* hull_points */
+  int want_cluster_stats; /* centroid / bbox of pcseg_cluster_record (else zero) */
+  /* in: caller buffers (host -- pinned for overlap -- or device) and their capacities in
+   * ELEMENTS (records, indices, points).  A null buffer skips that array. */
+  int* frame_stats;                      /* [F][8], as pcseg_batch_frame_stats */
+  int* frame_offsets;                    /* [5][F+1] exclusive prefix sums over frames of: planar regions,
+                                            planar inliers, boundary entries, cluster regions, cluster inliers */
+  pcseg_planar_record* planar;           int planar_cap;
+  int* planar_inlier_indices;            int planar_inlier_cap;
+  float* planar_inlier_xyz;              /* 3 per inlier, same capacity */
+  int* boundary_indices;                 int boundary_cap;
+  float* boundary_xyz;                   /* 3 per boundary entry */
+  unsigned char* boundary_discontinuous; /* flag per boundary entry (ps/planar_region.h:360-417) */
+  int* discontinuous_indices;            /* cloud index, ascending position in the inlier list; capacity boundary_cap;
+                                            a region's entries start at discontinuous_begin (= its boundary_begin) */
+  int* discontinuous_positions;          /* position in the region's inlier list (ps/detected_objects.cc:41-45) */
+  float* hull_points;                    /* 3 per hull vertex; capacity boundary_cap; hull_begin = boundary_begin */
+  pcseg_cluster_record* cluster;         int cluster_cap;
+  int* cluster_inlier_indices;           int cluster_inlier_cap;
+  float* cluster_inlier_xyz;
+  /* out (valid after pcseg_batch_wait): totals over the batch */
+  int n_planar, n_planar_inliers, n_boundary, n_cluster, n_cluster_inliers;
+  int error_flags;                       /* OR over frames of FrameStats.error_flags */
+} pcseg_batch_results;
+
+/* pcseg_batch_submit + region results: `results` (and every buffer it names) must stay valid until
+ * pcseg_batch_wait returns; wait fills the totals and returns PCSEG_ERR_CAPACITY when a caller
+ * buffer was too small (totals are still filled in, nothing is written past a capacity). */
+int pcseg_batch_submit_regions(pcseg_batch*, const float* xyz,
+                               const pcseg_pipeline_params* params, float* normals_out,
+                               int* labels_out, pcseg_batch_results* results);
+
+/* Replaces MultichannelCloud::TransformInPlace (ps/multichannel_cloud.cc:53-68): points <- pose * point,
+ * normals <- rotationMatrix(pose) * normal, with new_pose_current = (quaternion xyzw, translation) given
+ * in double and cast to float first (Pose3d::cast<float>, :55).  Either array may be null. */
+int pcseg_transform_in_place(pcseg_ctx*, float* points_xyz, float* normals_xyz, int n,
+                             const double q_xyzw[4], const double translation[3]);
+
+/* The gather of CreateClusterDetectedObjectProto (ps/detected_objects.h:62-74) /
+ * CreatePlanarDetectedObjectProto (ps/detected_objects.cc:36-46) for one index list:
+ * out_xyz[k] = xyz[indices[k]]; discontinuous (nullable, sorted or not) ->
+ * positions_out[j] ascending = positions k whose index is in the set; *n_positions = count. */
+int pcseg_gather_points(pcseg_ctx*, const float* xyz, int n_points, const int* indices, int n_indices,
+                        float* out_xyz, const int* discontinuous, int n_discontinuous,
+                        int* positions_out, int* n_positions);
+
 /* ---- Result accessors (host pointers valid until pcseg_regions_free).
  * Mirror PlanarRegion's accessors (ps/planar_region.h:427-450) and
  * ClusterRegion's (ps/cluster_region.h:161-168) as CSR arrays. ---- */
@@ -225,7 +305,7 @@ const float* pcseg_regions_estimators(const pcseg_regions*);          /* 10n: ac
 const int* pcseg_regions_boundary_offsets(const pcseg_regions*);      /* n+1 */
 const int* pcseg_regions_boundary_indices(const pcseg_regions*);
 const int* pcseg_regions_discontinuous_offsets(const pcseg_regions*); /* n+1 */
-const int* pcseg_regions_discontinuous_indices(const pcseg_regions*); /* sorted set */
+const int* pcseg_regions_discontinuous_indices(const pcseg_regions*); /* a set, listed in inlier order */
 const int* pcseg_regions_hull_offsets(const pcseg_regions*);          /* n+1 (points) */
 const float* pcseg_regions_hull_points(const pcseg_regions*);         /* xyz */
 const float* pcseg_regions_seed_points(const pcseg_regions*);         /* 3n (mean shift) */

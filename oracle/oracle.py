@@ -342,3 +342,28 @@ def seeds_average_normals(xyz, normals, rows, cols, neighborhood_size=5,
     if n < 0:
         raise ValueError("oracle_seeds_average_normals status %d" % n)
     return out[:n].copy()
+
+
+def port_lib():
+    """The restatement (liboracle.so) even inside `with reference():` -- for functions the
+    shim-compiled reference build does not export."""
+    global _LIB
+    if _LIB is None:
+        so = os.path.join(_HERE, "liboracle.so")
+        if not os.path.exists(so):
+            build()
+        _LIB = _bind(so)
+    return _LIB
+
+
+def transform_in_place(points, normals, q_xyzw, translation):
+    """ps/multichannel_cloud.cc:53-68; returns transformed copies (either may be None)."""
+    L = port_lib()
+    p = _f32(points).copy() if points is not None else None
+    n = _f32(normals).copy() if normals is not None else None
+    cnt = (p if p is not None else n).reshape(-1, 3).shape[0]
+    q = (C.c_double * 4)(*[float(v) for v in q_xyzw])
+    t = (C.c_double * 3)(*[float(v) for v in translation])
+    L.oracle_transform_in_place(_ptr(p, F32P) if p is not None else None,
+                                _ptr(n, F32P) if n is not None else None, cnt, q, t)
+    return p, n

@@ -1339,6 +1339,36 @@ int oracle_seeds_average_normals(const float* xyz, const float* normals,
   return k;
 }
 
+// MultichannelCloud::TransformInPlace, ps/multichannel_cloud.cc:53-68.  Pose3d::cast<float>() first
+// (:55); points: Pose3f * p = q * p + t (eigenmath::Pose3, x_edr_eigenmath 1.0.0, restated:
+// Eigen quaternion-vector product, then + translation); normals: rotationMatrix() * n with Eigen's
+// Quaternion::toRotationMatrix and the fixed-size 3-term reduction e0 + (e1 + e2).
+void oracle_transform_in_place(float* points, float* normals, int n, const double q_xyzw[4], const double t[3]) {
+  const Quat q{(float)q_xyzw[0], (float)q_xyzw[1], (float)q_xyzw[2], (float)q_xyzw[3]};
+  const V3 tr{(float)t[0], (float)t[1], (float)t[2]};
+  const float tx = 2.0f * q.x, ty = 2.0f * q.y, tz = 2.0f * q.z;
+  const float twx = tx * q.w, twy = ty * q.w, twz = tz * q.w;
+  const float txx = tx * q.x, txy = ty * q.x, txz = tz * q.x;
+  const float tyy = ty * q.y, tyz = tz * q.y, tzz = tz * q.z;
+  const float r00 = 1.0f - (tyy + tzz), r01 = txy - twz, r02 = txz + twy;
+  const float r10 = txy + twz, r11 = 1.0f - (txx + tzz), r12 = tyz - twx;
+  const float r20 = txz - twy, r21 = tyz + twx, r22 = 1.0f - (txx + tyy);
+  for (int i = 0; i < n; ++i) {
+    if (points) {
+      float* p = points + 3 * (size_t)i;
+      const V3 w = rotate(q, V3{p[0], p[1], p[2]}) + tr;
+      p[0] = w.x; p[1] = w.y; p[2] = w.z;
+    }
+    if (normals) {
+      float* p = normals + 3 * (size_t)i;
+      const V3 v{p[0], p[1], p[2]};
+      p[0] = r00 * v.x + (r01 * v.y + r02 * v.z);
+      p[1] = r10 * v.x + (r11 * v.y + r12 * v.z);
+      p[2] = r20 * v.x + (r21 * v.y + r22 * v.z);
+    }
+  }
+}
+
 int oracle_regions_count(const oracle_regions* r) { return r->count(); }
 const int* oracle_regions_inlier_offsets(const oracle_regions* r) { return r->inlier_offsets.data(); }
 const int* oracle_regions_inlier_indices(const oracle_regions* r) { return r->inlier_indices.data(); }

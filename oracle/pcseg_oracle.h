@@ -122,6 +122,11 @@ int oracle_seeds_average_normals(const float* xyz, const float* normals,
                                  float min_avg_normal_length, int* seeds_out,
                                  int cap);
 
+/* ps/multichannel_cloud.cc:53-68 MultichannelCloud::TransformInPlace (either array nullable).
+ * Port only: the reference's class needs the generated proto headers. */
+void oracle_transform_in_place(float* points, float* normals, int n,
+                               const double q_xyzw[4], const double t[3]);
+
 /* Result accessors (pointers valid until oracle_regions_free). */
 int oracle_regions_count(const oracle_regions*);
 const int* oracle_regions_inlier_offsets(const oracle_regions*);   /* n+1 */

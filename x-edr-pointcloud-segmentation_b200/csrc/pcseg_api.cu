@@ -19,6 +19,7 @@
 #include "meanshift_grow.cuh"
 #include "normals.cuh"
 #include "seeds.cuh"
+#include "results_pack.cuh"
 
 using namespace pcseg;
 
@@ -69,7 +70,6 @@ struct pcseg_ctx {
   // host<->device copies of the batched pipeline run on their own streams so that they
   // overlap the kernels (chunked H2D under the normals stage, normals D2H under growth)
   cudaStream_t copy_in = nullptr, copy_out = nullptr;
-  std::vector<cudaEvent_t> chunk_ev;  // 2 per chunk: H2D done, normals done
 };
 
 struct pcseg_regions {
@@ -103,7 +103,19 @@ struct pcseg_batch {
   cudaStream_t own_stream = nullptr, own_copy_in = nullptr, own_copy_out = nullptr;
   bool in_flight = false, wait_copy_out = false;
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  std::vector<cudaEvent_t> chunk_ev;  // 2 per chunk (H2D done, normals done) + 2
   DevBuf prof;
+  // region results packed over the batch (results_pack.cuh); allocated on first use
+  DevBuf pk_offsets, pk_planar, pk_pinl, pk_pinl_xyz, pk_bnd, pk_bnd_xyz, pk_bdisc, pk_disc_idx, pk_disc_pos,
+      pk_hull, pk_cluster, pk_cinl, pk_cinl_xyz, pk_err;
+  int* h_meta = nullptr;               // pinned: [5][F+1] offsets, [F][8] stats, 1 pack error word
+  // what the run in flight was asked for (pcseg_batch_wait finishes it)
+  pcseg_pipeline_params run_params{};
+  std::vector<int> run_seeds;          // PCSEG_SEEDS_EXPLICIT list (host copy for a re-run)
+  bool run_valid = false;
+  int* run_labels_out = nullptr;
+  pcseg_batch_results* run_results = nullptr;
+  bool cluster_ran = false;
 };
 
 namespace {
@@ -129,13 +141,13 @@ bool is_device_ptr(const void* p) {
 }
 
 // Brings `bytes` at src (host or device) to the device; returns the device view.
-int to_device(pcseg_ctx* c, const void* src, size_t bytes, DevBuf* staging, const void** out) {
+int to_device(pcseg_ctx* c, const void* src, size_t bytes, DevBuf* staging, const void** out, cudaStream_t stream = nullptr) {
   if (is_device_ptr(src)) {
     *out = src;
     return PCSEG_OK;
   }
   CU_TRY(c, staging->ensure(bytes));
-  CU_TRY(c, cudaMemcpyAsync(staging->p, src, bytes, cudaMemcpyHostToDevice, c->stream));
+  CU_TRY(c, cudaMemcpyAsync(staging->p, src, bytes, cudaMemcpyHostToDevice, stream ? stream : c->stream));
   *out = staging->p;
   return PCSEG_OK;
 }
@@ -153,10 +165,16 @@ __global__ void fill_int_kernel(int* p, size_t n, int v) {
   for (; i < n; i += stride) p[i] = v;
 }
 
-int fill_int(pcseg_ctx* c, int* p, size_t n, int v) {
+// The stream set a workspace enqueues on: its own (pcseg_batch_create) or the context's.
+inline cudaStream_t S(const pcseg_batch* b) { return b->own_stream ? b->own_stream : b->ctx->stream; }
+inline cudaStream_t SIn(const pcseg_batch* b) { return b->own_copy_in ? b->own_copy_in : b->ctx->copy_in; }
+inline cudaStream_t SOut(const pcseg_batch* b) { return b->own_copy_out ? b->own_copy_out : b->ctx->copy_out; }
+
+int fill_int(pcseg_ctx* c, int* p, size_t n, int v, cudaStream_t stream = nullptr) {
   if (n == 0) return PCSEG_OK;
+  if (!stream) stream = c->stream;
   int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 8);
-  fill_int_kernel<<<blocks, 256, 0, c->stream>>>(p, n, v);
+  fill_int_kernel<<<blocks, 256, 0, stream>>>(p, n, v);
   ++c->launches;
   CU_TRY(c, cudaGetLastError());
   return PCSEG_OK;
@@ -167,6 +185,11 @@ int check_planar_cfg(const pcseg_planar_config* cfg) {
   // period <= 0 is UB, min_region_inliers < 1 makes NaN seeds emit stale regions.
   if (cfg->plane_model_reestimation_period <= 0 || cfg->min_region_inliers < 1) return PCSEG_ERR_CONFIG;
   return PCSEG_OK;
+}
+int planar_region_bound(const pcseg_batch* b, const pcseg_planar_config* cfg) {
+  // An accepted region has a boundary that spans more than 3 rows and 3 columns
+  // (ps/planar_region.cc:91-106) and is 4-connected, so it has at least 5 + 5 - 1 cells.
+  return (int)(b->N / (size_t)std::max(cfg->min_region_inliers, 9)) + 1;
 }
 int check_cluster_cfg(const pcseg_cluster_config* cfg) {
   if (cfg->min_region_inliers < 1 || cfg->half_search_window < 0) return PCSEG_ERR_CONFIG;
@@ -215,6 +238,7 @@ int run_normals(pcseg_batch* b, const float* xyz_dev, float* normals_dev, float*
                 const pcseg_normals_params* p, const double sensor_t[3], int r0, int r1, int c0, int c1,
                 int f0 = 0, int nf = -1) {
   pcseg_ctx* c = b->ctx;
+  cudaStream_t stream = S(b);
   if (r1 <= r0 || c1 <= c0) return PCSEG_OK;
   if (nf < 0) nf = b->n_frames - f0;
   if (nf <= 0) return PCSEG_OK;
@@ -232,12 +256,12 @@ int run_normals(pcseg_batch* b, const float* xyz_dev, float* normals_dev, float*
   a.inv_list = b->inv_list.as<int>() + (size_t)f0 * kInvCap;
   a.inv_count = b->inv_count.as<int>() + f0;
   a.inv_cap = kInvCap;
-  CU_TRY(c, cudaMemsetAsync(a.inv_count, 0, nf * sizeof(int), c->stream));
+  CU_TRY(c, cudaMemsetAsync(a.inv_count, 0, nf * sizeof(int), stream));
   const int work = (r1 - r0) * (c1 - c0);
   dim3 grid((work + kNormalsBlock - 1) / kNormalsBlock, nf);
-  if (a.max2 <= FLT_MAX) normals_kernel<false><<<grid, kNormalsBlock, 0, c->stream>>>(a);
-  else normals_kernel<true><<<grid, kNormalsBlock, 0, c->stream>>>(a);  // max distance inf/NaN: explicit allFinite() test
-  normals_fixup_kernel<<<nf, 256, 0, c->stream>>>(a);
+  if (a.max2 <= FLT_MAX) normals_kernel<false><<<grid, kNormalsBlock, 0, stream>>>(a);
+  else normals_kernel<true><<<grid, kNormalsBlock, 0, stream>>>(a);  // max distance inf/NaN: explicit allFinite() test
+  normals_fixup_kernel<<<nf, 256, 0, stream>>>(a);
   c->launches += 2;
   CU_TRY(c, cudaGetLastError());
   return PCSEG_OK;
@@ -269,6 +293,7 @@ int run_planar(pcseg_batch* b, const float* xyz_dev, const float* normals_dev, c
                int n_seeds, int seeds_stride, const int* n_seeds_dev, const pcseg_planar_config* cfg,
                const float q[4], int id_offset, const ClusterArgs* fuse_cluster = nullptr, bool* fused = nullptr) {
   pcseg_ctx* c = b->ctx;
+  cudaStream_t stream = S(b);
   if (fused) *fused = false;
   PlanarArgs a;
   a.xyz = xyz_dev; a.normals = normals_dev; a.labels = b->labels.as<int>();
@@ -306,14 +331,14 @@ int run_planar(pcseg_batch* b, const float* xyz_dev, const float* normals_dev, c
     while (smem > smem_max) { a.ring /= 2; smem = (size_t)a.mask_words * 4 + (size_t)a.ring * 20 + smem_fixed; }
     if (fuse_cluster && getenv("PCSEG_FUSE")) {  // opt-in: measured slower (the extra code thrashes the instruction cache)
       CU_TRY(c, cudaFuncSetAttribute(planar_grow_kernel<kPipeBlock, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      planar_grow_kernel<kPipeBlock, true, true><<<b->n_frames, kPipeBlock, smem, c->stream>>>(a, *fuse_cluster);
+      planar_grow_kernel<kPipeBlock, true, true><<<b->n_frames, kPipeBlock, smem, stream>>>(a, *fuse_cluster);
       if (fused) *fused = true;
     } else {
       CU_TRY(c, cudaFuncSetAttribute(planar_grow_kernel<kPipeBlock, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      planar_grow_kernel<kPipeBlock, true, false><<<b->n_frames, kPipeBlock, smem, c->stream>>>(a, ClusterArgs{});
+      planar_grow_kernel<kPipeBlock, true, false><<<b->n_frames, kPipeBlock, smem, stream>>>(a, ClusterArgs{});
     }
   } else {
-    planar_grow_kernel<kGrowBlock, false, false><<<b->n_frames, kGrowBlock, 0, c->stream>>>(a, ClusterArgs{});
+    planar_grow_kernel<kGrowBlock, false, false><<<b->n_frames, kGrowBlock, 0, stream>>>(a, ClusterArgs{});
   }
   ++c->launches;
   CU_TRY(c, cudaGetLastError());
@@ -323,11 +348,12 @@ int run_planar(pcseg_batch* b, const float* xyz_dev, const float* normals_dev, c
 int run_cluster(pcseg_batch* b, const float* xyz_dev, const int* seeds_dev, int n_seeds,
                 const pcseg_cluster_config* cfg, int id_offset, int offset_from_planar) {
   pcseg_ctx* c = b->ctx;
+  cudaStream_t stream = S(b);
   ClusterArgs a;
   int st = make_cluster_args(b, xyz_dev, seeds_dev, n_seeds, cfg, id_offset, offset_from_planar, &a);
   if (st) return st;
-  if (a.half_window == 1) cluster_grow_kernel<kClusterBlock, true><<<b->n_frames, kClusterBlock, 0, c->stream>>>(a);
-  else cluster_grow_kernel<kClusterBlock, false><<<b->n_frames, kClusterBlock, 0, c->stream>>>(a);
+  if (a.half_window == 1) cluster_grow_kernel<kClusterBlock, true><<<b->n_frames, kClusterBlock, 0, stream>>>(a);
+  else cluster_grow_kernel<kClusterBlock, false><<<b->n_frames, kClusterBlock, 0, stream>>>(a);
   ++c->launches;
   CU_TRY(c, cudaGetLastError());
   return PCSEG_OK;
@@ -339,66 +365,6 @@ int map_error_flags(pcseg_ctx* c, int flags) {
   return PCSEG_ERR_CAPACITY;
 }
 
-// Host-side PlanarConvexHull output for one accepted region (result formatting:
-// the acceptance gate "hull has >= 3 vertices" already ran on the device).
-// ps/algorithms.h:526-549 with patch P1; PoseFromPlane / ConvexHull restated
-// (third-party, absent from the reference tree) as in the kernel's plane frame.
-struct HV3 { float x, y, z; };
-inline HV3 hcross(HV3 a, HV3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
-inline HV3 hadd(HV3 a, HV3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
-inline float hdot(HV3 a, HV3 b) { return a.x * b.x + (a.y * b.y + a.z * b.z); }
-inline HV3 hrot(float qx, float qy, float qz, float qw, HV3 v) {
-  HV3 qv{qx, qy, qz};
-  HV3 uv = hcross(qv, v);
-  uv = hadd(uv, uv);
-  HV3 t{v.x + qw * uv.x, v.y + qw * uv.y, v.z + qw * uv.z};
-  return hadd(t, hcross(qv, uv));
-}
-void host_planar_hull(const float* boundary_xyz, int nb, const float plane[4], std::vector<float>* out) {
-  HV3 n{plane[0], plane[1], plane[2]};
-  HV3 v1 = n;
-  float z = hdot(n, n);
-  if (z > 0.0f) { float s = sqrtf(z); v1 = {n.x / s, n.y / s, n.z / s}; }
-  HV3 v0{0.0f, 0.0f, 1.0f};
-  float c = hdot(v1, v0);
-  float qx, qy, qz, qw;
-  if (c < -1.0f + FLT_EPSILON) { qx = 1.0f; qy = qz = qw = 0.0f; }
-  else {
-    HV3 axis = hcross(v0, v1);
-    float s = sqrtf((1.0f + c) * 2.0f);
-    float invs = 1.0f / s;
-    qx = axis.x * invs; qy = axis.y * invs; qz = axis.z * invs; qw = s * 0.5f;
-  }
-  HV3 t{-plane[3] * n.x, -plane[3] * n.y, -plane[3] * n.z};
-  HV3 rt = hrot(-qx, -qy, -qz, qw, t);
-  HV3 ti{-rt.x, -rt.y, -rt.z};
-  struct P2 { double x, y; };
-  std::vector<P2> pts(nb);
-  for (int i = 0; i < nb; ++i) {
-    HV3 p{boundary_xyz[3 * i], boundary_xyz[3 * i + 1], boundary_xyz[3 * i + 2]};
-    HV3 pp = hadd(hrot(-qx, -qy, -qz, qw, p), ti);
-    pts[i] = {pp.x, pp.y};
-  }
-  std::sort(pts.begin(), pts.end(), [](const P2& a, const P2& b) { return a.x < b.x || (a.x == b.x && a.y < b.y); });
-  pts.erase(std::unique(pts.begin(), pts.end(), [](const P2& a, const P2& b) { return a.x == b.x && a.y == b.y; }), pts.end());
-  std::vector<P2> h;
-  int m = (int)pts.size();
-  if (m < 3) h = pts;
-  else {
-    h.resize(2 * m);
-    int k = 0;
-    auto cr = [](const P2& o, const P2& a, const P2& b) { return (a.x - o.x) * (b.y - o.y) - (a.y - o.y) * (b.x - o.x); };
-    for (int i = 0; i < m; ++i) { while (k >= 2 && cr(h[k - 2], h[k - 1], pts[i]) <= 0) --k; h[k++] = pts[i]; }
-    for (int i = m - 2, t0 = k + 1; i >= 0; --i) { while (k >= t0 && cr(h[k - 2], h[k - 1], pts[i]) <= 0) --k; h[k++] = pts[i]; }
-    h.resize(k - 1);
-  }
-  for (const P2& p : h) {
-    HV3 pp{(float)p.x, (float)p.y, 0.0f};
-    HV3 w = hadd(hrot(qx, qy, qz, qw, pp), t);
-    out->push_back(w.x); out->push_back(w.y); out->push_back(w.z);
-  }
-}
-
 }  // namespace
 
 // ===========================================================================
@@ -406,87 +372,166 @@ void host_planar_hull(const float* boundary_xyz, int nb, const float plane[4], s
 // ===========================================================================
 namespace {
 
+// Packs the region results of frames [f0, f0 + nf) on the device (results_pack.cuh) and queues the
+// copy of the frame offsets / stats / pack error word into the workspace's pinned staging block.
+// Enqueued on the workspace's main stream behind the growth kernels.
+struct PackWant {
+  bool inlier_xyz = false, boundary_xyz = false, hull = false, cluster_stats = false, cluster = false;
+};
+
+int run_pack(pcseg_batch* b, int f0, int nf, const PackWant& w) {
+  pcseg_ctx* c = b->ctx;
+  cudaStream_t stream = S(b);
+  const size_t N = b->N, F = (size_t)nf;
+  const size_t ecap = F * (size_t)b->bcap;
+  CU_TRY(c, b->pk_offsets.ensure(5 * ((size_t)b->n_frames + 1) * sizeof(int)));
+  CU_TRY(c, b->pk_planar.ensure(F * (size_t)b->rcap_planar * sizeof(pcseg_planar_record)));
+  CU_TRY(c, b->pk_pinl.ensure(F * N * sizeof(int)));
+  if (w.inlier_xyz) CU_TRY(c, b->pk_pinl_xyz.ensure(F * N * 3 * sizeof(float)));
+  CU_TRY(c, b->pk_bnd.ensure(ecap * sizeof(int)));
+  if (w.boundary_xyz) CU_TRY(c, b->pk_bnd_xyz.ensure(ecap * 3 * sizeof(float)));
+  CU_TRY(c, b->pk_bdisc.ensure(ecap));
+  CU_TRY(c, b->pk_disc_idx.ensure(ecap * sizeof(int)));
+  CU_TRY(c, b->pk_disc_pos.ensure(ecap * sizeof(int)));
+  if (w.hull) CU_TRY(c, b->pk_hull.ensure(ecap * 3 * sizeof(float)));
+  if (w.cluster) {
+    CU_TRY(c, b->pk_cluster.ensure(F * (size_t)b->rcap_cluster * sizeof(pcseg_cluster_record)));
+    CU_TRY(c, b->pk_cinl.ensure(F * N * sizeof(int)));
+    if (w.inlier_xyz) CU_TRY(c, b->pk_cinl_xyz.ensure(F * N * 3 * sizeof(float)));
+  }
+  CU_TRY(c, b->pk_err.ensure(sizeof(int)));
+  if (!b->h_meta) CU_TRY(c, cudaMallocHost((void**)&b->h_meta, (5 * ((size_t)b->n_frames + 1) + 8 * (size_t)b->n_frames + 1) * sizeof(int)));
+  PackArgs a;
+  a.F = nf; a.N = (int)N; a.rows = b->rows;
+  a.xyz = b->xyz_dev + (size_t)f0 * N * 3;
+  a.stats = b->stats.as<FrameStats>() + f0;
+  a.meta_planar = b->meta_planar.as<PlanarMeta>() + (size_t)f0 * b->rcap_planar; a.rcap_planar = b->rcap_planar;
+  a.meta_cluster = w.cluster ? b->meta_cluster.as<ClusterMeta>() + (size_t)f0 * b->rcap_cluster : nullptr;
+  a.rcap_cluster = b->rcap_cluster;
+  a.inl_planar = b->inl_planar.as<int>() + (size_t)f0 * N;
+  a.inl_cluster = b->inl_cluster.as<int>() + (size_t)f0 * N;
+  a.boundary = b->boundary.as<int>() + (size_t)f0 * b->bcap;
+  a.bflags = b->bflags.as<unsigned char>() + (size_t)f0 * b->bcap; a.bcap = b->bcap;
+  a.scratch = b->queue.as<int>() + (size_t)f0 * b->qcap * 2; a.scratch_stride = (size_t)b->qcap * 2;
+  a.offsets = b->pk_offsets.as<int>();
+  a.planar = b->pk_planar.as<pcseg_planar_record>();
+  a.p_inl = b->pk_pinl.as<int>(); a.p_inl_xyz = w.inlier_xyz ? b->pk_pinl_xyz.as<float>() : nullptr;
+  a.bnd = b->pk_bnd.as<int>(); a.bnd_xyz = w.boundary_xyz ? b->pk_bnd_xyz.as<float>() : nullptr;
+  a.bnd_disc = b->pk_bdisc.as<unsigned char>();
+  a.disc_idx = b->pk_disc_idx.as<int>(); a.disc_pos = b->pk_disc_pos.as<int>();
+  a.hull = w.hull ? b->pk_hull.as<float>() : nullptr;
+  a.cluster = b->pk_cluster.as<pcseg_cluster_record>();
+  a.c_inl = b->pk_cinl.as<int>(); a.c_inl_xyz = (w.cluster && w.inlier_xyz) ? b->pk_cinl_xyz.as<float>() : nullptr;
+  a.want_cluster_stats = w.cluster_stats ? 1 : 0;
+  a.err = b->pk_err.as<int>();
+  CU_TRY(c, cudaMemsetAsync(a.err, 0, sizeof(int), stream));
+  pack_offsets_kernel<<<1, 1024, 0, stream>>>(a);
+  const int slices = std::max(1, std::min(64, (148 * 8 + nf - 1) / nf));
+  pack_bulk_kernel<<<dim3(slices, nf), 256, 0, stream>>>(a);
+  pack_region_kernel<<<nf, kPackBlock, 0, stream>>>(a);
+  c->launches += 3;
+  CU_TRY(c, cudaGetLastError());
+  int* h = b->h_meta;
+  CU_TRY(c, cudaMemcpyAsync(h, a.offsets, 5 * (F + 1) * sizeof(int), cudaMemcpyDeviceToHost, stream));
+  CU_TRY(c, cudaMemcpyAsync(h + 5 * (F + 1), a.stats, F * sizeof(FrameStats), cudaMemcpyDeviceToHost, stream));
+  CU_TRY(c, cudaMemcpyAsync(h + 5 * (F + 1) + 8 * F, a.err, sizeof(int), cudaMemcpyDeviceToHost, stream));
+  return PCSEG_OK;
+}
+
+// Host view of the staging block after the stream has been synchronised.
+struct PackTotals {
+  const int* off[5];
+  const int* stats;
+  int n_planar, n_pinl, n_bnd, n_cluster, n_cinl, err;
+};
+PackTotals pack_totals(const pcseg_batch* b, int nf) {
+  PackTotals t;
+  const int F1 = nf + 1;
+  for (int k = 0; k < 5; ++k) t.off[k] = b->h_meta + k * F1;
+  t.stats = b->h_meta + 5 * F1;
+  t.n_planar = t.off[0][nf]; t.n_pinl = t.off[1][nf]; t.n_bnd = t.off[2][nf];
+  t.n_cluster = t.off[3][nf]; t.n_cinl = t.off[4][nf];
+  t.err = b->h_meta[5 * F1 + 8 * nf];
+  for (int f = 0; f < nf; ++f) t.err |= t.stats[8 * f + 5];
+  return t;
+}
+
+// dst (host or device, nullable) <- count elements of src_dev; false when the capacity is too small.
+template <typename T>
+bool copy_result(pcseg_batch* b, T* dst, long long cap, const T* src_dev, long long count, cudaError_t* e, int mult = 1) {
+  if (!dst || count <= 0) return true;
+  if (count > cap) return false;
+  cudaMemcpyKind k = is_device_ptr(dst) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+  cudaError_t r = cudaMemcpyAsync(dst, src_dev, (size_t)count * mult * sizeof(T), k, S(b));
+  if (r != cudaSuccess && *e == cudaSuccess) *e = r;
+  return true;
+}
+
+// One frame's regions through the packed path -> the CSR vectors of pcseg_regions.
 int collect_planar(pcseg_batch* b, int frame, pcseg_regions* r) {
   pcseg_ctx* c = b->ctx;
-  FrameStats st;
-  CU_TRY(c, cudaMemcpyAsync(&st, b->stats.as<FrameStats>() + frame, sizeof(st), cudaMemcpyDeviceToHost, c->stream));
-  CU_TRY(c, cudaStreamSynchronize(c->stream));
-  const int n = st.n_planar;
-  std::vector<PlanarMeta> meta(n);
-  std::vector<int> inl(st.planar_inliers), bnd(st.boundary_len);
-  std::vector<unsigned char> bfl(st.boundary_len);
-  if (n) CU_TRY(c, cudaMemcpyAsync(meta.data(), b->meta_planar.as<PlanarMeta>() + (size_t)frame * b->rcap_planar,
-                                   n * sizeof(PlanarMeta), cudaMemcpyDeviceToHost, c->stream));
-  if (!inl.empty()) CU_TRY(c, cudaMemcpyAsync(inl.data(), b->inl_planar.as<int>() + (size_t)frame * b->N,
-                                              inl.size() * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-  if (!bnd.empty()) {
-    CU_TRY(c, cudaMemcpyAsync(bnd.data(), b->boundary.as<int>() + (size_t)frame * b->bcap,
-                              bnd.size() * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-    CU_TRY(c, cudaMemcpyAsync(bfl.data(), b->bflags.as<unsigned char>() + (size_t)frame * b->bcap, bfl.size(),
-                              cudaMemcpyDeviceToHost, c->stream));
+  cudaStream_t stream = S(b);
+  PackWant w;
+  w.hull = true;
+  int st = run_pack(b, frame, 1, w);
+  if (st) return st;
+  CU_TRY(c, cudaStreamSynchronize(stream));
+  const PackTotals t = pack_totals(b, 1);
+  const int n = t.n_planar;
+  std::vector<pcseg_planar_record> rec(n);
+  std::vector<int> inl(t.n_pinl), bnd(t.n_bnd), didx(t.n_bnd);
+  std::vector<float> hull(3 * (size_t)t.n_bnd);
+  if (n) CU_TRY(c, cudaMemcpyAsync(rec.data(), b->pk_planar.p, n * sizeof(pcseg_planar_record), cudaMemcpyDeviceToHost, stream));
+  if (t.n_pinl) CU_TRY(c, cudaMemcpyAsync(inl.data(), b->pk_pinl.p, inl.size() * sizeof(int), cudaMemcpyDeviceToHost, stream));
+  if (t.n_bnd) {
+    CU_TRY(c, cudaMemcpyAsync(bnd.data(), b->pk_bnd.p, bnd.size() * sizeof(int), cudaMemcpyDeviceToHost, stream));
+    CU_TRY(c, cudaMemcpyAsync(didx.data(), b->pk_disc_idx.p, didx.size() * sizeof(int), cudaMemcpyDeviceToHost, stream));
+    CU_TRY(c, cudaMemcpyAsync(hull.data(), b->pk_hull.p, hull.size() * sizeof(float), cudaMemcpyDeviceToHost, stream));
   }
-  CU_TRY(c, cudaStreamSynchronize(c->stream));
-  // boundary xyz for the hull output: gather on the host from a device->host copy
-  // of just the boundary points (indexed copy kernel avoided: tiny data).
-  std::vector<float> bxyz(3 * bnd.size());
-  {
-    // one strided gather via cudaMemcpy2D is not possible for arbitrary indices;
-    // fetch the frame's points once if they are not host-visible.
-    std::vector<float> frame_xyz(3 * b->N);
-    CU_TRY(c, cudaMemcpyAsync(frame_xyz.data(), b->xyz_dev + (size_t)frame * b->N * 3, frame_xyz.size() * sizeof(float),
-                              cudaMemcpyDeviceToHost, c->stream));
-    CU_TRY(c, cudaStreamSynchronize(c->stream));
-    for (size_t i = 0; i < bnd.size(); ++i)
-      for (int k = 0; k < 3; ++k) bxyz[3 * i + k] = frame_xyz[3 * (size_t)bnd[i] + k];
-  }
+  CU_TRY(c, cudaStreamSynchronize(stream));
+  r->inlier_indices = std::move(inl);
+  r->boundary_indices = std::move(bnd);
   for (int i = 0; i < n; ++i) {
-    const PlanarMeta& m = meta[i];
-    r->inlier_indices.insert(r->inlier_indices.end(), inl.begin() + m.inlier_begin,
-                             inl.begin() + m.inlier_begin + m.inlier_count);
-    r->inlier_offsets.push_back((int)r->inlier_indices.size());
+    const pcseg_planar_record& m = rec[i];
+    r->inlier_offsets.push_back(m.inlier_begin + m.inlier_count);
     r->label_ids.push_back(m.label_id);
     r->seed_indices.push_back(m.seed_index);
     r->planes.insert(r->planes.end(), m.plane, m.plane + 4);
     r->centroids.insert(r->centroids.end(), m.centroid, m.centroid + 3);
     r->areas.push_back(m.area);
-    r->estimators.insert(r->estimators.end(), m.est, m.est + 10);
-    r->boundary_indices.insert(r->boundary_indices.end(), bnd.begin() + m.boundary_begin,
-                               bnd.begin() + m.boundary_begin + m.boundary_count);
-    r->boundary_offsets.push_back((int)r->boundary_indices.size());
-    std::vector<int> disc;
-    for (int k = 0; k < m.boundary_count; ++k)
-      if (bfl[m.boundary_begin + k]) disc.push_back(bnd[m.boundary_begin + k]);
-    std::sort(disc.begin(), disc.end());
-    disc.erase(std::unique(disc.begin(), disc.end()), disc.end());
-    r->disc_indices.insert(r->disc_indices.end(), disc.begin(), disc.end());
+    r->estimators.insert(r->estimators.end(), m.estimator, m.estimator + 10);
+    r->boundary_offsets.push_back(m.boundary_begin + m.boundary_count);
+    r->disc_indices.insert(r->disc_indices.end(), didx.begin() + m.discontinuous_begin,
+                           didx.begin() + m.discontinuous_begin + m.discontinuous_count);
     r->disc_offsets.push_back((int)r->disc_indices.size());
-    host_planar_hull(bxyz.data() + 3 * (size_t)m.boundary_begin, m.boundary_count, m.plane, &r->hull_points);
+    r->hull_points.insert(r->hull_points.end(), hull.begin() + 3 * (size_t)m.hull_begin,
+                          hull.begin() + 3 * (size_t)(m.hull_begin + m.hull_count));
     r->hull_offsets.push_back((int)(r->hull_points.size() / 3));
   }
-  return map_error_flags(c, st.error_flags);
+  return map_error_flags(c, t.err);
 }
 
 int collect_cluster(pcseg_batch* b, int frame, pcseg_regions* r) {
   pcseg_ctx* c = b->ctx;
-  FrameStats st;
-  CU_TRY(c, cudaMemcpyAsync(&st, b->stats.as<FrameStats>() + frame, sizeof(st), cudaMemcpyDeviceToHost, c->stream));
-  CU_TRY(c, cudaStreamSynchronize(c->stream));
-  const int n = st.n_cluster;
-  std::vector<ClusterMeta> meta(n);
-  std::vector<int> inl(st.cluster_inliers);
-  if (n) CU_TRY(c, cudaMemcpyAsync(meta.data(), b->meta_cluster.as<ClusterMeta>() + (size_t)frame * b->rcap_cluster,
-                                   n * sizeof(ClusterMeta), cudaMemcpyDeviceToHost, c->stream));
-  if (!inl.empty()) CU_TRY(c, cudaMemcpyAsync(inl.data(), b->inl_cluster.as<int>() + (size_t)frame * b->N,
-                                              inl.size() * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  cudaStream_t stream = S(b);
+  PackWant w;
+  w.cluster = true;
+  int st = run_pack(b, frame, 1, w);
+  if (st) return st;
+  CU_TRY(c, cudaStreamSynchronize(stream));
+  const PackTotals t = pack_totals(b, 1);
+  const int n = t.n_cluster;
+  std::vector<pcseg_cluster_record> rec(n);
+  std::vector<int> inl(t.n_cinl);
+  if (n) CU_TRY(c, cudaMemcpyAsync(rec.data(), b->pk_cluster.p, n * sizeof(pcseg_cluster_record), cudaMemcpyDeviceToHost, stream));
+  if (t.n_cinl) CU_TRY(c, cudaMemcpyAsync(inl.data(), b->pk_cinl.p, inl.size() * sizeof(int), cudaMemcpyDeviceToHost, stream));
+  CU_TRY(c, cudaStreamSynchronize(stream));
+  r->inlier_indices = std::move(inl);
   for (int i = 0; i < n; ++i) {
-    const ClusterMeta& m = meta[i];
-    r->inlier_indices.insert(r->inlier_indices.end(), inl.begin() + m.inlier_begin,
-                             inl.begin() + m.inlier_begin + m.inlier_count);
-    r->inlier_offsets.push_back((int)r->inlier_indices.size());
-    r->label_ids.push_back(m.label_id);
+    r->inlier_offsets.push_back(rec[i].inlier_begin + rec[i].inlier_count);
+    r->label_ids.push_back(rec[i].label_id);
   }
-  return map_error_flags(c, st.error_flags);
+  return map_error_flags(c, t.err);
 }
 
 int get_scratch(pcseg_ctx* c, int rows, int cols, pcseg_batch** out) {
@@ -502,7 +547,8 @@ int get_scratch(pcseg_ctx* c, int rows, int cols, pcseg_batch** out) {
   return PCSEG_OK;
 }
 
-int check_seeds_host(const int* seeds_host_or_dev, int n, size_t N, pcseg_ctx* c, DevBuf* staging, const int** dev) {
+int check_seeds_host(const int* seeds_host_or_dev, int n, size_t N, pcseg_ctx* c, DevBuf* staging, const int** dev,
+                     cudaStream_t stream = nullptr) {
   // Validates the range on the host copy (the reference would read out of
   // bounds); device-resident seeds are trusted.
   if (n == 0) { *dev = (const int*)staging->p; return PCSEG_OK; }
@@ -511,7 +557,7 @@ int check_seeds_host(const int* seeds_host_or_dev, int n, size_t N, pcseg_ctx* c
       if (seeds_host_or_dev[i] < 0 || (size_t)seeds_host_or_dev[i] >= N) return PCSEG_ERR_SEED_RANGE;
   }
   const void* d;
-  int st = to_device(c, seeds_host_or_dev, (size_t)n * sizeof(int), staging, &d);
+  int st = to_device(c, seeds_host_or_dev, (size_t)n * sizeof(int), staging, &d, stream);
   *dev = (const int*)d;
   return st;
 }
@@ -573,7 +619,6 @@ void pcseg_destroy(pcseg_ctx* c) {
   if (c->scratch) pcseg_batch_destroy(c->scratch);
   c->tmp_a.release();
   c->tmp_b.release();
-  for (cudaEvent_t e : c->chunk_ev) cudaEventDestroy(e);
   if (c->copy_in) cudaStreamDestroy(c->copy_in);
   if (c->copy_out) cudaStreamDestroy(c->copy_out);
   if (c->stream) cudaStreamDestroy(c->stream);
@@ -671,18 +716,28 @@ int pcseg_segment_planar(pcseg_ctx* c, const float* xyz, const float* normals, i
   if ((st = to_device(c, normals, N * 3 * sizeof(float), &b->normals, &nrm_dev))) return st;
   b->xyz_dev = (const float*)xyz_dev;
   b->normals_dev = (const float*)nrm_dev;
-  CU_TRY(c, cudaMemcpyAsync(b->labels.p, labels, N * sizeof(int),
-                            is_device_ptr(labels) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
-  CU_TRY(c, cudaMemsetAsync(b->stats.p, 0, sizeof(FrameStats), c->stream));
-  if (n_seeds > 0) {
-    const int* seeds_dev;
-    if ((st = check_seeds_host(seeds, n_seeds, N, c, &b->seeds, &seeds_dev))) return st;
-    if ((st = run_planar(b, b->xyz_dev, b->normals_dev, seeds_dev, n_seeds, 0, nullptr, cfg, robot_q_xyzw, id_offset))) return st;
+  pcseg_regions* r = nullptr;
+  for (int attempt = 0;; ++attempt) {
+    CU_TRY(c, cudaMemcpyAsync(b->labels.p, labels, N * sizeof(int),
+                              is_device_ptr(labels) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+    CU_TRY(c, cudaMemsetAsync(b->stats.p, 0, sizeof(FrameStats), c->stream));
+    if (n_seeds > 0) {
+      const int* seeds_dev;
+      if ((st = check_seeds_host(seeds, n_seeds, N, c, &b->seeds, &seeds_dev))) return st;
+      if ((st = run_planar(b, b->xyz_dev, b->normals_dev, seeds_dev, n_seeds, 0, nullptr, cfg, robot_q_xyzw, id_offset))) return st;
+    }
+    r = new pcseg_regions();
+    st = collect_planar(b, 0, r);
+    if (st == PCSEG_OK) break;
+    delete r;
+    // more planes than the region table holds (the reference has no limit): grow it and repeat
+    const int bound = planar_region_bound(b, cfg);
+    if (st != PCSEG_ERR_CAPACITY || attempt > 0 || b->rcap_planar >= bound) return st;
+    b->rcap_planar = bound;
+    CU_TRY(c, b->meta_planar.ensure((size_t)b->rcap_planar * sizeof(PlanarMeta)));
   }
-  if ((st = from_device(c, labels, b->labels.p, N * sizeof(int)))) return st;
-  pcseg_regions* r = new pcseg_regions();
-  st = collect_planar(b, 0, r);
-  if (st) { delete r; return st; }
+  if ((st = from_device(c, labels, b->labels.p, N * sizeof(int)))) { delete r; return st; }
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
   *out = r;
   return PCSEG_OK;
 }
@@ -724,6 +779,7 @@ namespace {
 int run_seed_finder(pcseg_batch* b, const float* xyz_dev, const float* nrm_dev, int nbhd, float max_d,
                     int min_support) {
   pcseg_ctx* c = b->ctx;
+  cudaStream_t stream = S(b);
   if (b->rows > b->cols) return PCSEG_ERR_UNSUPPORTED;  // transposed reads leave the buffer (UB in the reference)
   if (nbhd < 1 || nbhd * nbhd >= kSeedMaxKeys) return PCSEG_ERR_UNSUPPORTED;
   const size_t F = b->n_frames, N = b->N;
@@ -736,13 +792,13 @@ int run_seed_finder(pcseg_batch* b, const float* xyz_dev, const float* nrm_dev, 
   a.seeds = b->seeds.as<int>(); a.stride = (int)N; a.n_seeds = b->n_seeds.as<int>();
   // counts are laid out [F][N] inside the queue buffer
   dim3 grid((unsigned)((N + 255) / 256), (unsigned)F);
-  seed_support_count_kernel<<<grid, 256, 0, c->stream>>>(a);
+  seed_support_count_kernel<<<grid, 256, 0, stream>>>(a);
   {
     const int nkeys = nbhd * nbhd + 1;
     const size_t smem = (size_t)kSeedWarps * nkeys * sizeof(int);
     if (smem > 48 * 1024)
       CU_TRY(c, cudaFuncSetAttribute(seed_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    seed_order_kernel<<<(unsigned)F, 32 * kSeedWarps, smem, c->stream>>>(a, nkeys);
+    seed_order_kernel<<<(unsigned)F, 32 * kSeedWarps, smem, stream>>>(a, nkeys);
   }
   c->launches += 2;
   CU_TRY(c, cudaGetLastError());
@@ -959,6 +1015,7 @@ int pcseg_mean_shift(pcseg_ctx* c, const float* xyz, int rows, int cols, const p
 int pcseg_batch_create(pcseg_ctx* c, int n_frames, int rows, int cols, pcseg_batch** out) {
   if (!c || !out) return PCSEG_ERR_NULL;
   if (n_frames <= 0 || rows <= 0 || cols <= 0) return PCSEG_ERR_DIMS;
+  if ((size_t)n_frames * rows * cols > (size_t)INT_MAX) return PCSEG_ERR_UNSUPPORTED;  // packed result offsets are int32
   cudaSetDevice(c->device);
   pcseg_batch* b = new pcseg_batch();
   b->ctx = c; b->n_frames = n_frames; b->rows = rows; b->cols = cols; b->N = (size_t)rows * cols;
@@ -983,39 +1040,58 @@ void pcseg_batch_destroy(pcseg_batch* b) {
     if (s) { cudaStreamSynchronize(s); cudaStreamDestroy(s); }
   DevBuf* all[] = {&b->xyz, &b->normals, &b->labels, &b->queue, &b->claim, &b->inl_planar, &b->inl_cluster,
                    &b->boundary, &b->bflags, &b->meta_planar, &b->meta_cluster, &b->stats, &b->inv_list,
-                   &b->inv_count, &b->seeds, &b->n_seeds};
+                   &b->inv_count, &b->seeds, &b->n_seeds, &b->pk_offsets, &b->pk_planar, &b->pk_pinl,
+                   &b->pk_pinl_xyz, &b->pk_bnd, &b->pk_bnd_xyz, &b->pk_bdisc, &b->pk_disc_idx, &b->pk_disc_pos,
+                   &b->pk_hull, &b->pk_cluster, &b->pk_cinl, &b->pk_cinl_xyz, &b->pk_err};
   for (DevBuf* d : all) d->release();
   b->prof.release();
+  if (b->h_meta) cudaFreeHost(b->h_meta);
   for (auto& e : b->ev) if (e) cudaEventDestroy(e);
+  for (cudaEvent_t e : b->chunk_ev) cudaEventDestroy(e);
   delete b;
 }
 
 namespace {
-// Routes everything a run enqueues to the workspace's own streams (calls on one context are
-// serialised by the caller, so swapping the context's current streams is safe).
-struct StreamScope {
-  pcseg_ctx* c;
-  cudaStream_t s, ci, co;
-  StreamScope(pcseg_ctx* ctx, pcseg_batch* b) : c(ctx), s(ctx->stream), ci(ctx->copy_in), co(ctx->copy_out) {
-    if (b->own_stream) { c->stream = b->own_stream; c->copy_in = b->own_copy_in; c->copy_out = b->own_copy_out; }
-  }
-  ~StreamScope() { c->stream = s; c->copy_in = ci; c->copy_out = co; }
-};
-int batch_enqueue(pcseg_batch* b, const float* xyz, const pcseg_pipeline_params* p, float* normals_out,
-                  int* labels_out);
+int enqueue_normals_stage(pcseg_batch* b, const float* xyz, float* normals_out);
+int enqueue_growth_stage(pcseg_batch* b);
 }  // namespace
 
-int pcseg_batch_submit(pcseg_batch* b, const float* xyz, const pcseg_pipeline_params* p, float* normals_out,
-                       int* labels_out) {
+int pcseg_batch_submit_regions(pcseg_batch* b, const float* xyz, const pcseg_pipeline_params* p, float* normals_out,
+                               int* labels_out, pcseg_batch_results* results) {
   if (!b || !xyz || !p) return PCSEG_ERR_NULL;
   if (b->in_flight) {
     int st = pcseg_batch_wait(b);
     if (st) return st;
   }
-  StreamScope scope(b->ctx, b);
-  int st = batch_enqueue(b, xyz, p, normals_out, labels_out);
-  if (st == PCSEG_OK) b->in_flight = true;
-  return st;
+  if (b->rows <= 1) return PCSEG_ERR_DIMS;
+  int st = check_planar_cfg(&p->planar);
+  if (st) return st;
+  if (p->run_cluster_stage && (st = check_cluster_cfg(&p->cluster))) return st;
+  if (p->planar_seed_mode == PCSEG_SEEDS_EXPLICIT && p->n_planar_seeds > 0 && !p->planar_seeds) return PCSEG_ERR_NULL;
+  // the run's parameters are kept: pcseg_batch_wait may have to repeat the growth stages with a
+  // larger region table (the reference has no region limit)
+  b->run_params = *p;
+  b->run_seeds.clear();
+  if (p->planar_seed_mode == PCSEG_SEEDS_EXPLICIT && p->n_planar_seeds > 0) {
+    if (is_device_ptr(p->planar_seeds)) b->run_params.planar_seeds = p->planar_seeds;
+    else {
+      b->run_seeds.assign(p->planar_seeds, p->planar_seeds + p->n_planar_seeds);
+      b->run_params.planar_seeds = b->run_seeds.data();
+    }
+  }
+  b->run_labels_out = labels_out;
+  b->run_results = results;
+  b->run_valid = true;
+  cudaSetDevice(b->ctx->device);
+  if ((st = enqueue_normals_stage(b, xyz, normals_out))) return st;
+  if ((st = enqueue_growth_stage(b))) return st;
+  b->in_flight = true;
+  return PCSEG_OK;
+}
+
+int pcseg_batch_submit(pcseg_batch* b, const float* xyz, const pcseg_pipeline_params* p, float* normals_out,
+                       int* labels_out) {
+  return pcseg_batch_submit_regions(b, xyz, p, normals_out, labels_out, nullptr);
 }
 
 int pcseg_batch_wait(pcseg_batch* b) {
@@ -1024,8 +1100,55 @@ int pcseg_batch_wait(pcseg_batch* b) {
   cudaSetDevice(c->device);
   if (!b->in_flight) return PCSEG_OK;
   b->in_flight = false;
-  CU_TRY(c, cudaStreamSynchronize(b->own_stream ? b->own_stream : c->stream));
-  if (b->wait_copy_out) CU_TRY(c, cudaStreamSynchronize(b->own_copy_out ? b->own_copy_out : c->copy_out));
+  cudaStream_t stream = S(b);
+  CU_TRY(c, cudaStreamSynchronize(stream));
+  const int F = b->n_frames;
+  PackTotals t = pack_totals(b, F);
+  if ((t.err & kErrRegionCap) && b->rcap_planar < planar_region_bound(b, &b->run_params.planar)) {
+    // more planes than the region table holds: repeat the growth stages with the full bound
+    b->rcap_planar = planar_region_bound(b, &b->run_params.planar);
+    CU_TRY(c, b->meta_planar.ensure((size_t)F * b->rcap_planar * sizeof(PlanarMeta)));
+    int st = enqueue_growth_stage(b);
+    if (st) return st;
+    CU_TRY(c, cudaStreamSynchronize(stream));
+    t = pack_totals(b, F);
+  }
+  bool fits = true;
+  if (pcseg_batch_results* r = b->run_results) {
+    r->n_planar = t.n_planar; r->n_planar_inliers = t.n_pinl; r->n_boundary = t.n_bnd;
+    r->n_cluster = t.n_cluster; r->n_cluster_inliers = t.n_cinl; r->error_flags = t.err;
+    // one copy per array, exact sizes (now known), on the workspace's stream
+    cudaError_t e = cudaSuccess;
+    const int F1 = F + 1;
+    fits &= copy_result(b, r->frame_offsets, 5 * F1, b->pk_offsets.as<int>(), 5 * F1, &e);
+    fits &= copy_result(b, r->frame_stats, 8 * F, b->stats.as<int>(), 8 * F, &e);
+    fits &= copy_result(b, r->planar, r->planar_cap, b->pk_planar.as<pcseg_planar_record>(), t.n_planar, &e);
+    fits &= copy_result(b, r->planar_inlier_indices, r->planar_inlier_cap, b->pk_pinl.as<int>(), t.n_pinl, &e);
+    if (r->want_inlier_xyz)
+      fits &= copy_result(b, r->planar_inlier_xyz, r->planar_inlier_cap, b->pk_pinl_xyz.as<float>(), t.n_pinl, &e, 3);
+    fits &= copy_result(b, r->boundary_indices, r->boundary_cap, b->pk_bnd.as<int>(), t.n_bnd, &e);
+    if (r->want_boundary_xyz)
+      fits &= copy_result(b, r->boundary_xyz, r->boundary_cap, b->pk_bnd_xyz.as<float>(), t.n_bnd, &e, 3);
+    fits &= copy_result(b, r->boundary_discontinuous, r->boundary_cap, b->pk_bdisc.as<unsigned char>(), t.n_bnd, &e);
+    fits &= copy_result(b, r->discontinuous_indices, r->boundary_cap, b->pk_disc_idx.as<int>(), t.n_bnd, &e);
+    fits &= copy_result(b, r->discontinuous_positions, r->boundary_cap, b->pk_disc_pos.as<int>(), t.n_bnd, &e);
+    if (r->want_hull)
+      fits &= copy_result(b, r->hull_points, r->boundary_cap, b->pk_hull.as<float>(), t.n_bnd, &e, 3);
+    if (b->cluster_ran) {
+      fits &= copy_result(b, r->cluster, r->cluster_cap, b->pk_cluster.as<pcseg_cluster_record>(), t.n_cluster, &e);
+      fits &= copy_result(b, r->cluster_inlier_indices, r->cluster_inlier_cap, b->pk_cinl.as<int>(), t.n_cinl, &e);
+      if (r->want_inlier_xyz)
+        fits &= copy_result(b, r->cluster_inlier_xyz, r->cluster_inlier_cap, b->pk_cinl_xyz.as<float>(), t.n_cinl, &e, 3);
+    }
+    CU_TRY(c, e);
+    CU_TRY(c, cudaStreamSynchronize(stream));
+  }
+  if (b->wait_copy_out) CU_TRY(c, cudaStreamSynchronize(SOut(b)));
+  if (t.err) return map_error_flags(c, t.err);   // truncated label grid / region list: never silently OK
+  if (!fits) {
+    c->last_error = "a pcseg_batch_results buffer is smaller than the result (see the n_* totals)";
+    return PCSEG_ERR_CAPACITY;
+  }
   return PCSEG_OK;
 }
 
@@ -1037,14 +1160,13 @@ int pcseg_batch_run(pcseg_batch* b, const float* xyz, const pcseg_pipeline_param
 }
 
 namespace {
-int batch_enqueue(pcseg_batch* b, const float* xyz, const pcseg_pipeline_params* p, float* normals_out,
-                  int* labels_out) {
+// Normals of the whole batch.  Host buffers are processed in chunks of frames: chunk k's H2D
+// (copy-in stream) overlaps the normals kernel of chunk k-1, and its normals D2H (copy-out
+// stream) overlaps everything after.
+int enqueue_normals_stage(pcseg_batch* b, const float* xyz, float* normals_out) {
   pcseg_ctx* c = b->ctx;
-  if (b->rows <= 1) return PCSEG_ERR_DIMS;
-  int st = check_planar_cfg(&p->planar);
-  if (st) return st;
-  if (p->run_cluster_stage && (st = check_cluster_cfg(&p->cluster))) return st;
-  cudaSetDevice(c->device);
+  const pcseg_pipeline_params* p = &b->run_params;
+  cudaStream_t stream = S(b), s_in = SIn(b), s_out = SOut(b);
   const size_t F = b->n_frames, N = b->N;
   const bool xyz_host = !is_device_ptr(xyz);
   const bool nrm_host = normals_out && !is_device_ptr(normals_out);
@@ -1057,44 +1179,57 @@ int batch_enqueue(pcseg_batch* b, const float* xyz, const pcseg_pipeline_params*
     nrm_dev = b->normals.as<float>();
   }
   b->normals_dev = nrm_dev;
-  cudaEventRecord(b->ev[0], c->stream);
+  b->wait_copy_out = false;
+  cudaEventRecord(b->ev[0], stream);
+  int st;
   if (!xyz_host && !nrm_host) {
     if ((st = run_normals(b, b->xyz_dev, nrm_dev, nullptr, &p->normals, p->sensor_translation, 0, b->rows, 0, b->cols))) return st;
   } else {
-    // Host buffers: chunks of frames; chunk k's H2D (copy_in stream) overlaps the normals
-    // kernel of chunk k-1, and its normals D2H (copy_out stream) overlaps everything after.
-    const size_t chunk_frames = std::max<size_t>(1, std::min<size_t>(F, (size_t)(96u << 20) / (N * 12) ));
+    const size_t chunk_frames = std::max<size_t>(1, std::min<size_t>(F, (size_t)(96u << 20) / (N * 12)));
     const size_t n_chunks = (F + chunk_frames - 1) / chunk_frames;
-    while (c->chunk_ev.size() < 2 * n_chunks + 1) {
+    while (b->chunk_ev.size() < 2 * n_chunks + 2) {
       cudaEvent_t e;
       CU_TRY(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-      c->chunk_ev.push_back(e);
+      b->chunk_ev.push_back(e);
     }
     // the copy streams start after everything already queued on the main stream
-    cudaEvent_t start = c->chunk_ev[2 * n_chunks];
-    CU_TRY(c, cudaEventRecord(start, c->stream));
-    CU_TRY(c, cudaStreamWaitEvent(c->copy_in, start, 0));
-    CU_TRY(c, cudaStreamWaitEvent(c->copy_out, start, 0));
+    cudaEvent_t start = b->chunk_ev[2 * n_chunks];
+    CU_TRY(c, cudaEventRecord(start, stream));
+    CU_TRY(c, cudaStreamWaitEvent(s_in, start, 0));
+    CU_TRY(c, cudaStreamWaitEvent(s_out, start, 0));
     for (size_t k = 0; k < n_chunks; ++k) {
       const size_t f0 = k * chunk_frames, nf = std::min(chunk_frames, F - f0);
       const size_t off = f0 * N * 3, cnt = nf * N * 3 * sizeof(float);
       if (xyz_host) {
-        CU_TRY(c, cudaMemcpyAsync(b->xyz.as<float>() + off, xyz + off, cnt, cudaMemcpyHostToDevice, c->copy_in));
-        CU_TRY(c, cudaEventRecord(c->chunk_ev[2 * k], c->copy_in));
-        CU_TRY(c, cudaStreamWaitEvent(c->stream, c->chunk_ev[2 * k], 0));
+        CU_TRY(c, cudaMemcpyAsync(b->xyz.as<float>() + off, xyz + off, cnt, cudaMemcpyHostToDevice, s_in));
+        CU_TRY(c, cudaEventRecord(b->chunk_ev[2 * k], s_in));
+        CU_TRY(c, cudaStreamWaitEvent(stream, b->chunk_ev[2 * k], 0));
       }
       if ((st = run_normals(b, b->xyz_dev, nrm_dev, nullptr, &p->normals, p->sensor_translation, 0, b->rows, 0,
                             b->cols, (int)f0, (int)nf))) return st;
       if (nrm_host) {
-        CU_TRY(c, cudaEventRecord(c->chunk_ev[2 * k + 1], c->stream));
-        CU_TRY(c, cudaStreamWaitEvent(c->copy_out, c->chunk_ev[2 * k + 1], 0));
-        CU_TRY(c, cudaMemcpyAsync(normals_out + off, nrm_dev + off, cnt, cudaMemcpyDeviceToHost, c->copy_out));
+        CU_TRY(c, cudaEventRecord(b->chunk_ev[2 * k + 1], stream));
+        CU_TRY(c, cudaStreamWaitEvent(s_out, b->chunk_ev[2 * k + 1], 0));
+        CU_TRY(c, cudaMemcpyAsync(normals_out + off, nrm_dev + off, cnt, cudaMemcpyDeviceToHost, s_out));
+        b->wait_copy_out = true;
       }
     }
   }
-  cudaEventRecord(b->ev[1], c->stream);
-  if ((st = fill_int(c, b->labels.as<int>(), F * N, kUnlabeled))) return st;  // PrepareUnlabeledLabels
-  CU_TRY(c, cudaMemsetAsync(b->stats.p, 0, F * sizeof(FrameStats), c->stream));
+  cudaEventRecord(b->ev[1], stream);
+  return PCSEG_OK;
+}
+
+// PrepareUnlabeledLabels -> seeds -> planar growth -> cluster growth -> labels out -> region pack.
+// Everything after the normals; pcseg_batch_wait repeats it when the region table was too small.
+int enqueue_growth_stage(pcseg_batch* b) {
+  pcseg_ctx* c = b->ctx;
+  const pcseg_pipeline_params* p = &b->run_params;
+  cudaStream_t stream = S(b);
+  const size_t F = b->n_frames, N = b->N;
+  float* nrm_dev = const_cast<float*>(b->normals_dev);
+  int st;
+  if ((st = fill_int(c, b->labels.as<int>(), F * N, kUnlabeled, stream))) return st;  // PrepareUnlabeledLabels
+  CU_TRY(c, cudaMemsetAsync(b->stats.p, 0, F * sizeof(FrameStats), stream));
   const int* seeds_dev = nullptr;
   int n_seeds = (int)N, stride = 0;
   const int* n_seeds_dev = nullptr;
@@ -1102,13 +1237,12 @@ int batch_enqueue(pcseg_batch* b, const float* xyz, const pcseg_pipeline_params*
     if ((st = run_seed_finder(b, b->xyz_dev, nrm_dev, 9, 0.05f, 12))) return st;  // ps/segmentation.h:193-194 defaults
     seeds_dev = b->seeds.as<int>(); stride = (int)N; n_seeds_dev = b->n_seeds.as<int>();
   } else if (p->planar_seed_mode == PCSEG_SEEDS_EXPLICIT) {
-    if (p->n_planar_seeds > 0 && !p->planar_seeds) return PCSEG_ERR_NULL;
     if (p->n_planar_seeds > 0) {
-      if ((st = check_seeds_host(p->planar_seeds, p->n_planar_seeds, N, c, &b->seeds, &seeds_dev))) return st;
+      if ((st = check_seeds_host(p->planar_seeds, p->n_planar_seeds, N, c, &b->seeds, &seeds_dev, stream))) return st;
     }
     n_seeds = p->n_planar_seeds;
   }
-  cudaEventRecord(b->ev[2], c->stream);
+  cudaEventRecord(b->ev[2], stream);
   bool fused = false;
   if (!(p->planar_seed_mode == PCSEG_SEEDS_EXPLICIT && n_seeds == 0)) {
     ClusterArgs ca;
@@ -1116,13 +1250,43 @@ int batch_enqueue(pcseg_batch* b, const float* xyz, const pcseg_pipeline_params*
     if ((st = run_planar(b, b->xyz_dev, nrm_dev, seeds_dev, n_seeds, stride, n_seeds_dev, &p->planar,
                          p->robot_q_xyzw, 0, p->run_cluster_stage ? &ca : nullptr, &fused))) return st;
   }
-  cudaEventRecord(b->ev[3], c->stream);
+  cudaEventRecord(b->ev[3], stream);
   if (p->run_cluster_stage && !fused) {
     if ((st = run_cluster(b, b->xyz_dev, nullptr, (int)N, &p->cluster, 0, 1))) return st;
   }
-  cudaEventRecord(b->ev[4], c->stream);
-  if (labels_out && (st = from_device(c, labels_out, b->labels.p, F * N * sizeof(int)))) return st;
-  b->wait_copy_out = nrm_host;
+  b->cluster_ran = p->run_cluster_stage != 0;
+  cudaEventRecord(b->ev[4], stream);
+  if (b->run_labels_out) {
+    // label grid out on the copy-out stream, beside the region pack
+    cudaStream_t s_out = SOut(b);
+    while (b->chunk_ev.size() < 1) {
+      cudaEvent_t e;
+      CU_TRY(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+      b->chunk_ev.push_back(e);
+    }
+    cudaEvent_t grown = b->chunk_ev.back();
+    CU_TRY(c, cudaEventRecord(grown, stream));
+    CU_TRY(c, cudaStreamWaitEvent(s_out, grown, 0));
+    cudaMemcpyKind k = is_device_ptr(b->run_labels_out) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+    CU_TRY(c, cudaMemcpyAsync(b->run_labels_out, b->labels.p, F * N * sizeof(int), k, s_out));
+    b->wait_copy_out = true;
+  }
+  if (b->run_results) {
+    PackWant w;
+    w.inlier_xyz = b->run_results->want_inlier_xyz != 0;
+    w.boundary_xyz = b->run_results->want_boundary_xyz != 0;
+    w.hull = b->run_results->want_hull != 0;
+    w.cluster_stats = b->run_results->want_cluster_stats != 0;
+    w.cluster = b->cluster_ran;
+    if ((st = run_pack(b, 0, (int)F, w))) return st;
+  } else {
+    // error flags travel with every run (pcseg_batch_wait must not return OK on a truncated result)
+    if (!b->h_meta) CU_TRY(c, cudaMallocHost((void**)&b->h_meta, (5 * (F + 1) + 8 * F + 1) * sizeof(int)));
+    std::memset(b->h_meta, 0, (5 * (F + 1) + 1) * sizeof(int));
+    b->h_meta[5 * (F + 1) + 8 * F] = 0;
+    CU_TRY(c, cudaMemcpyAsync(b->h_meta + 5 * (F + 1), b->stats.p, F * sizeof(FrameStats), cudaMemcpyDeviceToHost, stream));
+  }
+  cudaEventRecord(b->ev[5], stream);
   return PCSEG_OK;
 }
 }  // namespace
@@ -1150,14 +1314,14 @@ int pcseg_batch_regions(pcseg_batch* b, int frame, int kind, pcseg_regions** out
   return PCSEG_OK;
 }
 
-int pcseg_batch_stage_times(pcseg_batch* b, float* ms4) {
-  if (!b || !ms4) return PCSEG_ERR_NULL;
+int pcseg_batch_stage_times(pcseg_batch* b, float* ms5) {
+  if (!b || !ms5) return PCSEG_ERR_NULL;
   pcseg_ctx* c = b->ctx;
   cudaSetDevice(c->device);
   if (int w = pcseg_batch_wait(b)) return w;
-  CU_TRY(c, cudaEventSynchronize(b->ev[4]));
-  // normals (+fix-up) | label init + seed finder | planar growth | cluster growth
-  for (int i = 0; i < 4; ++i) CU_TRY(c, cudaEventElapsedTime(ms4 + i, b->ev[i], b->ev[i + 1]));
+  CU_TRY(c, cudaEventSynchronize(b->ev[5]));
+  // normals (+fix-up) | label init + seed finder | planar growth | cluster growth | region pack
+  for (int i = 0; i < 5; ++i) CU_TRY(c, cudaEventElapsedTime(ms5 + i, b->ev[i], b->ev[i + 1]));
   return PCSEG_OK;
 }
 
@@ -1173,6 +1337,97 @@ int pcseg_batch_profile(pcseg_batch* b, long long* out16_per_frame) {
 void* pcseg_batch_stream(const pcseg_batch* b) { return b ? (void*)(b->own_stream ? b->own_stream : b->ctx->stream) : nullptr; }
 int* pcseg_batch_device_labels(pcseg_batch* b) { return b ? b->labels.as<int>() : nullptr; }
 float* pcseg_batch_device_normals(pcseg_batch* b) { return b ? const_cast<float*>(b->normals_dev) : nullptr; }
+
+// ---- result export ------------------------------------------
+int pcseg_transform_in_place(pcseg_ctx* c, float* points_xyz, float* normals_xyz, int n, const double q_xyzw[4],
+                             const double translation[3]) {
+  if (!c || !q_xyzw || !translation) return PCSEG_ERR_NULL;
+  if (n < 0) return PCSEG_ERR_DIMS;
+  if (n == 0 || (!points_xyz && !normals_xyz)) return PCSEG_OK;
+  cudaSetDevice(c->device);
+  const size_t bytes = (size_t)n * 3 * sizeof(float);
+  TransformArgs a;
+  a.n = n;
+  // new_pose_current.cast<float>(), ps/multichannel_cloud.cc:55
+  a.qx = (float)q_xyzw[0]; a.qy = (float)q_xyzw[1]; a.qz = (float)q_xyzw[2]; a.qw = (float)q_xyzw[3];
+  a.tx = (float)translation[0]; a.ty = (float)translation[1]; a.tz = (float)translation[2];
+  const bool p_dev = points_xyz && is_device_ptr(points_xyz), n_dev = normals_xyz && is_device_ptr(normals_xyz);
+  a.points = points_xyz; a.normals = normals_xyz;
+  if (points_xyz && !p_dev) {
+    CU_TRY(c, c->tmp_a.ensure(bytes));
+    CU_TRY(c, cudaMemcpyAsync(c->tmp_a.p, points_xyz, bytes, cudaMemcpyHostToDevice, c->stream));
+    a.points = c->tmp_a.as<float>();
+  }
+  if (normals_xyz && !n_dev) {
+    CU_TRY(c, c->tmp_b.ensure(bytes));
+    CU_TRY(c, cudaMemcpyAsync(c->tmp_b.p, normals_xyz, bytes, cudaMemcpyHostToDevice, c->stream));
+    a.normals = c->tmp_b.as<float>();
+  }
+  const int blocks = (int)std::min<size_t>(((size_t)n + 255) / 256, 148 * 16);
+  transform_in_place_kernel<<<blocks, 256, 0, c->stream>>>(a);
+  ++c->launches;
+  CU_TRY(c, cudaGetLastError());
+  if (points_xyz && !p_dev) CU_TRY(c, cudaMemcpyAsync(points_xyz, a.points, bytes, cudaMemcpyDeviceToHost, c->stream));
+  if (normals_xyz && !n_dev) CU_TRY(c, cudaMemcpyAsync(normals_xyz, a.normals, bytes, cudaMemcpyDeviceToHost, c->stream));
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  return PCSEG_OK;
+}
+
+int pcseg_gather_points(pcseg_ctx* c, const float* xyz, int n_points, const int* indices, int n_indices,
+                        float* out_xyz, const int* discontinuous, int n_discontinuous, int* positions_out,
+                        int* n_positions) {
+  if (!c || !xyz || (n_indices > 0 && (!indices || !out_xyz))) return PCSEG_ERR_NULL;
+  if (n_discontinuous > 0 && (!discontinuous || !positions_out || !n_positions)) return PCSEG_ERR_NULL;
+  if (n_points < 0 || n_indices < 0 || n_discontinuous < 0) return PCSEG_ERR_DIMS;
+  if (n_positions) *n_positions = 0;
+  if (n_indices == 0) return PCSEG_OK;
+  cudaSetDevice(c->device);
+  if (!is_device_ptr(indices))
+    for (int i = 0; i < n_indices; ++i)
+      if (indices[i] < 0 || indices[i] >= n_points) return PCSEG_ERR_SEED_RANGE;  // AtUnsafe would read out of bounds
+  if (n_discontinuous > 0 && !is_device_ptr(discontinuous))
+    for (int i = 0; i < n_discontinuous; ++i)
+      if (discontinuous[i] < 0 || discontinuous[i] >= n_points) return PCSEG_ERR_SEED_RANGE;
+  DevBuf sx, si, so, sd, sm, sp, sn;
+  const void *xyz_dev, *idx_dev;
+  int st;
+  if ((st = to_device(c, xyz, (size_t)n_points * 3 * sizeof(float), &sx, &xyz_dev))) return st;
+  if ((st = to_device(c, indices, (size_t)n_indices * sizeof(int), &si, &idx_dev))) return st;
+  const bool out_dev = is_device_ptr(out_xyz);
+  float* out_d = out_xyz;
+  if (!out_dev) {
+    CU_TRY(c, so.ensure((size_t)n_indices * 3 * sizeof(float)));
+    out_d = so.as<float>();
+  }
+  const int blocks = std::min((n_indices + 255) / 256, 148 * 16);
+  gather_points_kernel<<<blocks, 256, 0, c->stream>>>((const float*)xyz_dev, (const int*)idx_dev, n_indices, out_d);
+  ++c->launches;
+  if (!out_dev) CU_TRY(c, cudaMemcpyAsync(out_xyz, out_d, (size_t)n_indices * 3 * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+  if (n_discontinuous > 0) {
+    const void* disc_dev;
+    if ((st = to_device(c, discontinuous, (size_t)n_discontinuous * sizeof(int), &sd, &disc_dev))) return st;
+    CU_TRY(c, sm.ensure((size_t)n_points));
+    CU_TRY(c, cudaMemsetAsync(sm.p, 0, (size_t)n_points, c->stream));
+    CU_TRY(c, sp.ensure((size_t)n_indices * sizeof(int)));
+    CU_TRY(c, sn.ensure(sizeof(int)));
+    mark_cells_kernel<<<std::min((n_discontinuous + 255) / 256, 148 * 16), 256, 0, c->stream>>>(
+        (const int*)disc_dev, n_discontinuous, sm.as<unsigned char>(), 1);
+    positions_of_marked_kernel<<<1, 1024, 0, c->stream>>>((const int*)idx_dev, n_indices, sm.as<unsigned char>(),
+                                                          sp.as<int>(), sn.as<int>());
+    c->launches += 2;
+    int np = 0;
+    CU_TRY(c, cudaMemcpyAsync(&np, sn.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CU_TRY(c, cudaStreamSynchronize(c->stream));
+    *n_positions = np;
+    if (np > 0) {
+      cudaMemcpyKind k = is_device_ptr(positions_out) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+      CU_TRY(c, cudaMemcpyAsync(positions_out, sp.p, (size_t)np * sizeof(int), k, c->stream));
+    }
+  }
+  CU_TRY(c, cudaGetLastError());
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  return PCSEG_OK;
+}
 
 // ---- accessors ---------------------------------------------------------------
 int pcseg_regions_count(const pcseg_regions* r) { return (int)r->label_ids.size(); }

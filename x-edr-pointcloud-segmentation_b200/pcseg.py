@@ -53,6 +53,50 @@ class PipelineParams(C.Structure):
                 ("run_cluster_stage", C.c_int)]
 
 
+class PlanarRecord(C.Structure):
+    _fields_ = [("frame", C.c_int), ("label_id", C.c_int), ("seed_index", C.c_int),
+                ("inlier_begin", C.c_int), ("inlier_count", C.c_int),
+                ("boundary_begin", C.c_int), ("boundary_count", C.c_int),
+                ("discontinuous_begin", C.c_int), ("discontinuous_count", C.c_int),
+                ("hull_begin", C.c_int), ("hull_count", C.c_int),
+                ("plane", C.c_float * 4), ("centroid", C.c_float * 3), ("area", C.c_float),
+                ("estimator", C.c_float * 10)]
+
+
+class ClusterRecord(C.Structure):
+    _fields_ = [("frame", C.c_int), ("label_id", C.c_int), ("inlier_begin", C.c_int), ("inlier_count", C.c_int),
+                ("centroid", C.c_float * 3), ("bbox_min", C.c_float * 3), ("bbox_max", C.c_float * 3)]
+
+
+PLANAR_RECORD_DTYPE = np.dtype([
+    ("frame", "<i4"), ("label_id", "<i4"), ("seed_index", "<i4"), ("inlier_begin", "<i4"), ("inlier_count", "<i4"),
+    ("boundary_begin", "<i4"), ("boundary_count", "<i4"), ("discontinuous_begin", "<i4"),
+    ("discontinuous_count", "<i4"), ("hull_begin", "<i4"), ("hull_count", "<i4"),
+    ("plane", "<f4", 4), ("centroid", "<f4", 3), ("area", "<f4"), ("estimator", "<f4", 10)])
+CLUSTER_RECORD_DTYPE = np.dtype([
+    ("frame", "<i4"), ("label_id", "<i4"), ("inlier_begin", "<i4"), ("inlier_count", "<i4"),
+    ("centroid", "<f4", 3), ("bbox_min", "<f4", 3), ("bbox_max", "<f4", 3)])
+assert PLANAR_RECORD_DTYPE.itemsize == C.sizeof(PlanarRecord) and CLUSTER_RECORD_DTYPE.itemsize == C.sizeof(ClusterRecord)
+
+
+class BatchResultsStruct(C.Structure):
+    _fields_ = [("want_inlier_xyz", C.c_int), ("want_boundary_xyz", C.c_int), ("want_hull", C.c_int),
+                ("want_cluster_stats", C.c_int),
+                ("frame_stats", C.c_void_p), ("frame_offsets", C.c_void_p),
+                ("planar", C.c_void_p), ("planar_cap", C.c_int),
+                ("planar_inlier_indices", C.c_void_p), ("planar_inlier_cap", C.c_int),
+                ("planar_inlier_xyz", C.c_void_p),
+                ("boundary_indices", C.c_void_p), ("boundary_cap", C.c_int),
+                ("boundary_xyz", C.c_void_p), ("boundary_discontinuous", C.c_void_p),
+                ("discontinuous_indices", C.c_void_p), ("discontinuous_positions", C.c_void_p),
+                ("hull_points", C.c_void_p),
+                ("cluster", C.c_void_p), ("cluster_cap", C.c_int),
+                ("cluster_inlier_indices", C.c_void_p), ("cluster_inlier_cap", C.c_int),
+                ("cluster_inlier_xyz", C.c_void_p),
+                ("n_planar", C.c_int), ("n_planar_inliers", C.c_int), ("n_boundary", C.c_int),
+                ("n_cluster", C.c_int), ("n_cluster_inliers", C.c_int), ("error_flags", C.c_int)]
+
+
 SEEDS_ALL_DESCENDING, SEEDS_PLANE_SUPPORT, SEEDS_EXPLICIT = 0, 1, 2
 
 EXPORTS = """pcseg_default_normals_params pcseg_default_planar_config
@@ -61,6 +105,7 @@ pcseg_last_error pcseg_launch_count pcseg_stream pcseg_prepare_unlabeled_labels
 pcseg_normals_organized pcseg_segment_planar pcseg_segment_cluster
 pcseg_mean_shift_modes pcseg_mean_shift_modes_range pcseg_mean_shift_from_modes
 pcseg_mean_shift pcseg_seeds_plane_support
+pcseg_batch_submit_regions pcseg_transform_in_place pcseg_gather_points
 pcseg_batch_create pcseg_batch_destroy pcseg_batch_run pcseg_batch_submit pcseg_batch_wait pcseg_batch_stream pcseg_batch_frame_stats
 pcseg_batch_regions pcseg_batch_stage_times pcseg_batch_profile pcseg_batch_device_labels pcseg_batch_device_normals
 pcseg_regions_count pcseg_regions_inlier_offsets pcseg_regions_inlier_indices
@@ -325,6 +370,29 @@ class Context:
         return out[:n.value].copy()
 
 
+    def transform_in_place(self, points=None, normals=None, q_xyzw=(0, 0, 0, 1), translation=(0, 0, 0)):
+        """MultichannelCloud::TransformInPlace (ps/multichannel_cloud.cc:53-68); arrays are modified in place."""
+        n = (points if points is not None else normals).reshape(-1, 3).shape[0]
+        q = (C.c_double * 4)(*[float(v) for v in q_xyzw])
+        t = (C.c_double * 3)(*[float(v) for v in translation])
+        self._check(self.L.pcseg_transform_in_place(
+            self.h, _addr(points) if points is not None else None,
+            _addr(normals) if normals is not None else None, n, q, t))
+
+    def gather_points(self, xyz, indices, discontinuous=None):
+        """Create*DetectedObjectProto gathers (ps/detected_objects.cc:36-46, .h:62-74)."""
+        xyz = _f32(xyz).reshape(-1)
+        indices = _i32(indices)
+        out = np.zeros((indices.size, 3), np.float32)
+        disc = _i32(discontinuous) if discontinuous is not None else np.zeros(0, np.int32)
+        pos = np.zeros(max(indices.size, 1), np.int32)
+        npos = C.c_int(0)
+        self._check(self.L.pcseg_gather_points(
+            self.h, _addr(xyz), xyz.size // 3, _addr(indices), indices.size, _addr(out),
+            _addr(disc) if disc.size else None, disc.size, _addr(pos), C.byref(npos)))
+        return out, pos[:npos.value].copy()
+
+
 class Batch:
     """Persistent workspace for n_frames x rows x cols (pcseg_batch_*)."""
 
@@ -367,9 +435,18 @@ class Batch:
         return out
 
     def stage_times(self):
-        out = np.zeros(4, np.float32)
+        out = np.zeros(5, np.float32)
         self.ctx._check(self.ctx.L.pcseg_batch_stage_times(self.h, _addr(out)))
-        return dict(zip(("normals", "seeds", "planar", "cluster"), [float(v) for v in out]))
+        return dict(zip(("normals", "seeds", "planar", "cluster", "pack"), [float(v) for v in out]))
+
+    def submit_regions(self, xyz, params, results, normals_out=None, labels_out=None):
+        """Asynchronous run that also returns every frame's regions (pcseg_batch_submit_regions);
+        `results` is a BatchResults whose buffers must stay alive until wait()."""
+        self._keep = (xyz, params, normals_out, labels_out, results)
+        self.ctx._check(self.ctx.L.pcseg_batch_submit_regions(
+            self.h, _addr(xyz), C.byref(params),
+            _addr(normals_out) if normals_out is not None else None,
+            _addr(labels_out) if labels_out is not None else None, C.byref(results.s)))
 
     def profile(self):
         out = np.zeros((self.n_frames, 16), np.int64)
@@ -390,6 +467,103 @@ class Batch:
     @property
     def device_normals(self):
         return self.ctx.L.pcseg_batch_device_normals(self.h)
+
+
+class BatchResults:
+    """Caller-side buffers of pcseg_batch_results for a workspace of n_frames x n_points.
+    alloc(shape, dtype) -> array-like with .ctypes / numpy view; pass bench.py's pinned allocator for
+    overlap, default numpy.  Capacities: every point can be an inlier; boundary entries are bounded
+    by boundary_cap (default n_frames * 8192)."""
+
+    def __init__(self, n_frames, n_points, inlier_xyz=False, boundary_xyz=False, hull=True, cluster_stats=True,
+                 boundary_cap=None, region_cap=None, alloc=None):
+        alloc = alloc or (lambda shape, dtype: np.zeros(shape, dtype))
+        F, N = n_frames, n_points
+        bc = boundary_cap or F * 8192
+        rc = region_cap or F * 256
+        self.F = F
+        self.frame_stats = alloc((F, 8), np.int32)
+        self.frame_offsets = alloc((5, F + 1), np.int32)
+        self.planar = alloc((rc,), PLANAR_RECORD_DTYPE)
+        self.planar_inlier_indices = alloc((F * N,), np.int32)
+        self.planar_inlier_xyz = alloc((F * N, 3), np.float32) if inlier_xyz else None
+        self.boundary_indices = alloc((bc,), np.int32)
+        self.boundary_xyz = alloc((bc, 3), np.float32) if boundary_xyz else None
+        self.boundary_discontinuous = alloc((bc,), np.uint8)
+        self.discontinuous_indices = alloc((bc,), np.int32)
+        self.discontinuous_positions = alloc((bc,), np.int32)
+        self.hull_points = alloc((bc, 3), np.float32) if hull else None
+        self.cluster = alloc((rc,), CLUSTER_RECORD_DTYPE)
+        self.cluster_inlier_indices = alloc((F * N,), np.int32)
+        self.cluster_inlier_xyz = alloc((F * N, 3), np.float32) if inlier_xyz else None
+        s = BatchResultsStruct()
+        s.want_inlier_xyz, s.want_boundary_xyz, s.want_hull = int(inlier_xyz), int(boundary_xyz), int(hull)
+        s.want_cluster_stats = int(cluster_stats)
+        ptr = lambda a: (a.ctypes.data if a is not None else None)
+        s.frame_stats, s.frame_offsets = ptr(self.frame_stats), ptr(self.frame_offsets)
+        s.planar, s.planar_cap = ptr(self.planar), rc
+        s.planar_inlier_indices, s.planar_inlier_cap = ptr(self.planar_inlier_indices), F * N
+        s.planar_inlier_xyz = ptr(self.planar_inlier_xyz)
+        s.boundary_indices, s.boundary_cap = ptr(self.boundary_indices), bc
+        s.boundary_xyz, s.boundary_discontinuous = ptr(self.boundary_xyz), ptr(self.boundary_discontinuous)
+        s.discontinuous_indices, s.discontinuous_positions = ptr(self.discontinuous_indices), ptr(self.discontinuous_positions)
+        s.hull_points = ptr(self.hull_points)
+        s.cluster, s.cluster_cap = ptr(self.cluster), rc
+        s.cluster_inlier_indices, s.cluster_inlier_cap = ptr(self.cluster_inlier_indices), F * N
+        s.cluster_inlier_xyz = ptr(self.cluster_inlier_xyz)
+        self.s = s
+
+    @property
+    def d2h_bytes(self):
+        """Bytes the last completed run copied into these buffers."""
+        s = self.s
+        n = 4 * (5 * (self.F + 1) + 8 * self.F)
+        n += s.n_planar * PLANAR_RECORD_DTYPE.itemsize + s.n_cluster * CLUSTER_RECORD_DTYPE.itemsize
+        n += 4 * s.n_planar_inliers + 4 * s.n_cluster_inliers
+        if s.want_inlier_xyz:
+            n += 12 * (s.n_planar_inliers + s.n_cluster_inliers)
+        n += s.n_boundary * (4 + 1 + 4 + 4 + (12 if s.want_boundary_xyz else 0) + (12 if s.want_hull else 0))
+        return n
+
+    def frame_regions(self, f, kind):
+        """Regions of frame f as the same namespace _collect() builds (views, frame-local CSR)."""
+        s = self.s
+        off = np.asarray(self.frame_offsets)
+        r = SimpleNamespace()
+        if kind == "planar":
+            recs = np.asarray(self.planar)[off[0, f]:off[0, f + 1]]
+            r.n = len(recs)
+            ii = np.asarray(self.planar_inlier_indices)
+            r.inliers = [ii[m["inlier_begin"]:m["inlier_begin"] + m["inlier_count"]] for m in recs]
+            r.label_ids = recs["label_id"].copy()
+            r.seed_indices = recs["seed_index"].copy()
+            r.planes, r.centroids, r.areas, r.estimators = recs["plane"], recs["centroid"], recs["area"], recs["estimator"]
+            bi = np.asarray(self.boundary_indices)
+            r.boundaries = [bi[m["boundary_begin"]:m["boundary_begin"] + m["boundary_count"]] for m in recs]
+            di, dp = np.asarray(self.discontinuous_indices), np.asarray(self.discontinuous_positions)
+            r.disc = [di[m["discontinuous_begin"]:m["discontinuous_begin"] + m["discontinuous_count"]] for m in recs]
+            r.disc_positions = [dp[m["discontinuous_begin"]:m["discontinuous_begin"] + m["discontinuous_count"]] for m in recs]
+            if self.hull_points is not None:
+                hp = np.asarray(self.hull_points)
+                r.hulls = [hp[m["hull_begin"]:m["hull_begin"] + m["hull_count"]] for m in recs]
+            if self.planar_inlier_xyz is not None:
+                px = np.asarray(self.planar_inlier_xyz)
+                r.inlier_xyz = [px[m["inlier_begin"]:m["inlier_begin"] + m["inlier_count"]] for m in recs]
+            if self.boundary_xyz is not None:
+                bx = np.asarray(self.boundary_xyz)
+                r.boundary_xyz = [bx[m["boundary_begin"]:m["boundary_begin"] + m["boundary_count"]] for m in recs]
+        else:
+            recs = np.asarray(self.cluster)[off[3, f]:off[3, f + 1]]
+            r.n = len(recs)
+            ii = np.asarray(self.cluster_inlier_indices)
+            r.inliers = [ii[m["inlier_begin"]:m["inlier_begin"] + m["inlier_count"]] for m in recs]
+            r.label_ids = recs["label_id"].copy()
+            r.centroids, r.bbox_min, r.bbox_max = recs["centroid"], recs["bbox_min"], recs["bbox_max"]
+            if self.cluster_inlier_xyz is not None:
+                cx = np.asarray(self.cluster_inlier_xyz)
+                r.inlier_xyz = [cx[m["inlier_begin"]:m["inlier_begin"] + m["inlier_count"]] for m in recs]
+        r.records = recs
+        return r
 
 
 def pipeline_params(normals=None, planar=None, cluster=None, sensor_t=(0, 0, 0),
