@@ -11,7 +11,7 @@ all: lib oracle host_test
 lib: $(PKG)/libpcseg_b200.so
 
 $(PKG)/libpcseg_b200.so: $(CSRC)/pcseg_api.cu $(wildcard $(CSRC)/*.cuh) include/pcseg_b200.h
-	$(NVCC) $(NVFLAGS) $(EXTRA) -o $@ $(CSRC)/pcseg_api.cu
+	$(NVCC) $(NVFLAGS) $(EXTRA) -o $@.tmp $(CSRC)/pcseg_api.cu && mv -f $@.tmp $@
 
 oracle:
 	$(MAKE) -C oracle all

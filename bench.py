@@ -61,7 +61,7 @@ def cpu_kind():
     return "reference" if oracle.ref_available() else "port"
 
 
-def _cpu_pipeline(xyz):
+def _cpu_pipeline(xyz, want_regions=False):
     """The reference's CPU path for one frame: ComputeNormalsOrganized ->
     SegmentRegions<PlanarRegion> -> SegmentRegions<ClusterRegion> (oracle/_ref when built,
     else the oracle port)."""
@@ -73,6 +73,8 @@ def _cpu_pipeline(xyz):
         labels = np.full(N_PTS, -1, np.int32)
         lab, regs = oracle.segment_planar(xyz, nrm, ROWS, COLS, seeds, labels)
         lab2, cl = oracle.segment_cluster(xyz, ROWS, COLS, seeds, lab, id_offset=regs.n)
+    if want_regions:
+        return lab2, regs, cl
     return lab2, regs.n, cl.n
 
 
@@ -166,6 +168,16 @@ def bind_to_gpu_numa_node(local_rank):
         return "unbound (%s)" % type(e).__name__
 
 
+def ncu_traffic():
+    """DRAM bytes per launch / warp instructions per point of the kernels from the committed ncu
+    capture of this same command (profiles/ncu_traffic.json, written from `ncu --set full`)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            return json.load(f)
+    except Exception:
+        return {}
+
+
 def measured_peak_gbs():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -182,6 +194,10 @@ def run_reference(args, rank, world):
     cores = os.cpu_count() or 1
     sample = min(FRAMES_PER_GPU, int(os.environ.get("PCSEG_BENCH_REF_SAMPLE", 4 * cores)))  # frames per step
     kind = cpu_kind()
+    if kind == "reference":
+        import oracle
+        with oracle.reference():
+            oracle.lib()   # dlopen oracle/_ref/libref.so in THIS process: the forked workers inherit the mapping
     global _FRAMES
     _FRAMES = gen_frames(list(range(sample)))
     with mp.get_context("fork").Pool(cores) as pool:
@@ -256,27 +272,41 @@ def main():
     ids = [rank * FRAMES_PER_GPU + k for k in range(F)]
     host = torch.from_numpy(gen_frames(ids)).pin_memory()           # [F, N, 3] pinned
     dev_xyz = host.to("cuda", non_blocking=False)
-    out_normals = torch.empty((F, N_PTS, 3), dtype=torch.float32).pin_memory()
-    out_labels = torch.empty((F, N_PTS), dtype=torch.int32).pin_memory()
+
+    pinned_keep = []
+
+    def pinned(shape, dtype):
+        """numpy view of pinned host memory (kept alive in pinned_keep)."""
+        n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        t = torch.empty(max(n, 1), dtype=torch.uint8).pin_memory()
+        pinned_keep.append(t)
+        return t.numpy()[:n].view(dtype).reshape(shape)
 
     ctx = pcseg.Context(local_rank)
     D = args.depth
     batches = [pcseg.Batch(ctx, F, ROWS, COLS) for _ in range(D)]
     batch = batches[0]
-    out_normals, out_labels = [out_normals], [out_labels]
-    try:  # one pinned output set per workspace; a host that cannot pin that much runs with fewer in flight
-        for _ in range(D - 1):
-            out_normals.append(torch.empty((F, N_PTS, 3), dtype=torch.float32).pin_memory())
-            out_labels.append(torch.empty((F, N_PTS), dtype=torch.int32).pin_memory())
+    # one pinned output set per workspace: label grid + region results (records, inlier / boundary /
+    # discontinuity lists, hulls); a host that cannot pin that much runs with fewer in flight
+    ol_np, res, res_do, on_np = [], [], [], None
+    try:
+        for _ in range(D):
+            ol_np.append(pinned((F, N_PTS), np.int32))
+            res.append(pcseg.BatchResults(F, N_PTS, hull=True, alloc=pinned))
     except RuntimeError:
-        D = min(len(out_normals), len(out_labels))
-        out_normals, out_labels = out_normals[:D], out_labels[:D]
+        D = min(len(ol_np), len(res))
+        if D == 0:
+            raise
+        ol_np, res = ol_np[:D], res[:D]
         for b in batches[D:]:
             b.close()
         batches = batches[:D]
     mode = pcseg.SEEDS_ALL_DESCENDING if args.seed_mode == "alldesc" else pcseg.SEEDS_PLANE_SUPPORT
     params = pcseg.pipeline_params(seed_mode=mode, run_cluster=True)
+    params_ps = pcseg.pipeline_params(seed_mode=pcseg.SEEDS_PLANE_SUPPORT, run_cluster=True)
     stream = torch.cuda.ExternalStream(batch.stream)
+    # device-resident arm: same job (growth + region pack with hulls), results stay in HBM
+    res_dev = [pcseg.BatchResults(F, N_PTS, hull=True, alloc=lambda shape, dtype: None) for _ in range(D)]
 
     def barrier():
         if world > 1:
@@ -290,14 +320,15 @@ def main():
             return float(t.item())
         return x
 
-    stage_acc = {"normals": 0.0, "seeds": 0.0, "planar": 0.0, "cluster": 0.0}
+    stage_acc = {"normals": 0.0, "seeds": 0.0, "planar": 0.0, "cluster": 0.0, "pack": 0.0}
 
-    def run_steps(steps, submit, collect=False):
+    def run_steps(steps, submit, collect=False, nws=None):
         """`steps` passes of the pipeline, step i on workspace i % D; a workspace is waited for
         (and its stage timers read) before it is reused, and all are drained at the end."""
+        nws = nws or D
         busy = [False] * D
         for i in range(steps):
-            j = i % D
+            j = i % nws
             if busy[j]:
                 batches[j].wait()
                 if collect:
@@ -312,7 +343,7 @@ def main():
                     for k, v in batches[j].stage_times().items():
                         stage_acc[k] += v
 
-    def timed(submit, steps, collect=False):
+    def timed(submit, steps, collect=False, nws=None):
         """K steps bracketed by barrier+sync; device time between two CUDA events on the first
         workspace's stream (idle at both records, so they bracket the whole region); also the
         host wall clock."""
@@ -320,53 +351,140 @@ def main():
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
         e0.record(stream)
-        run_steps(steps, submit, collect)
+        run_steps(steps, submit, collect, nws)
         e1.record(stream)
         e1.synchronize()
         wall = (time.perf_counter() - t0) * 1e3
         barrier()
         return max_over_ranks(e0.elapsed_time(e1)), max_over_ranks(wall)
 
+    def timed3(submit, steps, host_clock, collect=False, nws=None):
+        """Three timed regions of K steps: the median one is reported, min/max as the spread (the
+        D-workspace schedule is dynamic and moves by a few per cent run to run)."""
+        ms = []
+        for rep in range(3):
+            d, w = timed(submit, steps, collect and rep == 0, nws)
+            ms.append((max(d, w) if host_clock else d) / steps)
+        ms.sort()
+        return ms[1], ms
+
+    total_pts = F * N_PTS * world
+
+    def mpts(ms_step):
+        return total_pts / (ms_step * 1e-3) / 1e6
+
     # ---- device-resident arm (value) ----
-    submit_dev = lambda j: batches[j].submit(dev_xyz.data_ptr(), params)
+    submit_dev = lambda j: batches[j].submit_regions(dev_xyz.data_ptr(), params, res_dev[j])
     run_steps(max(args.warmup, D), submit_dev)   # every workspace allocates its buffers on first use
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
     l0 = ctx.launches
-    dev_ms, dev_wall = timed(submit_dev, args.steps, collect=True)
-    launches = ctx.launches - l0
+    ms_per_step, dev_spread = timed3(submit_dev, args.steps, host_clock=False, collect=True)
+    launches = (ctx.launches - l0) // 3
     clocks = sampler.stop() if rank == 0 else None
     stats = batch.frame_stats()
-    ms_per_step = dev_ms / args.steps
-    total_pts = F * N_PTS * world
-    value = total_pts / (ms_per_step * 1e-3) / 1e6
+    value = mpts(ms_per_step)
 
-    # ---- end-to-end arm (host buffers through the C ABI): every step copies its 256 frames in
-    # from pinned host memory and its result out.  The result of the path is the label grid (the
-    # regions' inlier sets; PlanarRegion/ClusterRegion come out, north_star); the normals are an
-    # intermediate that a caller may also ask for -- measured as a second variant. ----
+    # ---- end-to-end arm (host buffers through the C ABI): every step copies its 256 frames in from
+    # pinned host memory and copies OUT what the reference's SegmentRegions calls return: the label
+    # grid and every frame's PlanarRegion / ClusterRegion (records with plane, centroid, area,
+    # estimator sums; inlier, boundary and discontinuity index lists; convex hulls). ----
     host_np = host.numpy()
-    on_np = [t.numpy() for t in out_normals]
-    ol_np = [t.numpy() for t in out_labels]
-    submit_e2e = lambda j: batches[j].submit(host_np, params, labels_out=ol_np[j])
+    submit_e2e = lambda j: batches[j].submit_regions(host_np, params, res[j], labels_out=ol_np[j])
     run_steps(max(2, D), submit_e2e)             # staging buffers of every workspace exist before timing
-    e2e_ms, e2e_wall = timed(submit_e2e, args.steps)
-    e2e_ms_step = max(e2e_ms, e2e_wall) / args.steps
-    e2e_value = total_pts / (e2e_ms_step * 1e-3) / 1e6
-    submit_e2e_n = lambda j: batches[j].submit(host_np, params, normals_out=on_np[j], labels_out=ol_np[j])
-    run_steps(max(2, D), submit_e2e_n)
-    e2en_ms, e2en_wall = timed(submit_e2e_n, args.steps)
-    e2en_ms_step = max(e2en_ms, e2en_wall) / args.steps
-    e2en_value = total_pts / (e2en_ms_step * 1e-3) / 1e6
-    e2e_ok = int(stats[:, 5].max()) == 0
-    ol_np = ol_np[0]
+    e2e_ms_step, e2e_spread = timed3(submit_e2e, args.steps, host_clock=True)
+    e2e_value = mpts(e2e_ms_step)
+    e2e_d2h = int(F * N_PTS * 4 + res[0].d2h_bytes) * world
+    e2e_ok = int(stats[:, 5].max()) == 0 and res[0].s.error_flags == 0
+    regions_total = (int(res[0].s.n_planar), int(res[0].s.n_cluster))
+    variants = {}
+    # variant: label grid only (round 1's e2e)
+    submit_lab = lambda j: batches[j].submit(host_np, params, labels_out=ol_np[j])
+    run_steps(max(2, D), submit_lab)
+    v_ms, v_sp = timed3(submit_lab, args.steps, host_clock=True)
+    variants["labels_only"] = {"value": mpts(v_ms), "ms_per_step": v_ms, "d2h_bytes_per_step": int(F * N_PTS * 4) * world,
+                               "outputs": "label grid only"}
+    # variant: the primary seed list of SURVEY.md 8d, FindSeedPointsFromPlaneSupport on the device
+    if args.seed_mode == "alldesc":
+        submit_ps = lambda j: batches[j].submit_regions(host_np, params_ps, res[j], labels_out=ol_np[j])
+        run_steps(max(2, D), submit_ps)
+        v_ms, v_sp = timed3(submit_ps, args.steps, host_clock=True)
+        st_ps = batch.stage_times()
+        variants["seeds_planesupport"] = {"value": mpts(v_ms), "ms_per_step": v_ms, "spread_ms": v_sp,
+                                          "regions": [int(res[0].s.n_planar), int(res[0].s.n_cluster)],
+                                          "outputs": "labels + regions, planar seeds = FindSeedPointsFromPlaneSupport (device)",
+                                          "stage_ms_last_workspace_overlapped": st_ps}
+        submit_dps = lambda j: batches[j].submit_regions(dev_xyz.data_ptr(), params_ps, res_dev[j])
+        run_steps(D, submit_dps)
+        v_ms, v_sp = timed3(submit_dps, args.steps, host_clock=False)
+        variants["seeds_planesupport"]["value_device_resident"] = mpts(v_ms)
+        batch.run(dev_xyz.data_ptr(), params_ps)
+        variants["seeds_planesupport"]["stage_ms"] = batch.stage_times()
+    # variant: DetectedObjects payload as well (inlier + boundary xyz gathers of ps/detected_objects.cc:21-48);
+    # two workspaces in flight (the xyz result buffers are 1.9 GB of pinned memory each)
+    D2 = min(D, 2)
+    try:
+        keep0 = len(pinned_keep)
+        res_do = [pcseg.BatchResults(F, N_PTS, inlier_xyz=True, boundary_xyz=True, hull=True, alloc=pinned, share=res[j])
+                  for j in range(D2)]
+        submit_do = lambda j: batches[j].submit_regions(host_np, params, res_do[j], labels_out=ol_np[j])
+        run_steps(D2, submit_do, nws=D2)
+        v_ms, v_sp = timed3(submit_do, args.steps, host_clock=True, nws=D2)
+        variants["detected_objects"] = {"value": mpts(v_ms), "ms_per_step": v_ms, "spread_ms": v_sp,
+                                        "d2h_bytes_per_step": int(F * N_PTS * 4 + res_do[0].d2h_bytes) * world,
+                                        "workspaces_in_flight": D2,
+                                        "outputs": "labels + regions + inlier/boundary xyz (DetectedObjects geometry)"}
+    except RuntimeError as e:
+        variants["detected_objects"] = {"skipped": "host could not pin the xyz result buffers (%s)" % type(e).__name__}
+    res_do = None
+    del pinned_keep[keep0:]
+    # variant: normals copied back too
+    try:
+        on_np = [pinned((F, N_PTS, 3), np.float32) for _ in range(D2)]
+        submit_n = lambda j: batches[j].submit_regions(host_np, params, res[j], normals_out=on_np[j], labels_out=ol_np[j])
+        run_steps(D2, submit_n, nws=D2)
+        v_ms, v_sp = timed3(submit_n, args.steps, host_clock=True, nws=D2)
+        variants["with_normals"] = {"value": mpts(v_ms), "ms_per_step": v_ms, "workspaces_in_flight": D2,
+                                    "d2h_bytes_per_step": e2e_d2h + int(F * N_PTS * 12) * world,
+                                    "outputs": "labels + regions + normals"}
+    except RuntimeError as e:
+        variants["with_normals"] = {"skipped": "host could not pin the normals buffers (%s)" % type(e).__name__}
+    on_np = None
+    del pinned_keep[keep0:]
 
-    # ---- one batch alone, synchronous: its latency (all frames submitted up front) ----
+    # ---- host <-> device path of this box: plain pinned copies, both directions at once, all ranks
+    # together (the ceiling of any e2e number; measured, not assumed) ----
+    probe_bytes = 256 << 20
+    ph = torch.empty(probe_bytes, dtype=torch.uint8).pin_memory()
+    ph2 = torch.empty(probe_bytes, dtype=torch.uint8).pin_memory()
+    pd = torch.empty(probe_bytes, dtype=torch.uint8, device="cuda")
+    pd2 = torch.empty(probe_bytes, dtype=torch.uint8, device="cuda")
+    s_a, s_b = torch.cuda.Stream(), torch.cuda.Stream()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(4):
+        with torch.cuda.stream(s_a):
+            pd.copy_(ph, non_blocking=True)
+        with torch.cuda.stream(s_b):
+            ph2.copy_(pd2, non_blocking=True)
+    torch.cuda.synchronize()
+    probe_s = max_over_ranks(time.perf_counter() - t0)
+    barrier()
+    host_copy_gbs = world * 4 * 2 * probe_bytes / probe_s / 1e9
+    e2e_copy_gbs = (int(F * N_PTS * 12) * world + e2e_d2h) / (e2e_ms_step * 1e-3) / 1e9
+    del ph, ph2, pd, pd2
+
+    ol0 = ol_np[0]
+    run_steps(1, submit_e2e)   # workspace 0 holds the headline configuration's result again (parity check below)
+
+    # ---- one batch alone, synchronous: its latency (all 256 frames submitted up front; a frame's
+    # result is complete when its batch is, so this is every frame's completion - submit time) ----
     sync_ms = []
     for it in range(3):
         t0 = time.perf_counter()
-        batch.run(dev_xyz.data_ptr(), params)
+        batch.submit_regions(dev_xyz.data_ptr(), params, res_dev[0])
+        batch.wait()
         sync_ms.append((time.perf_counter() - t0) * 1e3)
     batch_latency_ms = statistics.median(sync_ms)
     stage_ms_sync = batch.stage_times()   # one batch alone: no other workspace's kernels beside it
@@ -398,25 +516,46 @@ def main():
                  "cluster": 24.0 * float((F * N_PTS) - int(stats[:, 2].sum()))}
     if fused:
         alg_bytes["planar"] += alg_bytes["cluster"]
+    traffic = ncu_traffic()
     roof = {}
     for k in ("normals", "planar") if fused else ("normals", "planar", "cluster"):
         ach = alg_bytes[k] / (stage_ms[k] * 1e-3) / 1e9 if stage_ms[k] > 0 else 0.0
+        kname = {"planar": "planar_grow_kernel", "normals": "normals_kernel", "cluster": "cluster_grow_kernel"}[k]
+        tr = traffic.get(kname, {})
         roof[k] = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                   "traffic": None, "kernel_ms": stage_ms[k], "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)"}
+                   "traffic": tr.get("dram_bytes_per_launch") if F == FRAMES_PER_GPU else None,
+                   "algorithmic_bytes_per_launch": alg_bytes[k],
+                   "kernel_ms": stage_ms[k], "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)"}
+        if "warp_instructions_per_point" in tr:
+            # second roof for an issue-bound kernel: warp instructions issued against 148 SMs x 4
+            # schedulers x 1 instruction / cycle at the sampled SM clock
+            mhz = (clocks or {}).get("sm_mhz") or 1965.0
+            issue_peak = 148 * 4 * mhz * 1e6
+            wi = tr["warp_instructions_per_point"] * F * N_PTS / 32.0
+            roof[k]["issue"] = {"bound": "issue", "warp_instructions_per_launch": wi,
+                                "achieved": wi / (stage_ms[k] * 1e-3) / 1e9, "peak": issue_peak / 1e9,
+                                "unit": "G warp-instr/s", "frac": wi / (stage_ms[k] * 1e-3) / issue_peak,
+                                "source": tr.get("source")}
     roofline = dict(roof[dom])
     roofline["kernel"] = {"planar": "planar_grow_kernel" + (" (planar + fused cluster growth)" if fused else ""),
                           "normals": "normals_kernel", "cluster": "cluster_grow_kernel"}[dom]
+    roofline["traffic_source"] = traffic.get("source")
     roofline["note"] = ("kernel_ms: one batch alone (CUDA events on its stream); latency-bound serial FIFO chain "
-                        "(one re-fit per 30 inliers) whose top stall is instruction fetch, not bandwidth-bound; "
-                        "see DESIGN.md section 8 and profiles/")
+                        "(one re-fit per 30 inliers), not bandwidth-bound; see DESIGN.md section 8 and profiles/")
 
-    # ---- CPU baseline: oracle port, single thread, bounded sample ----
+    # ---- CPU baseline: the reference's own sources (oracle/_ref), single thread, bounded sample;
+    # the same run is the parity check of the e2e outputs (labels + region inlier lists) ----
     ns = min(args.cpu_sample, F)
     t0 = time.perf_counter()
     mismatched_frames = 0
     for i in range(ns):
-        lab_cpu, _, _ = _cpu_pipeline(host_np[i])
-        mismatched_frames += int(not np.array_equal(lab_cpu, ol_np[i]))  # oracle as the checker
+        lab_cpu, pr, cr = _cpu_pipeline(host_np[i], want_regions=True)
+        g = res[0].frame_regions(i, "planar")
+        c = res[0].frame_regions(i, "cluster")
+        same = np.array_equal(lab_cpu, ol0[i]) and g.n == pr.n and c.n == cr.n
+        same = same and all(np.array_equal(g.inliers[k], pr.inliers[k]) for k in range(min(g.n, pr.n)))
+        same = same and all(np.array_equal(c.inliers[k], cr.inliers[k]) for k in range(min(c.n, cr.n)))
+        mismatched_frames += int(not same)  # oracle as the checker
     cpu_s = time.perf_counter() - t0
     cpu_value = ns * N_PTS / cpu_s / 1e6
 
@@ -424,25 +563,34 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic (seeded analytic ray casting, SURVEY.md 8d C2)",
-        "config": {"workload": "C2: batch of %d 640x480 organized depth frames per GPU, normals+planes+clusters, "
+        "config": {"workload": "C2: batch of %d 640x480 organized depth frames per GPU, normals+planes+clusters+region records, "
                                "planar seeds %s, frame-wise sharding" % (F, args.seed_mode),
                    "frames_per_gpu": F, "rows": ROWS, "cols": COLS, "points_per_step": total_pts,
                    "l2": "inputs larger than L2 (%.0f MB of points per GPU per step)" % (F * N_PTS * 12 / 1e6),
                    "workspaces_in_flight": D, "numa": numa},
-        "p50_frame_ms": batch_latency_ms, "latency_ms_single_frame": statistics.median(lat),
+        "value_spread_ms_per_step": dev_spread,
+        "batch_latency_ms": batch_latency_ms,
+        "p50_frame_ms": batch_latency_ms,
+        "p50_frame_ms_definition": "all frames of the batch submitted up front; every frame's result completes with its "
+                                   "batch, so completion - submit is the synchronous batch latency for each of them",
+        "latency_ms_single_frame": statistics.median(lat),
         "stage_ms": stage_ms, "stage_ms_in_timed_region_overlapped": stage_ms_overlapped,
         "regions_per_frame": {"planar": float(stats[:, 0].mean()), "cluster": float(stats[:, 1].mean())},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(F * N_PTS * 12) * world,
-                "d2h_bytes_per_step": int(F * N_PTS * 4) * world, "ms_per_step": e2e_ms_step,
-                "outputs": "labels (int32 per point) to pinned host memory", "ok": e2e_ok},
-        "e2e_with_normals": {"value": e2en_value, "unit": UNIT, "h2d_bytes_per_step": int(F * N_PTS * 12) * world,
-                             "d2h_bytes_per_step": int(F * N_PTS * 16) * world, "ms_per_step": e2en_ms_step,
-                             "outputs": "normals + labels to pinned host memory"},
+                "d2h_bytes_per_step": e2e_d2h, "ms_per_step": e2e_ms_step, "spread_ms_per_step": e2e_spread,
+                "outputs": "label grid + every frame's PlanarRegion/ClusterRegion (records, inlier / boundary / "
+                           "discontinuity index lists, convex hulls) to pinned host memory",
+                "regions_per_step": {"planar": regions_total[0], "cluster": regions_total[1]}, "ok": e2e_ok,
+                "copy_gbs_achieved": e2e_copy_gbs},
+        "e2e_variants": variants,
+        "host_copy_probe": {"gbs_both_directions_all_ranks": host_copy_gbs,
+                            "what": "4 x 256 MB pinned H2D + 4 x 256 MB D2H concurrently per rank, torch copies"},
         "gpu_launches": int(launches),
         "roofline": roofline, "roofline_all": roof,
         "cpu_baseline": {"value": cpu_value, "unit": UNIT, "cores": 1, "kind": cpu_kind(),
                          "sample": "%d frames of the same batch, single-threaded (the reference's native mode), %.1f s" % (ns, cpu_s)},
-        "parity": {"frames_checked_vs_oracle": ns, "frames_with_label_mismatch": mismatched_frames},
+        "parity": {"frames_checked_vs_oracle": ns, "frames_with_label_or_region_mismatch": mismatched_frames,
+                   "checked": "labels, region counts, every region's inlier index list"},
         "clocks": clocks, "host_cores": os.cpu_count(),
     }
     print(json.dumps(line), flush=True)

@@ -153,6 +153,65 @@ int pcseg_seeds_plane_support(pcseg_ctx*, const float* xyz, const float* normals
                               float max_plane_distance, int min_num_support,
                               int* seeds_out, int cap, int* n_out);
 
+/* Replaces ps/segmentation.h:137-184 FindSeedPointsFromAverageNormals (with the sliding window
+ * of :79-120; quirk Q1 reproduced literally, so rows <= cols is required as the reference's
+ * transposed reads would leave the buffer otherwise).  Seeds come out in the reference's order
+ * (row outer, col inner).  Returns the number of seeds in *n_out (may exceed cap; only cap are
+ * written).  neighborhood_size <= 32. */
+int pcseg_seeds_average_normals(pcseg_ctx*, const float* xyz, const float* normals,
+                                int rows, int cols, int neighborhood_size,
+                                int min_num_valid_normals, float min_avg_normal_length,
+                                int* seeds_out, int cap, int* n_out);
+
+/* Replaces ps/planar_region.h:478-519 FindSeedPointsFromLastPlanarRegions.  The previous
+ * regions are given by what the function reads of them: inlier_indices().size(), centroid(),
+ * plane().normal().  current_pose_prev = (q_xyzw, translation), an eigenmath::Pose3f.
+ * The seeds found are APPENDED to seeds_inout[*n_inout ...] (the reference does not clear its
+ * output vector) in the reference's order: previous regions by ascending inlier count,
+ * insertion order within a count (std::multimap). */
+int pcseg_seeds_last_planar_regions(pcseg_ctx*, const float* xyz, const float* normals,
+                                    int n_points, int n_prev, const int* prev_inlier_counts,
+                                    const float* prev_centroids, const float* prev_plane_normals,
+                                    const float q_xyzw[4], const float translation[3],
+                                    float max_distance, float max_normal_difference_angle,
+                                    int* seeds_inout, int cap, int* n_inout);
+
+/* ---- PlaneEstimator (ps/plane_estimator.h:37-120, ps/plane_estimator.cc:46-229) ----
+ * Query row used below: {plane valid, curvature, centroid xyz, plane normal xyz, plane offset,
+ * cumulative weight}.  Accumulator state: {covariance accumulator[6], cumulative centroid xyz,
+ * cumulative weight} -- the same 10 floats as pcseg_regions_estimators and
+ * PlaneEstimatorProto (ps/plane_estimator.proto:22-32). */
+
+/* Least-squares plane fits of n_regions index sets at once (north_star item 2): per region
+ * Clear(); [SetNormalOrientation(hint);] AddPoints(points, indices) in list order -- sequential
+ * fp32 sums, as the reference (ps/plane_estimator.h:97-103) -- then Plane()/Centroid()/Curvature().
+ * weights (nullable) per index entry: weighted AddPoint (ps/plane_estimator.cc:67-77).
+ * hints (nullable) 3 floats per region.  query_out: 10 floats per region; state_out (nullable)
+ * 10 floats per region.  A region with no entries returns the state right after Clear(). */
+int pcseg_fit_planes(pcseg_ctx*, const float* xyz, int n_points, const int* offsets,
+                     const int* indices, int n_regions, const float* weights,
+                     const float* hints, float* query_out, float* state_out);
+
+/* The whole class, op by op on ONE estimator chain (the reference's semantics including the
+ * lazy recomputation and the kept normal orientation): ops[i] with 4 float args each:
+ *   0 AddPoint(xyz)  1 AddPoint(xyz, w)  2 SetNormalOrientation(xyz)  3 query (appends a row)
+ *   4 Clear()  5 select active estimator slot x (4 slots)  6 Merge(slot x)  7 Transform(pose x)
+ *   8 Merge(slot x, pose y).   poses: 7 doubles each (quaternion xyzw, translation): Pose3d.
+ * *n_queries receives the number of rows written; PCSEG_ERR_CONFIG where the reference
+ * CHECK-aborts (Plane()/Transform() with zero weight), PCSEG_ERR_CAPACITY if cap rows are not enough. */
+int pcseg_plane_estimator_replay(pcseg_ctx*, const int* ops, const float* args, int n_ops,
+                                 const double* poses, int n_poses, float* query_out, int cap,
+                                 int* n_queries);
+
+/* Transform (ps/plane_estimator.cc:142-182) of n accumulator states in place; poses: 7 doubles,
+ * one per state (pose_per_state != 0) or one shared.  PCSEG_ERR_CONFIG if a state has weight <= 0. */
+int pcseg_plane_estimators_transform(pcseg_ctx*, float* states, int n, const double* poses,
+                                     int pose_per_state);
+/* Merge (ps/plane_estimator.cc:128-140): dst[i] += src[i], src[i] first transformed by its pose
+ * when poses is non-null (this_pose_other). */
+int pcseg_plane_estimators_merge(pcseg_ctx*, float* dst_states, const float* src_states, int n,
+                                 const double* poses, int pose_per_state);
+
 /* ---- Batched pipeline (extension: the reference has no batch entry point;
  * a caller looping ComputeNormalsOrganized -> SegmentRegions<PlanarRegion> ->
  * SegmentRegions<ClusterRegion> over independent frames binds this instead).

@@ -234,6 +234,67 @@ def plane_estimator_replay(ops):
     return out.reshape(-1, 10)[:nq]
 
 
+def plane_estimator_replay2(ops, poses=()):
+    """Extended op list (see pcseg_oracle.h): 5 select slot, 6 Merge(slot), 7 Transform(pose),
+    8 Merge(slot, pose).  poses: list of (qx, qy, qz, qw, tx, ty, tz) doubles."""
+    L = lib()
+    codes = _i32([o[0] for o in ops])
+    args = _f32([[o[1], o[2], o[3], o[4]] for o in ops]).reshape(-1)
+    pz = np.ascontiguousarray(np.asarray(poses, np.float64).reshape(-1))
+    nq = sum(1 for o in ops if o[0] == 3)
+    out = np.zeros(max(nq, 1) * 10, np.float32)
+    got = L.oracle_plane_estimator_replay2(_ptr(codes, I32P), _ptr(args, F32P), len(ops),
+                                           pz.ctypes.data_as(C.POINTER(C.c_double)), len(pz) // 7,
+                                           _ptr(out, F32P), out.size)
+    if got < 0:
+        raise ValueError("oracle_plane_estimator_replay2 status %d" % got)
+    assert got == nq, got
+    return out.reshape(-1, 10)[:nq]
+
+
+def fit_planes_csr(xyz, offsets, indices, hints=None, weights=None):
+    """PlaneEstimator over CSR index sets (ps/plane_estimator.h:97-103 AddPoints(points, indices) per
+    region, after SetNormalOrientation(hint) when hints are given; weighted AddPoint when weights are).
+    Returns [n, 10] query rows {valid, curvature, centroid xyz, normal xyz, offset, weight}; a region
+    with no points gives the state right after Clear()."""
+    xyz = _f32(xyz).reshape(-1, 3)
+    offsets = np.asarray(offsets)
+    rows = []
+    for r in range(len(offsets) - 1):
+        ops = []
+        if hints is not None:
+            ops.append((2, *[float(v) for v in hints[r]], 0.0))
+        for k in range(int(offsets[r]), int(offsets[r + 1])):
+            pt = xyz[int(indices[k])]
+            if weights is None:
+                ops.append((0, float(pt[0]), float(pt[1]), float(pt[2]), 0.0))
+            else:
+                ops.append((1, float(pt[0]), float(pt[1]), float(pt[2]), float(weights[k])))
+        ops.append((3, 0, 0, 0, 0))
+        rows.append(plane_estimator_replay(ops)[0])
+    return np.asarray(rows, np.float32).reshape(-1, 10)
+
+
+def seeds_last_planar_regions(xyz, normals, prev_inlier_counts, prev_centroids, prev_normals,
+                              q_xyzw=(0, 0, 0, 1), translation=(0, 0, 0), max_distance=0.5,
+                              max_normal_difference_angle=0.2):
+    """ps/planar_region.h:478-519; returns the appended seed indices."""
+    L = lib()
+    xyz = _f32(xyz).reshape(-1)
+    normals = _f32(normals).reshape(-1)
+    cnt = _i32(prev_inlier_counts)
+    cen = _f32(prev_centroids).reshape(-1)
+    nrm = _f32(prev_normals).reshape(-1)
+    q = (C.c_float * 4)(*[float(v) for v in q_xyzw])
+    t = (C.c_float * 3)(*[float(v) for v in translation])
+    out = np.zeros(max(len(cnt), 1), np.int32)
+    n = L.oracle_seeds_last_planar_regions(_ptr(xyz, F32P), _ptr(normals, F32P), xyz.size // 3, len(cnt),
+                                           _ptr(cnt, I32P), _ptr(cen, F32P), _ptr(nrm, F32P), q, t,
+                                           C.c_float(max_distance), C.c_float(max_normal_difference_angle),
+                                           _ptr(out, I32P))
+    return out[:n].copy()
+
+
 def eig3(a6):
     L = lib()
     a = _f32(a6)

@@ -308,6 +308,66 @@ class PlaneEstimator {
       plane_.n = hint;
     }
   }
+  void Merge(const PlaneEstimator& o) {  // .cc:128-133
+    for (int i = 0; i < 6; ++i) accumulator_[i] += o.accumulator_[i];
+    cumulative_centroid_ = cumulative_centroid_ + o.cumulative_centroid_;
+    cumulative_weights_ += o.cumulative_weights_;
+    plane_up_to_date_ = false;
+  }
+  // Transform(const Pose3d& new_pose_current), .cc:142-182.  pose = quaternion xyzw + translation in
+  // double: rotationMatrix() is evaluated in double and cast to float (:159-160), the pose itself is
+  // cast to float before it is applied to the centroid (:164).
+  void Transform(const double q[4], const double t[3]) {
+    if (!(cumulative_weights_ > 0.0f)) abort();  // CHECK_GT(cumulative_weights_, 0.0f)
+    if (!plane_up_to_date_) centroid_ = cumulative_centroid_ / cumulative_weights_;
+    float accu[6];
+    for (int i = 0; i < 6; ++i) accu[i] = accumulator_[i] / cumulative_weights_;
+    M3 cov;
+    cov.m[0] = accu[0] - centroid_.x * centroid_.x;
+    cov.m[1] = accu[1] - centroid_.x * centroid_.y;
+    cov.m[2] = accu[2] - centroid_.x * centroid_.z;
+    cov.m[4] = accu[3] - centroid_.y * centroid_.y;
+    cov.m[5] = accu[4] - centroid_.y * centroid_.z;
+    cov.m[8] = accu[5] - centroid_.z * centroid_.z;
+    cov.m[3] = cov.m[1];
+    cov.m[6] = cov.m[2];
+    cov.m[7] = cov.m[5];
+    // Quaterniond::toRotationMatrix (Geometry/Quaternion.h), then .cast<float>()
+    const double tx = 2.0 * q[0], ty = 2.0 * q[1], tz = 2.0 * q[2];
+    const double twx = tx * q[3], twy = ty * q[3], twz = tz * q[3];
+    const double txx = tx * q[0], txy = ty * q[0], txz = tz * q[0];
+    const double tyy = ty * q[1], tyz = tz * q[1], tzz = tz * q[2];
+    M3 rot;
+    rot(0, 0) = (float)(1.0 - (tyy + tzz)); rot(0, 1) = (float)(txy - twz); rot(0, 2) = (float)(txz + twy);
+    rot(1, 0) = (float)(txy + twz); rot(1, 1) = (float)(1.0 - (txx + tzz)); rot(1, 2) = (float)(tyz - twx);
+    rot(2, 0) = (float)(txz - twy); rot(2, 1) = (float)(tyz + twx); rot(2, 2) = (float)(1.0 - (txx + tyy));
+    // rotation * covariance * rotation.transpose(): lazy coefficient products, each a 3-term
+    // reduction e0 + (e1 + e2); the left product is evaluated into a temporary first
+    M3 rc, out;
+    for (int c = 0; c < 3; ++c)
+      for (int r = 0; r < 3; ++r)
+        rc(r, c) = rot(r, 0) * cov(0, c) + (rot(r, 1) * cov(1, c) + rot(r, 2) * cov(2, c));
+    for (int c = 0; c < 3; ++c)
+      for (int r = 0; r < 3; ++r)
+        out(r, c) = rc(r, 0) * rot(c, 0) + (rc(r, 1) * rot(c, 1) + rc(r, 2) * rot(c, 2));
+    const Quat qf{(float)q[0], (float)q[1], (float)q[2], (float)q[3]};
+    const V3 tf{(float)t[0], (float)t[1], (float)t[2]};
+    const V3 nc = rotate(qf, centroid_) + tf;
+    accumulator_[0] = out.m[0] + nc.x * nc.x;
+    accumulator_[1] = out.m[1] + nc.x * nc.y;
+    accumulator_[2] = out.m[2] + nc.x * nc.z;
+    accumulator_[3] = out.m[4] + nc.y * nc.y;
+    accumulator_[4] = out.m[5] + nc.y * nc.z;
+    accumulator_[5] = out.m[8] + nc.z * nc.z;
+    for (float& a : accumulator_) a *= cumulative_weights_;
+    cumulative_centroid_ = V3{nc.x * cumulative_weights_, nc.y * cumulative_weights_, nc.z * cumulative_weights_};
+    plane_up_to_date_ = false;
+  }
+  void MergeWithPose(const PlaneEstimator& o, const double q[4], const double t[3]) {  // .cc:135-140
+    PlaneEstimator other(o);
+    other.Transform(q, t);
+    Merge(other);
+  }
   float weight() const { return cumulative_weights_; }
   void state(float out[10]) const {
     for (int i = 0; i < 6; ++i) out[i] = accumulator_[i];
@@ -996,9 +1056,17 @@ int oracle_find_normal_support_neighbors(const float* xyz, int rows, int cols,
 
 int oracle_plane_estimator_replay(const int* ops, const float* args, int n_ops,
                                   float* out, int out_cap) {
-  PlaneEstimator est;
+  return oracle_plane_estimator_replay2(ops, args, n_ops, nullptr, 0, out, out_cap);
+}
+
+int oracle_plane_estimator_replay2(const int* ops, const float* args, int n_ops,
+                                   const double* poses, int n_poses,
+                                   float* out, int out_cap) {
+  PlaneEstimator slots[4];
+  int cur = 0;
   int nq = 0;
   for (int i = 0; i < n_ops; ++i) {
+    PlaneEstimator& est = slots[cur];
     V3 p{args[4 * i], args[4 * i + 1], args[4 * i + 2]};
     float w = args[4 * i + 3];
     switch (ops[i]) {
@@ -1028,6 +1096,32 @@ int oracle_plane_estimator_replay(const int* ops, const float* args, int n_ops,
         break;
       }
       case 4: est.Clear(); break;
+      case 5: {  // select the active estimator
+        const int k = (int)p.x;
+        if (k < 0 || k >= 4) return -2;
+        cur = k;
+        break;
+      }
+      case 6: {  // Merge(other)
+        const int k = (int)p.x;
+        if (k < 0 || k >= 4 || k == cur) return -2;
+        est.Merge(slots[k]);
+        break;
+      }
+      case 7: {  // Transform(pose)
+        const int pi = (int)p.x;
+        if (pi < 0 || pi >= n_poses) return -2;
+        if (!(est.weight() > 0.0f)) return -3;  // CHECK_GT
+        est.Transform(poses + 7 * pi, poses + 7 * pi + 4);
+        break;
+      }
+      case 8: {  // Merge(other, this_pose_other)
+        const int k = (int)p.x, pi = (int)p.y;
+        if (k < 0 || k >= 4 || k == cur || pi < 0 || pi >= n_poses) return -2;
+        if (!(slots[k].weight() > 0.0f)) return -3;
+        est.MergeWithPose(slots[k], poses + 7 * pi, poses + 7 * pi + 4);
+        break;
+      }
       default: return -2;
     }
   }
@@ -1335,6 +1429,43 @@ int oracle_seeds_average_normals(const float* xyz, const float* normals,
         ++k;
       }
     }
+  }
+  return k;
+}
+
+// FindSeedPointsFromLastPlanarRegions, ps/planar_region.h:478-519.  prev_* describe the previous
+// regions (inlier_indices().size(), centroid(), plane().normal()); the multimap orders them by
+// inlier count, insertion order within a count.  Returns the number of seeds appended.
+int oracle_seeds_last_planar_regions(const float* xyz, const float* normals, int n_points, int n_prev,
+                                     const int* prev_inlier_counts, const float* prev_centroids,
+                                     const float* prev_normals, const float q_xyzw[4], const float t[3],
+                                     float max_distance, float max_normal_difference_angle, int* seeds_out) {
+  const float kMaxSq = max_distance * max_distance;
+  const float kCos = o_cosf(max_normal_difference_angle);
+  const Quat q{q_xyzw[0], q_xyzw[1], q_xyzw[2], q_xyzw[3]};
+  const V3 tr{t[0], t[1], t[2]};
+  struct SeedPoint { V3 point, normal; };
+  std::multimap<int, SeedPoint> past;
+  for (int i = 0; i < n_prev; ++i) {
+    const V3 c{prev_centroids[3 * i], prev_centroids[3 * i + 1], prev_centroids[3 * i + 2]};
+    const V3 n{prev_normals[3 * i], prev_normals[3 * i + 1], prev_normals[3 * i + 2]};
+    past.emplace(prev_inlier_counts[i], SeedPoint{rotate(q, c) + tr, rotate(q, n)});
+  }
+  int k = 0;
+  for (const auto& kv : past) {
+    const SeedPoint& sp = kv.second;
+    float min_sq = kMaxSq;
+    int min_idx = -1;
+    for (int j = 0; j < n_points; ++j) {
+      const V3 p{xyz[3 * j], xyz[3 * j + 1], xyz[3 * j + 2]};
+      const V3 nr{normals[3 * j], normals[3 * j + 1], normals[3 * j + 2]};
+      const float sq = sqnorm(sp.point - p);
+      if (sq < min_sq && dot(sp.normal, nr) > kCos) {
+        min_sq = sq;
+        min_idx = j;
+      }
+    }
+    if (min_idx >= 0) seeds_out[k++] = min_idx;
   }
   return k;
 }

@@ -76,6 +76,14 @@ int oracle_find_normal_support_neighbors(const float* xyz, int rows, int cols,
 int oracle_plane_estimator_replay(const int* ops, const float* args, int n_ops,
                                   float* out, int out_cap);
 
+/* Same with the rest of the class (ps/plane_estimator.cc:128-182): four estimator slots and
+ *         5 = select active slot x, 6 = Merge(slot x), 7 = Transform(pose x),
+ *         8 = Merge(slot x, pose y).  poses: 7 doubles each (quaternion xyzw, translation),
+ * an eigenmath::Pose3d.  Returns -3 where the reference would CHECK-abort (zero weight). */
+int oracle_plane_estimator_replay2(const int* ops, const float* args, int n_ops,
+                                   const double* poses, int n_poses,
+                                   float* out, int out_cap);
+
 /* Eigen 3.4.0 SelfAdjointEigenSolver<Matrix3f>::computeDirect restated.
  * a = 6 floats (m00,m10,m20,m11,m21,m22); evals[3]; evecs col-major 9. */
 void oracle_eig3(const float* a, float* evals, float* evecs);
@@ -121,6 +129,14 @@ int oracle_seeds_average_normals(const float* xyz, const float* normals,
                                  int min_num_valid_normals,
                                  float min_avg_normal_length, int* seeds_out,
                                  int cap);
+
+/* ps/planar_region.h:478-519 FindSeedPointsFromLastPlanarRegions; previous regions given by
+ * inlier count, centroid and plane normal; pose = current_pose_prev (Pose3f).  seeds_out has room
+ * for n_prev entries; returns the number appended. */
+int oracle_seeds_last_planar_regions(const float* xyz, const float* normals, int n_points, int n_prev,
+                                     const int* prev_inlier_counts, const float* prev_centroids,
+                                     const float* prev_normals, const float q_xyzw[4], const float t[3],
+                                     float max_distance, float max_normal_difference_angle, int* seeds_out);
 
 /* ps/multichannel_cloud.cc:53-68 MultichannelCloud::TransformInPlace (either array nullable).
  * Port only: the reference's class needs the generated proto headers. */

@@ -110,12 +110,54 @@ int oracle_find_normal_support_neighbors(const float* xyz, int rows, int cols, i
 }
 
 int oracle_plane_estimator_replay(const int* ops, const float* args, int n_ops, float* out, int out_cap) {
-  mobility::PlaneEstimator est;
+  return oracle_plane_estimator_replay2(ops, args, n_ops, nullptr, 0, out, out_cap);
+}
+
+int oracle_plane_estimator_replay2(const int* ops, const float* args, int n_ops, const double* poses, int n_poses,
+                                   float* out, int out_cap) {
+  mobility::PlaneEstimator slots[4];
+  int cur = 0;
   int nq = 0;
+  auto pose = [&](int k) {
+    const double* q = poses + 7 * k;
+    return eigenmath::Pose3d(eigenmath::Quaterniond(q[3], q[0], q[1], q[2]), eigenmath::Vector3d(q[4], q[5], q[6]));
+  };
+  auto weight = [](const mobility::PlaneEstimator& e) {
+    mobility::PlaneEstimatorProto proto;
+    e.ToProto(&proto);
+    return proto.cumulative_weights();
+  };
   for (int i = 0; i < n_ops; ++i) {
+    mobility::PlaneEstimator& est = slots[cur];
     const float* a = args + 4 * i;
     const Vector3f p(a[0], a[1], a[2]);
     switch (ops[i]) {
+      case 5: {
+        const int k = static_cast<int>(a[0]);
+        if (k < 0 || k >= 4) return -2;
+        cur = k;
+        break;
+      }
+      case 6: {
+        const int k = static_cast<int>(a[0]);
+        if (k < 0 || k >= 4 || k == cur) return -2;
+        est.Merge(slots[k]);
+        break;
+      }
+      case 7: {
+        const int pi = static_cast<int>(a[0]);
+        if (pi < 0 || pi >= n_poses) return -2;
+        if (!(weight(est) > 0.0f)) return -3;  // the reference CHECK-aborts
+        est.Transform(pose(pi));
+        break;
+      }
+      case 8: {
+        const int k = static_cast<int>(a[0]), pi = static_cast<int>(a[1]);
+        if (k < 0 || k >= 4 || k == cur || pi < 0 || pi >= n_poses) return -2;
+        if (!(weight(slots[k]) > 0.0f)) return -3;
+        est.Merge(slots[k], pose(pi));
+        break;
+      }
       case 0: est.AddPoint(p); break;
       case 1: est.AddPoint(p, a[3]); break;
       case 2: est.SetNormalOrientation(p); break;
@@ -313,6 +355,29 @@ int oracle_seeds_average_normals(const float* xyz, const float* normals, int row
     for (int i = 0; i < n && i < cap; ++i) seeds_out[i] = s[i];
   });
   return n;
+}
+
+int oracle_seeds_last_planar_regions(const float* xyz, const float* normals, int n_points, int n_prev,
+                                     const int* prev_inlier_counts, const float* prev_centroids,
+                                     const float* prev_normals, const float q_xyzw[4], const float t[3],
+                                     float max_distance, float max_normal_difference_angle, int* seeds_out) {
+  auto p = PointsView(xyz, 1, n_points);
+  auto nr = PointsView(normals, 1, n_points);
+  std::vector<mobility::PlanarRegion<>> prev(n_prev, mobility::PlanarRegion<>(mobility::PlanarRegionConfigProto()));
+  for (int i = 0; i < n_prev; ++i) {
+    prev[i].MutableInlierIndicesForTestOnly()->assign(prev_inlier_counts[i], 0);
+    *prev[i].mutable_centroid() = Vector3f(prev_centroids[3 * i], prev_centroids[3 * i + 1], prev_centroids[3 * i + 2]);
+    *prev[i].mutable_plane() = eigenmath::Plane3f(
+        Vector3f(prev_normals[3 * i], prev_normals[3 * i + 1], prev_normals[3 * i + 2]), Vector3f(0.0f, 0.0f, 0.0f));
+  }
+  const eigenmath::Pose3f pose(eigenmath::Quaternionf(q_xyzw[3], q_xyzw[0], q_xyzw[1], q_xyzw[2]),
+                               Vector3f(t[0], t[1], t[2]));
+  std::vector<int> seeds;
+  mobility::FindSeedPointsFromLastPlanarRegions(static_cast<const Cloud<Vector3f>&>(p),
+                                                static_cast<const Cloud<Vector3f>&>(nr), prev, pose, max_distance,
+                                                max_normal_difference_angle, &seeds);
+  for (size_t i = 0; i < seeds.size(); ++i) seeds_out[i] = seeds[i];
+  return static_cast<int>(seeds.size());
 }
 
 int oracle_regions_count(const oracle_regions* r) { return static_cast<int>(r->label_ids.size()); }

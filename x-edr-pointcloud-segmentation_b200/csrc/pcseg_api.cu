@@ -20,6 +20,7 @@
 #include "normals.cuh"
 #include "seeds.cuh"
 #include "results_pack.cuh"
+#include "plane_estimator.cuh"
 
 using namespace pcseg;
 
@@ -428,7 +429,8 @@ int run_pack(pcseg_batch* b, int f0, int nf, const PackWant& w) {
   pack_offsets_kernel<<<1, 1024, 0, stream>>>(a);
   const int slices = std::max(1, std::min(64, (148 * 8 + nf - 1) / nf));
   pack_bulk_kernel<<<dim3(slices, nf), 256, 0, stream>>>(a);
-  pack_region_kernel<<<nf, kPackBlock, 0, stream>>>(a);
+  CU_TRY(c, cudaFuncSetAttribute(pack_region_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPackRegionSmem));
+  pack_region_kernel<<<nf, kPackBlock, kPackRegionSmem, stream>>>(a);
   c->launches += 3;
   CU_TRY(c, cudaGetLastError());
   int* h = b->h_meta;
@@ -832,6 +834,218 @@ int pcseg_seeds_plane_support(pcseg_ctx* c, const float* xyz, const float* norma
   if (ncopy > 0 && (st = from_device(c, seeds_out, b->seeds.p, (size_t)ncopy * sizeof(int)))) return st;
   CU_TRY(c, cudaStreamSynchronize(c->stream));
   return PCSEG_OK;
+}
+
+int pcseg_seeds_average_normals(pcseg_ctx* c, const float* xyz, const float* normals, int rows, int cols,
+                                int neighborhood_size, int min_num_valid_normals, float min_avg_normal_length,
+                                int* seeds_out, int cap, int* n_out) {
+  if (!c || !xyz || !normals || !seeds_out || !n_out) return PCSEG_ERR_NULL;
+  if (rows <= 1 || cols <= 0) return PCSEG_ERR_DIMS;  // CHECK_GT(points.Rows(), 1), ps/segmentation.h:143
+  if (rows > cols) return PCSEG_ERR_UNSUPPORTED;       // transposed reads leave the buffer (UB in the reference)
+  if (neighborhood_size < 1 || neighborhood_size > kAvgMaxNbhd) return PCSEG_ERR_UNSUPPORTED;
+  *n_out = 0;
+  if (rows < neighborhood_size || cols < neighborhood_size) return PCSEG_OK;  // :150-152
+  cudaSetDevice(c->device);
+  pcseg_batch* b;
+  int st = get_scratch(c, rows, cols, &b);
+  if (st) return st;
+  const size_t N = b->N;
+  const void* nrm_dev;
+  if ((st = to_device(c, normals, N * 3 * sizeof(float), &b->normals, &nrm_dev))) return st;
+  CU_TRY(c, b->seeds.ensure(N * sizeof(int)));
+  CU_TRY(c, b->n_seeds.ensure(sizeof(int)));
+  AvgSeedArgs a;
+  a.normals = (const float*)nrm_dev; a.rows = rows; a.cols = cols;
+  a.nbhd = neighborhood_size; a.half = neighborhood_size / 2; a.min_valid = min_num_valid_normals;
+  a.sq_min_len = min_avg_normal_length * min_avg_normal_length;  // :146-147
+  a.flags = b->queue.as<unsigned char>(); a.flag_stride = N;      // scratch: the idle growth queue
+  a.seeds = b->seeds.as<int>(); a.stride = (int)N; a.n_seeds = b->n_seeds.as<int>();
+  const int nrows = rows - 2 * a.half;
+  seed_avg_normals_flag_kernel<<<dim3((nrows + 63) / 64, 1), 64, 0, c->stream>>>(a);
+  seed_avg_normals_order_kernel<<<1, 1024, 0, c->stream>>>(a);
+  c->launches += 2;
+  CU_TRY(c, cudaGetLastError());
+  int n = 0;
+  CU_TRY(c, cudaMemcpyAsync(&n, b->n_seeds.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  *n_out = n;
+  const int ncopy = std::min(n, cap);
+  if (ncopy > 0 && (st = from_device(c, seeds_out, b->seeds.p, (size_t)ncopy * sizeof(int)))) return st;
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  return PCSEG_OK;
+}
+
+int pcseg_seeds_last_planar_regions(pcseg_ctx* c, const float* xyz, const float* normals, int n_points, int n_prev,
+                                    const int* prev_inlier_counts, const float* prev_centroids,
+                                    const float* prev_plane_normals, const float q_xyzw[4], const float translation[3],
+                                    float max_distance, float max_normal_difference_angle, int* seeds_inout, int cap,
+                                    int* n_inout) {
+  if (!c || !xyz || !normals || !q_xyzw || !translation || !seeds_inout || !n_inout) return PCSEG_ERR_NULL;
+  if (n_prev > 0 && (!prev_inlier_counts || !prev_centroids || !prev_plane_normals)) return PCSEG_ERR_NULL;
+  if (n_points < 0 || n_prev < 0 || *n_inout < 0) return PCSEG_ERR_DIMS;
+  if (n_prev == 0 || n_points == 0) return PCSEG_OK;
+  cudaSetDevice(c->device);
+  // std::multimap<int, SeedPoint>: ascending inlier count, insertion order within a count (:490-498)
+  std::vector<int> order(n_prev);
+  for (int i = 0; i < n_prev; ++i) order[i] = i;
+  std::stable_sort(order.begin(), order.end(), [&](int l, int r) { return prev_inlier_counts[l] < prev_inlier_counts[r]; });
+  std::vector<float> cen(3 * (size_t)n_prev), nrm(3 * (size_t)n_prev);
+  for (int i = 0; i < n_prev; ++i)
+    for (int k = 0; k < 3; ++k) {
+      cen[3 * i + k] = prev_centroids[3 * order[i] + k];
+      nrm[3 * i + k] = prev_plane_normals[3 * order[i] + k];
+    }
+  DevBuf sx, sn, sc, sp, so;
+  const void *xyz_dev, *nrm_dev;
+  int st;
+  if ((st = to_device(c, xyz, (size_t)n_points * 3 * sizeof(float), &sx, &xyz_dev))) return st;
+  if ((st = to_device(c, normals, (size_t)n_points * 3 * sizeof(float), &sn, &nrm_dev))) return st;
+  CU_TRY(c, sc.ensure(cen.size() * sizeof(float)));
+  CU_TRY(c, sp.ensure(nrm.size() * sizeof(float)));
+  CU_TRY(c, so.ensure((size_t)n_prev * sizeof(int)));
+  CU_TRY(c, cudaMemcpyAsync(sc.p, cen.data(), cen.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+  CU_TRY(c, cudaMemcpyAsync(sp.p, nrm.data(), nrm.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+  LastSeedArgs a;
+  a.xyz = (const float*)xyz_dev; a.normals = (const float*)nrm_dev; a.n_points = n_points;
+  a.centroids = sc.as<float>(); a.pnormals = sp.as<float>();
+  a.qx = q_xyzw[0]; a.qy = q_xyzw[1]; a.qz = q_xyzw[2]; a.qw = q_xyzw[3];
+  a.tx = translation[0]; a.ty = translation[1]; a.tz = translation[2];
+  a.max_sq = max_distance * max_distance;                                  // :485
+  a.cos_max = (float)std::cos((double)max_normal_difference_angle);        // cosf, :486 (libm policy)
+  a.out = so.as<int>();
+  seed_last_regions_kernel<<<n_prev, 512, 0, c->stream>>>(a);
+  ++c->launches;
+  CU_TRY(c, cudaGetLastError());
+  std::vector<int> found(n_prev);
+  CU_TRY(c, cudaMemcpyAsync(found.data(), so.p, (size_t)n_prev * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  int n = *n_inout;
+  bool fits = true;
+  for (int i = 0; i < n_prev; ++i)
+    if (found[i] >= 0) {
+      if (n < cap) seeds_inout[n] = found[i];
+      else fits = false;
+      ++n;
+    }
+  *n_inout = n;
+  return fits ? PCSEG_OK : PCSEG_ERR_CAPACITY;
+}
+
+int pcseg_fit_planes(pcseg_ctx* c, const float* xyz, int n_points, const int* offsets, const int* indices,
+                     int n_regions, const float* weights, const float* hints, float* query_out, float* state_out) {
+  if (!c || !xyz || !offsets || !query_out) return PCSEG_ERR_NULL;
+  if (n_points < 0 || n_regions < 0) return PCSEG_ERR_DIMS;
+  if (n_regions == 0) return PCSEG_OK;
+  cudaSetDevice(c->device);
+  // the CSR must be well-formed (AtUnsafe would read out of bounds): host-resident lists are checked
+  int total = 0;
+  if (!is_device_ptr(offsets)) {
+    for (int r = 0; r < n_regions; ++r)
+      if (offsets[r] < 0 || offsets[r + 1] < offsets[r]) return PCSEG_ERR_DIMS;
+    total = offsets[n_regions];
+  } else {
+    CU_TRY(c, cudaMemcpy(&total, offsets + n_regions, sizeof(int), cudaMemcpyDeviceToHost));
+  }
+  if (total > 0 && !indices) return PCSEG_ERR_NULL;
+  if (total > 0 && !is_device_ptr(indices))
+    for (int i = 0; i < total; ++i)
+      if (indices[i] < 0 || indices[i] >= n_points) return PCSEG_ERR_SEED_RANGE;
+  DevBuf sx, so, si, sw, sh, sq, ss;
+  const void *xyz_dev, *off_dev, *idx_dev = nullptr, *w_dev = nullptr, *h_dev = nullptr;
+  int st;
+  if ((st = to_device(c, xyz, (size_t)n_points * 3 * sizeof(float), &sx, &xyz_dev))) return st;
+  if ((st = to_device(c, offsets, ((size_t)n_regions + 1) * sizeof(int), &so, &off_dev))) return st;
+  if (total > 0 && (st = to_device(c, indices, (size_t)total * sizeof(int), &si, &idx_dev))) return st;
+  if (weights && total > 0 && (st = to_device(c, weights, (size_t)total * sizeof(float), &sw, &w_dev))) return st;
+  if (hints && (st = to_device(c, hints, (size_t)n_regions * 3 * sizeof(float), &sh, &h_dev))) return st;
+  const bool q_dev = is_device_ptr(query_out), s_dev = state_out && is_device_ptr(state_out);
+  FitArgs a;
+  a.xyz = (const float*)xyz_dev; a.offsets = (const int*)off_dev; a.indices = (const int*)idx_dev;
+  a.weights = (const float*)w_dev; a.hints = (const float*)h_dev; a.n_regions = n_regions;
+  a.query = query_out; a.state = state_out;
+  if (!q_dev) { CU_TRY(c, sq.ensure((size_t)n_regions * 10 * sizeof(float))); a.query = sq.as<float>(); }
+  if (state_out && !s_dev) { CU_TRY(c, ss.ensure((size_t)n_regions * 10 * sizeof(float))); a.state = ss.as<float>(); }
+  const int blocks = std::min((n_regions + kFitWarps - 1) / kFitWarps, 148 * 8);
+  fit_planes_csr_kernel<<<blocks, 32 * kFitWarps, 0, c->stream>>>(a);
+  ++c->launches;
+  CU_TRY(c, cudaGetLastError());
+  if (!q_dev) CU_TRY(c, cudaMemcpyAsync(query_out, a.query, (size_t)n_regions * 10 * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+  if (state_out && !s_dev) CU_TRY(c, cudaMemcpyAsync(state_out, a.state, (size_t)n_regions * 10 * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  return PCSEG_OK;
+}
+
+int pcseg_plane_estimator_replay(pcseg_ctx* c, const int* ops, const float* args, int n_ops, const double* poses,
+                                 int n_poses, float* query_out, int cap, int* n_queries) {
+  if (!c || !n_queries || (n_ops > 0 && (!ops || !args)) || (cap > 0 && !query_out)) return PCSEG_ERR_NULL;
+  if (n_ops < 0 || n_poses < 0 || cap < 0 || (n_poses > 0 && !poses)) return PCSEG_ERR_DIMS;
+  *n_queries = 0;
+  if (n_ops == 0) return PCSEG_OK;
+  cudaSetDevice(c->device);
+  DevBuf so, sa, sp, sq, sr;
+  const void *ops_dev, *args_dev, *poses_dev = nullptr;
+  int st;
+  if ((st = to_device(c, ops, (size_t)n_ops * sizeof(int), &so, &ops_dev))) return st;
+  if ((st = to_device(c, args, (size_t)n_ops * 4 * sizeof(float), &sa, &args_dev))) return st;
+  if (n_poses > 0 && (st = to_device(c, poses, (size_t)n_poses * 7 * sizeof(double), &sp, &poses_dev))) return st;
+  CU_TRY(c, sq.ensure(std::max<size_t>(1, (size_t)cap) * 10 * sizeof(float)));
+  CU_TRY(c, sr.ensure(sizeof(int)));
+  ReplayArgs a;
+  a.ops = (const int*)ops_dev; a.args = (const float*)args_dev; a.n_ops = n_ops;
+  a.poses = (const double*)poses_dev; a.n_poses = n_poses;
+  a.out = sq.as<float>(); a.cap = cap; a.result = sr.as<int>();
+  estimator_replay_kernel<<<1, 32, 0, c->stream>>>(a);
+  ++c->launches;
+  CU_TRY(c, cudaGetLastError());
+  int res = 0;
+  CU_TRY(c, cudaMemcpyAsync(&res, sr.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  if (res == -1) return PCSEG_ERR_CAPACITY;
+  if (res == -2) return PCSEG_ERR_UNSUPPORTED;
+  if (res < 0) return PCSEG_ERR_CONFIG;  // CHECK_GT(cumulative_weights_, 0.0f)
+  *n_queries = res;
+  if (res > 0) {
+    cudaMemcpyKind k = is_device_ptr(query_out) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+    CU_TRY(c, cudaMemcpyAsync(query_out, sq.p, (size_t)res * 10 * sizeof(float), k, c->stream));
+    CU_TRY(c, cudaStreamSynchronize(c->stream));
+  }
+  return PCSEG_OK;
+}
+
+namespace {
+int estimators_apply(pcseg_ctx* c, float* dst, const float* src, int n, const double* poses, int per_state, bool merge) {
+  if (!c || !dst || (merge && !src) || (!merge && !poses)) return PCSEG_ERR_NULL;
+  if (n < 0) return PCSEG_ERR_DIMS;
+  if (n == 0) return PCSEG_OK;
+  cudaSetDevice(c->device);
+  DevBuf sd, ss, sp, se;
+  const size_t bytes = (size_t)n * 10 * sizeof(float);
+  const void *dst_dev, *src_dev = nullptr, *poses_dev = nullptr;
+  int st;
+  const bool d_dev = is_device_ptr(dst);
+  if ((st = to_device(c, dst, bytes, &sd, &dst_dev))) return st;
+  if (merge && (st = to_device(c, src, bytes, &ss, &src_dev))) return st;
+  if (poses && (st = to_device(c, poses, (size_t)(per_state ? n : 1) * 7 * sizeof(double), &sp, &poses_dev))) return st;
+  CU_TRY(c, se.ensure(sizeof(int)));
+  CU_TRY(c, cudaMemsetAsync(se.p, 0, sizeof(int), c->stream));
+  const int blocks = (n + 127) / 128, stride = per_state ? 7 : 0;
+  if (merge) estimator_merge_kernel<<<blocks, 128, 0, c->stream>>>((float*)dst_dev, (const float*)src_dev, n, (const double*)poses_dev, stride, se.as<int>());
+  else estimator_transform_kernel<<<blocks, 128, 0, c->stream>>>((float*)dst_dev, n, (const double*)poses_dev, stride, se.as<int>());
+  ++c->launches;
+  CU_TRY(c, cudaGetLastError());
+  int err = 0;
+  CU_TRY(c, cudaMemcpyAsync(&err, se.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  if (!d_dev) CU_TRY(c, cudaMemcpyAsync(dst, dst_dev, bytes, cudaMemcpyDeviceToHost, c->stream));
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  return err ? PCSEG_ERR_CONFIG : PCSEG_OK;
+}
+}  // namespace
+
+int pcseg_plane_estimators_transform(pcseg_ctx* c, float* states, int n, const double* poses, int pose_per_state) {
+  return estimators_apply(c, states, nullptr, n, poses, pose_per_state, false);
+}
+int pcseg_plane_estimators_merge(pcseg_ctx* c, float* dst, const float* src, int n, const double* poses, int pose_per_state) {
+  return estimators_apply(c, dst, src, n, poses, pose_per_state, true);
 }
 
 int pcseg_mean_shift_modes_range(pcseg_ctx* c, const float* xyz, int rows, int cols, const int* labels,

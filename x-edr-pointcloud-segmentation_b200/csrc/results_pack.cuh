@@ -165,8 +165,10 @@ __device__ __forceinline__ float ord2f(unsigned o) {
   return __uint_as_float((o & 0x80000000u) ? (o & 0x7fffffffu) : ~o);
 }
 
-constexpr int kPackSortSmem = 4096;  // keys sorted in shared memory; longer lists use the frame's scratch
+constexpr int kPackSortSmem = 4096;  // keys sorted in shared memory (two buffers); longer lists use the frame's scratch
 constexpr int kPackBlock = 256;
+constexpr int kPackChunk = 32;       // points per thread in a hull filter round
+constexpr size_t kPackRegionSmem = 2 * (size_t)kPackSortSmem * sizeof(unsigned long long);
 
 __device__ __forceinline__ int next_pow2(int n) {
   int p = 1;
@@ -174,14 +176,57 @@ __device__ __forceinline__ int next_pow2(int n) {
   return p;
 }
 
-// cross((a - o), (b - o)) in double, as the restated collision::ConvexHull (oracle/shims/collision/convex_hull.h)
+// cross((a - o), (b - o)) in double, as the restated collision::ConvexHull (oracle/shims/collision/convex_hull.h).
+// Inputs are floats widened to double: the differences and products are exact, so the SIGN of the result
+// is exact and the hull does not depend on the order in which triples are tested.
 __device__ __forceinline__ double hull_cross(double ox, double oy, double ax, double ay, double bx, double by) {
   return (ax - ox) * (by - oy) - (ay - oy) * (bx - ox);
+}
+__device__ __forceinline__ double key_x(unsigned long long v) { return (double)ord2f((unsigned)(v >> 32)); }
+__device__ __forceinline__ double key_y(unsigned long long v) { return (double)ord2f((unsigned)v); }
+__device__ __forceinline__ bool hull_pops(unsigned long long o, unsigned long long a, unsigned long long b) {
+  return hull_cross(key_x(o), key_y(o), key_x(a), key_y(a), key_x(b), key_y(b)) <= 0.0;
+}
+
+// Ordered compaction of src[0, n) entries with keep(i) into dst; returns the count (all threads).
+template <typename Keep>
+__device__ __forceinline__ int cta_compact(const unsigned long long* src, int n, unsigned long long* dst, int* s_w, Keep keep) {
+  int written = 0;
+  for (int c0 = 0; c0 < n; c0 += kPackBlock) {
+    const int i = c0 + threadIdx.x;
+    const bool k = i < n && keep(i);
+    const unsigned long long v = k ? src[i] : 0ull;
+    int total;
+    const int off = block_scan_excl<kPackBlock>(k ? 1 : 0, &total, s_w);  // barriers inside: src read before dst written
+    if (k) dst[written + off] = v;
+    written += total;
+  }
+  __syncthreads();
+  return written;
+}
+
+// Andrew's monotone chain over sorted unique points pts[0, m) -> hull (counter-clockwise, collinear
+// points dropped) in out[]; returns the vertex count.  One thread.
+__device__ int hull_chain(const unsigned long long* pts, int m, unsigned long long* out) {
+  int k = 0;
+  if (m < 3) {
+    for (int i = 0; i < m; ++i) out[k++] = pts[i];
+    return k;
+  }
+  for (int i = 0; i < m; ++i) {
+    while (k >= 2 && hull_pops(out[k - 2], out[k - 1], pts[i])) --k;
+    out[k++] = pts[i];
+  }
+  for (int i = m - 2, t0 = k + 1; i >= 0; --i) {
+    while (k >= t0 && hull_pops(out[k - 2], out[k - 1], pts[i])) --k;
+    out[k++] = pts[i];
+  }
+  return k - 1;  // the start point is repeated at the end
 }
 
 // One CTA per frame.
 __global__ void __launch_bounds__(kPackBlock) pack_region_kernel(PackArgs a) {
-  __shared__ unsigned long long s_keys[kPackSortSmem];
+  extern __shared__ __align__(16) unsigned long long s_keys[];  // 2 * kPackSortSmem words (dynamic)
   __shared__ int s_count;
   __shared__ int s_w[kPackBlock / 32 + 1];
   __shared__ double s_red[kPackBlock / 32][3];
@@ -192,7 +237,7 @@ __global__ void __launch_bounds__(kPackBlock) pack_region_kernel(PackArgs a) {
   const float* xyz = a.xyz + (size_t)f * a.N * 3;
   int* scratch = a.scratch + (size_t)f * a.scratch_stride;
   const int* posmap = scratch;
-  // sort / stack space behind the position map (8-byte aligned)
+  // sort space behind the position map (8-byte aligned) for boundaries longer than the shared buffers
   unsigned long long* gkeys = reinterpret_cast<unsigned long long*>(scratch + ((a.N + 1) & ~1));
   const size_t gcap = (a.scratch_stride - (size_t)((a.N + 1) & ~1)) / 2;  // 64-bit words available
   const int r0 = a.offsets[kPackOffPlanar * F1 + f];
@@ -206,117 +251,108 @@ __global__ void __launch_bounds__(kPackBlock) pack_region_kernel(PackArgs a) {
     const PlanarMeta m = meta[r];
     const int nb = m.boundary_count;
     const int n2 = next_pow2(max(nb, 1));
-    unsigned long long* keys = s_keys;
-    // the sort buffer also holds the hull stack behind the keys: 2 * n2 words
-    bool fits = 2 * n2 <= kPackSortSmem;
-    if (!fits) {
+    unsigned long long* keys = s_keys;                 // two buffers of n2 words each
+    unsigned long long* keys2 = s_keys + kPackSortSmem;
+    bool ok = true;
+    unsigned long long* hull_spill = gkeys;             // chain output when it may not fit in a sort buffer
+    if (n2 > kPackSortSmem) {
       keys = gkeys;
-      if ((size_t)2 * n2 > gcap) {  // boundary longer than the scratch can sort: report, skip the side outputs
-        if (t == 0) atomicOr(a.err, kErrBoundaryCap);
-        if (t == 0) {
-          pcseg_planar_record rec;
-          rec.frame = f; rec.label_id = m.label_id; rec.seed_index = m.seed_index;
-          rec.inlier_begin = i0 + m.inlier_begin; rec.inlier_count = m.inlier_count;
-          rec.boundary_begin = b0 + m.boundary_begin; rec.boundary_count = nb;
-          rec.discontinuous_begin = b0 + m.boundary_begin; rec.discontinuous_count = 0;
-          rec.hull_begin = b0 + m.boundary_begin; rec.hull_count = 0;
-          for (int k = 0; k < 4; ++k) rec.plane[k] = m.plane[k];
-          for (int k = 0; k < 3; ++k) rec.centroid[k] = m.centroid[k];
-          rec.area = m.area;
-          for (int k = 0; k < 10; ++k) rec.estimator[k] = m.est[k];
-          a.planar[r0 + r] = rec;
-        }
-        continue;
-      }
+      keys2 = gkeys + n2;
+      hull_spill = gkeys + 2 * (size_t)n2;
+      ok = (size_t)4 * n2 <= gcap;  // else: boundary longer than the scratch can sort
     }
-    // ---- discontinuous boundary set -> positions in the inlier list, ascending, unique
-    // (the reference walks the inlier list and tests set membership, ps/detected_objects.cc:39-46)
-    for (int i = t; i < n2; i += kPackBlock) {
-      unsigned long long key = ~0ull;
-      if (i < nb && bfl[m.boundary_begin + i]) key = (unsigned long long)(unsigned)(posmap[bnd[m.boundary_begin + i]] - m.inlier_begin);
-      keys[i] = key;
-    }
-    __syncthreads();
-    cta_bitonic_sort(keys, n2);
-    if (t == 0) s_count = 0;
-    __syncthreads();
-    // ordered unique compaction: few entries, chunks of kPackBlock with a ballot-free serial carry
-    {
-      int written = 0;
-      for (int c0 = 0; c0 < n2; c0 += kPackBlock) {
-        const int i = c0 + t;
-        const unsigned long long k = (i < n2) ? keys[i] : ~0ull;
-        const bool keep = k != ~0ull && (i == 0 || keys[i - 1] != k);
-        int total;
-        const int off = block_scan_excl<kPackBlock>(keep ? 1 : 0, &total, s_w);
-        if (keep) {
-          const int pos = (int)k;
-          const int o = b0 + m.boundary_begin + written + off;
-          a.disc_pos[o] = pos;
-          a.disc_idx[o] = a.inl_planar[(size_t)f * a.N + m.inlier_begin + pos];
-        }
-        written += total;
-        if (keys[min(c0 + kPackBlock, n2) - 1] == ~0ull) break;  // sorted: only padding follows (uniform)
-      }
-      if (t == 0) s_count = written;
-    }
-    __syncthreads();
-    const int n_disc = s_count;
-    // ---- PlanarConvexHull output, ps/algorithms.h:526-549 (patch P1)
-    int n_hull = 0;
-    if (a.hull) {
-      float plane[4] = {m.plane[0], m.plane[1], m.plane[2], m.plane[3]};
-      const PlaneFrame pf = make_plane_frame(plane);
-      for (int i = t; i < n2; i += kPackBlock) {
-        unsigned long long key = ~0ull;
-        if (i < nb) {
-          double x, y;
-          plane_xy(pf, ld3(xyz, bnd[m.boundary_begin + i]), &x, &y);
-          const float fx = (float)x + 0.0f, fy = (float)y + 0.0f;  // plane_xy widens floats; -0 -> +0
-          key = ((unsigned long long)f2ord(fx) << 32) | f2ord(fy);
-        }
-        keys[i] = key;
+    int n_disc = 0, n_hull = 0;
+    if (!ok) {
+      if (t == 0) atomicOr(a.err, kErrBoundaryCap);
+    } else {
+      // ---- discontinuous boundary set -> positions in the inlier list, ascending, unique
+      // (the reference walks the inlier list and tests set membership, ps/detected_objects.cc:39-46)
+      if (t == 0) s_count = 0;
+      __syncthreads();
+      for (int i = t; i < nb; i += kPackBlock)
+        if (bfl[m.boundary_begin + i])
+          keys[atomicAdd(&s_count, 1)] = (unsigned long long)(unsigned)(posmap[bnd[m.boundary_begin + i]] - m.inlier_begin);
+      __syncthreads();
+      const int nf = s_count;
+      const int nf2 = next_pow2(max(nf, 1));
+      for (int i = nf + t; i < nf2; i += kPackBlock) keys[i] = ~0ull;
+      __syncthreads();
+      cta_bitonic_sort(keys, nf2);
+      n_disc = cta_compact(keys, nf, keys2, s_w, [&](int i) { return i == 0 || keys[i - 1] != keys[i]; });
+      for (int i = t; i < n_disc; i += kPackBlock) {
+        const int pos = (int)keys2[i];
+        const int o = b0 + m.boundary_begin + i;
+        a.disc_pos[o] = pos;
+        a.disc_idx[o] = a.inl_planar[(size_t)f * a.N + m.inlier_begin + pos];
       }
       __syncthreads();
-      cta_bitonic_sort(keys, n2);
-      if (t == 0) {
-        // Andrew's monotone chain over the sorted unique points (collinear points dropped), by one
-        // thread: O(nb) dependent steps on data that sits in shared memory / L1.
-        unsigned long long* stack = keys + n2;
-        int mcount = 0;  // unique points, compacted in place at the front of keys
-        for (int i = 0; i < nb; ++i)
-          if (i == 0 || keys[i] != keys[i - 1]) keys[mcount++] = keys[i];
-        int k = 0;
-        auto px = [&](unsigned long long v) { return (double)ord2f((unsigned)(v >> 32)); };
-        auto py = [&](unsigned long long v) { return (double)ord2f((unsigned)v); };
-        if (mcount < 3) {
-          for (int i = 0; i < mcount; ++i) stack[k++] = keys[i];
-        } else {
-          for (int i = 0; i < mcount; ++i) {
-            const double x = px(keys[i]), y = py(keys[i]);
-            while (k >= 2 && hull_cross(px(stack[k - 2]), py(stack[k - 2]), px(stack[k - 1]), py(stack[k - 1]), x, y) <= 0.0) --k;
-            stack[k++] = keys[i];
+      // ---- PlanarConvexHull output, ps/algorithms.h:526-549 (patch P1)
+      if (a.hull) {
+        float plane[4] = {m.plane[0], m.plane[1], m.plane[2], m.plane[3]};
+        const PlaneFrame pf = make_plane_frame(plane);
+        for (int i = t; i < n2; i += kPackBlock) {
+          unsigned long long key = ~0ull;
+          if (i < nb) {
+            double x, y;
+            plane_xy(pf, ld3(xyz, bnd[m.boundary_begin + i]), &x, &y);
+            const float fx = (float)x + 0.0f, fy = (float)y + 0.0f;  // plane_xy widens floats; -0 -> +0
+            key = ((unsigned long long)f2ord(fx) << 32) | f2ord(fy);
           }
-          for (int i = mcount - 2, t0 = k + 1; i >= 0; --i) {
-            const double x = px(keys[i]), y = py(keys[i]);
-            while (k >= t0 && hull_cross(px(stack[k - 2]), py(stack[k - 2]), px(stack[k - 1]), py(stack[k - 1]), x, y) <= 0.0) --k;
-            stack[k++] = keys[i];
-          }
-          --k;  // the start point is repeated at the end
+          keys[i] = key;
         }
+        __syncthreads();
+        cta_bitonic_sort(keys, n2);
+        int mcount = cta_compact(keys, nb, keys2, s_w, [&](int i) { return i == 0 || keys[i - 1] != keys[i]; });
+        unsigned long long *cur = keys2, *oth = keys;
+        // Filter rounds: a vertex of the hull of the whole set is a vertex of the hull of every subset
+        // that contains it, so points that are not on the hull of their own run of <= kPackChunk
+        // consecutive (sorted) points are dropped, all runs in parallel, until one thread's chain is short.
+        while (mcount > 4 * kPackChunk) {
+          const int prev = mcount;
+          const int per = min(kPackChunk, max(4, (mcount + kPackBlock - 1) / kPackBlock));
+          int written = 0;
+          for (int tile0 = 0; tile0 < mcount; tile0 += per * kPackBlock) {
+            const int c0 = tile0 + t * per, c1 = min(c0 + per, mcount);
+            unsigned keepmask = 0u;
+            if (c0 < c1) {
+              unsigned long long h[2 * kPackChunk];
+              const int hk = hull_chain(cur + c0, c1 - c0, h);
+              // mark the chunk's points that are hull vertices (h is a subsequence of the chunk in
+              // ascending order for the lower part, descending for the upper part)
+              for (int q = 0; q < hk; ++q)
+                for (int i = c0; i < c1; ++i)
+                  if (cur[i] == h[q]) { keepmask |= 1u << (i - c0); break; }
+            }
+            int total;
+            const int off = block_scan_excl<kPackBlock>(__popc(keepmask), &total, s_w);
+            int o = written + off;
+            for (unsigned mm = keepmask; mm; mm &= mm - 1) oth[o++] = cur[c0 + __ffs(mm) - 1];
+            written += total;
+          }
+          __syncthreads();
+          unsigned long long* tmp = cur; cur = oth; oth = tmp;
+          mcount = written;
+          if (mcount >= prev) break;  // every point is a vertex of its run: nothing more to drop
+        }
+        // the chain's stack holds at most 2 * mcount entries
+        unsigned long long* hull_out = oth;
+        if (2 * mcount > kPackSortSmem && n2 <= kPackSortSmem) hull_out = hull_spill;
+        if (n2 > kPackSortSmem) hull_out = hull_spill;
+        if (n2 <= kPackSortSmem && hull_out == hull_spill && (size_t)2 * mcount > gcap) mcount = 0;  // cannot happen for N >= 8
+        if (t == 0) s_count = hull_chain(cur, mcount, hull_out);
+        __syncthreads();
+        n_hull = s_count;
+        oth = hull_out;
         // back to the cloud frame: world_pose_plane * (x, y, 0)
         const V3 n{plane[0], plane[1], plane[2]};
         const V3 tr = vscale(-plane[3], n);
         float* out = a.hull + 3 * (size_t)(b0 + m.boundary_begin);
-        for (int i = 0; i < k; ++i) {
-          const V3 pp{ord2f((unsigned)(stack[i] >> 32)), ord2f((unsigned)stack[i]), 0.0f};
+        for (int i = t; i < n_hull; i += kPackBlock) {
+          const V3 pp{ord2f((unsigned)(oth[i] >> 32)), ord2f((unsigned)oth[i]), 0.0f};
           const V3 w = vadd(qrotate(pf.qx, pf.qy, pf.qz, pf.qw, pp), tr);
           out[3 * i] = w.x; out[3 * i + 1] = w.y; out[3 * i + 2] = w.z;
         }
-        s_count = k;
       }
-      __syncthreads();
-      n_hull = s_count;
     }
     if (t == 0) {
       pcseg_planar_record rec;

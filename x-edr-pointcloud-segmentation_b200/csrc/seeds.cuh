@@ -1,4 +1,5 @@
-// seeds.cuh -- FindSeedPointsFromPlaneSupport on the GPU.
+// seeds.cuh -- the three seed finders on the GPU: FindSeedPointsFromPlaneSupport (below),
+// FindSeedPointsFromAverageNormals and FindSeedPointsFromLastPlanarRegions (end of file).
 //
 // Replaces ps/segmentation.h:190-230 with detail::GetNumPlaneSupportPoints
 // (:54-73).  Quirk Q1 is reproduced literally: the reference passes (col,row)
@@ -130,6 +131,136 @@ __global__ void __launch_bounds__(32 * kSeedWarps) seed_order_kernel(SeedArgs a,
       out[basepos + rank] = i;  // seed index = col * Rows + row = linear cell index
     }
     __syncwarp();
+  }
+}
+
+
+// ---------------------------------------------------------------------------
+// FindSeedPointsFromAverageNormals, ps/segmentation.h:137-184 with
+// detail::GetSquaredAverageNormalLengthAndUpdateSlidingWindow (:79-120).
+// Quirk Q1 literally: normals.AtUnsafe(col - n, row + i - k) reads
+// data[(row + i - k) * Rows + (col - n)], the seed index is
+// LinearizeIndex(row, col) - k = col * Rows + row - k.
+// The sliding row sums are order-sensitive fp32 (subtract the leaving normal,
+// add the entering one, column after column), so one thread walks one `row` of
+// the reference's outer loop through all columns with its n running sums; rows
+// are independent.  Flags go to a (row, col)-ordered byte grid; the seeds are
+// emitted in the reference's loop order (row outer, col inner) by an ordered
+// compaction.
+// ---------------------------------------------------------------------------
+constexpr int kAvgMaxNbhd = 32;
+
+struct AvgSeedArgs {
+  const float* normals;  // [F][N][3]
+  int rows, cols;
+  int nbhd, half, min_valid;
+  float sq_min_len;      // min_avg_normal_length^2
+  unsigned char* flags;  // [F][flag_stride]: (row - half) * cols + col
+  size_t flag_stride;
+  int* seeds;            // [F][stride]
+  int stride;
+  int* n_seeds;          // [F]
+};
+
+__global__ void __launch_bounds__(64) seed_avg_normals_flag_kernel(AvgSeedArgs a) {
+  const int f = blockIdx.y;
+  const int rr = blockIdx.x * blockDim.x + threadIdx.x;  // row - half
+  const int rows = a.rows, cols = a.cols, n = a.nbhd, half = a.half;
+  const int row = rr + half;
+  if (row >= rows - half) return;
+  const float* nrm = a.normals + (size_t)f * rows * cols * 3;
+  unsigned char* flags = a.flags + (size_t)f * a.flag_stride + (size_t)rr * cols;
+  V3 avg_row[kAvgMaxNbhd];
+  int nvalid_row[kAvgMaxNbhd];
+  for (int i = 0; i < n; ++i) { avg_row[i] = V3{0.0f, 0.0f, 0.0f}; nvalid_row[i] = 0; }
+  for (int col = 0; col < cols; ++col) {
+    V3 avg{0.0f, 0.0f, 0.0f};
+    int num_valid = 0;
+    for (int i = 0; i < n; ++i) {
+      const int q = (row + i - half) * rows;  // Q1: AtUnsafe(col', row + i - k) -> data[(row+i-k)*Rows + col']
+      if (col >= n) {
+        const V3 leaving = ld3(nrm, q + col - n);
+        if (vfinite(leaving)) { avg_row[i] = vsub(avg_row[i], leaving); --nvalid_row[i]; }
+      }
+      const V3 entering = ld3(nrm, q + col);
+      if (vfinite(entering)) { avg_row[i] = vadd(avg_row[i], entering); ++nvalid_row[i]; }
+      const int new_num = num_valid + nvalid_row[i];
+      // (int * Vector3f + int * Vector3f) / int, the ints converted to float (:113-115)
+      const float wa = (float)num_valid, wb = (float)nvalid_row[i];
+      avg = vdiv(vadd(vscale(wa, avg), vscale(wb, avg_row[i])), (float)new_num);
+      num_valid = new_num;
+    }
+    const float sq = vsqn(avg);
+    flags[col] = (col >= n - 1 && num_valid >= a.min_valid && sq >= a.sq_min_len) ? 1 : 0;
+  }
+}
+
+// One CTA per frame: seeds in (row outer, col inner) order.
+__global__ void __launch_bounds__(1024) seed_avg_normals_order_kernel(AvgSeedArgs a) {
+  __shared__ int s_w[33];
+  const int f = blockIdx.x;
+  const int rows = a.rows, cols = a.cols, half = a.half;
+  const int total = (rows - 2 * half) * cols;
+  const unsigned char* flags = a.flags + (size_t)f * a.flag_stride;
+  int* out = a.seeds + (size_t)f * a.stride;
+  int written = 0;
+  for (int c0 = 0; c0 < total; c0 += 1024) {
+    const int k = c0 + threadIdx.x;
+    const bool keep = k < total && flags[k] != 0;
+    int tot;
+    const int off = block_scan_excl<1024>(keep ? 1 : 0, &tot, s_w);
+    if (keep) {
+      const int row = k / cols + half, col = k % cols;
+      out[written + off] = col * rows + row - half;  // LinearizeIndex(row, col) - kHalfNeighborhoodSize
+    }
+    written += tot;
+  }
+  if (threadIdx.x == 0) a.n_seeds[f] = written;
+}
+
+// ---------------------------------------------------------------------------
+// FindSeedPointsFromLastPlanarRegions, ps/planar_region.h:478-519: per previous
+// region (already in multimap order) the nearest current point whose normal
+// agrees with the transformed region normal; strict "<" keeps the first
+// minimum in index order, so the reduction key is (distance, index).  One CTA
+// per previous region; the transformed seed point / normal
+// (current_pose_prev * centroid, quaternion * normal) are computed on the device.
+// ---------------------------------------------------------------------------
+struct LastSeedArgs {
+  const float* xyz;       // [n_points][3]
+  const float* normals;   // [n_points][3]
+  int n_points;
+  const float* centroids; // [n_prev][3]
+  const float* pnormals;  // [n_prev][3]
+  float qx, qy, qz, qw, tx, ty, tz;
+  float max_sq, cos_max;
+  int* out;               // [n_prev]: index or -1
+};
+
+__global__ void __launch_bounds__(512) seed_last_regions_kernel(LastSeedArgs a) {
+  __shared__ unsigned long long s_best[16];
+  const int r = blockIdx.x;
+  const V3 sp = vadd(qrotate(a.qx, a.qy, a.qz, a.qw, ld3(a.centroids, r)), V3{a.tx, a.ty, a.tz});
+  const V3 sn = qrotate(a.qx, a.qy, a.qz, a.qw, ld3(a.pnormals, r));
+  // squared distances are >= 0, so their bit patterns order like the values; key = (bits, index)
+  unsigned long long best = ~0ull;
+  for (int j = threadIdx.x; j < a.n_points; j += blockDim.x) {
+    const float sq = vsqn(vsub(sp, ld3(a.xyz, j)));
+    if (sq < a.max_sq && vdot(sn, ld3(a.normals, j)) > a.cos_max) {
+      const unsigned long long key = ((unsigned long long)__float_as_uint(sq + 0.0f) << 32) | (unsigned)j;
+      best = key < best ? key : best;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long v = __shfl_xor_sync(0xffffffffu, best, o);
+    best = v < best ? v : best;
+  }
+  if ((threadIdx.x & 31) == 0) s_best[threadIdx.x >> 5] = best;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 16; ++w) best = s_best[w] < best ? s_best[w] : best;
+    a.out[r] = best == ~0ull ? -1 : (int)(unsigned)best;
   }
 }
 

@@ -104,7 +104,8 @@ pcseg_default_cluster_config pcseg_create pcseg_destroy pcseg_status_string
 pcseg_last_error pcseg_launch_count pcseg_stream pcseg_prepare_unlabeled_labels
 pcseg_normals_organized pcseg_segment_planar pcseg_segment_cluster
 pcseg_mean_shift_modes pcseg_mean_shift_modes_range pcseg_mean_shift_from_modes
-pcseg_mean_shift pcseg_seeds_plane_support
+pcseg_mean_shift pcseg_seeds_plane_support pcseg_seeds_average_normals pcseg_seeds_last_planar_regions
+pcseg_fit_planes pcseg_plane_estimator_replay pcseg_plane_estimators_transform pcseg_plane_estimators_merge
 pcseg_batch_submit_regions pcseg_transform_in_place pcseg_gather_points
 pcseg_batch_create pcseg_batch_destroy pcseg_batch_run pcseg_batch_submit pcseg_batch_wait pcseg_batch_stream pcseg_batch_frame_stats
 pcseg_batch_regions pcseg_batch_stage_times pcseg_batch_profile pcseg_batch_device_labels pcseg_batch_device_normals
@@ -369,6 +370,83 @@ class Context:
             C.c_float(max_plane_distance), min_support, _addr(out), out.size, C.byref(n)))
         return out[:n.value].copy()
 
+    def seeds_average_normals(self, xyz, normals, rows, cols, neighborhood_size=5,
+                              min_num_valid_normals=8, min_avg_normal_length=0.9999):
+        """FindSeedPointsFromAverageNormals (ps/segmentation.h:137-184)."""
+        xyz = _f32(xyz).reshape(-1)
+        normals = _f32(normals).reshape(-1)
+        out = np.zeros(rows * cols, np.int32)
+        n = C.c_int(0)
+        self._check(self.L.pcseg_seeds_average_normals(
+            self.h, _addr(xyz), _addr(normals), rows, cols, neighborhood_size, min_num_valid_normals,
+            C.c_float(min_avg_normal_length), _addr(out), out.size, C.byref(n)))
+        return out[:n.value].copy()
+
+    def seeds_last_planar_regions(self, xyz, normals, prev_inlier_counts, prev_centroids, prev_normals,
+                                  q_xyzw=(0, 0, 0, 1), translation=(0, 0, 0), max_distance=0.5,
+                                  max_normal_difference_angle=0.2, seeds=None):
+        """FindSeedPointsFromLastPlanarRegions (ps/planar_region.h:478-519); appends to `seeds`."""
+        xyz = _f32(xyz).reshape(-1)
+        normals = _f32(normals).reshape(-1)
+        cnt = _i32(prev_inlier_counts)
+        cen = _f32(prev_centroids).reshape(-1)
+        nrm = _f32(prev_normals).reshape(-1)
+        have = _i32(seeds if seeds is not None else [])
+        out = np.zeros(have.size + max(cnt.size, 1), np.int32)
+        out[:have.size] = have
+        n = C.c_int(have.size)
+        q = (C.c_float * 4)(*[float(v) for v in q_xyzw])
+        t = (C.c_float * 3)(*[float(v) for v in translation])
+        self._check(self.L.pcseg_seeds_last_planar_regions(
+            self.h, _addr(xyz), _addr(normals), xyz.size // 3, cnt.size, _addr(cnt), _addr(cen), _addr(nrm), q, t,
+            C.c_float(max_distance), C.c_float(max_normal_difference_angle), _addr(out), out.size, C.byref(n)))
+        return out[:n.value].copy()
+
+    # ---- PlaneEstimator (ps/plane_estimator.h:37-120) ----
+    def fit_planes(self, xyz, offsets, indices, weights=None, hints=None, want_state=False):
+        """Plane fits over CSR index sets; returns query rows [n, 10] (and states [n, 10])."""
+        xyz = _f32(xyz).reshape(-1)
+        offsets = _i32(offsets)
+        indices = _i32(indices)
+        n = offsets.size - 1
+        w = _f32(weights) if weights is not None else None
+        h = _f32(hints).reshape(-1) if hints is not None else None
+        q = np.zeros((max(n, 0), 10), np.float32)
+        st = np.zeros((max(n, 0), 10), np.float32) if want_state else None
+        self._check(self.L.pcseg_fit_planes(
+            self.h, _addr(xyz), xyz.size // 3, _addr(offsets), _addr(indices) if indices.size else None, n,
+            _addr(w) if w is not None else None, _addr(h) if h is not None else None, _addr(q),
+            _addr(st) if want_state else None))
+        return (q, st) if want_state else q
+
+    def plane_estimator_replay(self, ops, poses=()):
+        """Same op list as oracle.plane_estimator_replay2; returns query rows [n_queries, 10]."""
+        codes = _i32([o[0] for o in ops])
+        args = _f32([[o[1], o[2], o[3], o[4]] for o in ops]).reshape(-1)
+        pz = np.ascontiguousarray(np.asarray(poses, np.float64).reshape(-1))
+        cap = max(1, sum(1 for o in ops if o[0] == 3))
+        out = np.zeros((cap, 10), np.float32)
+        n = C.c_int(0)
+        self._check(self.L.pcseg_plane_estimator_replay(
+            self.h, _addr(codes), _addr(args), len(ops), _addr(pz) if pz.size else None, pz.size // 7, _addr(out),
+            cap, C.byref(n)))
+        return out[:n.value].copy()
+
+    def plane_estimators_transform(self, states, poses):
+        """Transform of [n, 10] accumulator states (returns a copy); poses [n, 7] or one (7,)."""
+        s = _f32(states).reshape(-1, 10).copy()
+        pz = np.ascontiguousarray(np.asarray(poses, np.float64).reshape(-1))
+        self._check(self.L.pcseg_plane_estimators_transform(self.h, _addr(s), s.shape[0], _addr(pz), int(pz.size > 7)))
+        return s
+
+    def plane_estimators_merge(self, dst, src, poses=None):
+        d = _f32(dst).reshape(-1, 10).copy()
+        s = _f32(src).reshape(-1, 10)
+        pz = np.ascontiguousarray(np.asarray(poses, np.float64).reshape(-1)) if poses is not None else None
+        self._check(self.L.pcseg_plane_estimators_merge(
+            self.h, _addr(d), _addr(s), d.shape[0], _addr(pz) if pz is not None else None,
+            int(pz is not None and pz.size > 7)))
+        return d
 
     def transform_in_place(self, points=None, normals=None, q_xyzw=(0, 0, 0, 1), translation=(0, 0, 0)):
         """MultichannelCloud::TransformInPlace (ps/multichannel_cloud.cc:53-68); arrays are modified in place."""
@@ -476,8 +554,24 @@ class BatchResults:
     by boundary_cap (default n_frames * 8192)."""
 
     def __init__(self, n_frames, n_points, inlier_xyz=False, boundary_xyz=False, hull=True, cluster_stats=True,
-                 boundary_cap=None, region_cap=None, alloc=None):
-        alloc = alloc or (lambda shape, dtype: np.zeros(shape, dtype))
+                 boundary_cap=None, region_cap=None, alloc=None, share=None):
+        base = alloc or (lambda shape, dtype: np.zeros(shape, dtype))
+        names = iter(("frame_stats", "frame_offsets", "planar", "planar_inlier_indices", "planar_inlier_xyz",
+                      "boundary_indices", "boundary_xyz", "boundary_discontinuous", "discontinuous_indices",
+                      "discontinuous_positions", "hull_points", "cluster", "cluster_inlier_indices",
+                      "cluster_inlier_xyz"))
+        skipped = {"planar_inlier_xyz": not inlier_xyz, "boundary_xyz": not boundary_xyz, "hull_points": not hull,
+                   "cluster_inlier_xyz": not inlier_xyz}
+
+        def alloc(shape, dtype):
+            """Arrays are requested in the order of `names`; one that `share` (another BatchResults of
+            the same geometry) already holds is reused instead of allocated."""
+            name = next(names)
+            while skipped.get(name):
+                name = next(names)
+            have = getattr(share, name, None) if share is not None else None
+            return have if have is not None else base(shape, dtype)
+
         F, N = n_frames, n_points
         bc = boundary_cap or F * 8192
         rc = region_cap or F * 256
