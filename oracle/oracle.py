@@ -295,6 +295,15 @@ def seeds_last_planar_regions(xyz, normals, prev_inlier_counts, prev_centroids, 
     return out[:n].copy()
 
 
+def sort_order(intensities, sort_mode=0):
+    """Permutation of the reference's std::sort by intensity (ps/mean_shift_segmentation.h:276-280)."""
+    L = port_lib()
+    v = np.ascontiguousarray(intensities, np.float64)
+    out = np.zeros(v.size, np.int32)
+    L.oracle_sort_order(v.ctypes.data_as(C.POINTER(C.c_double)), v.size, int(sort_mode), _ptr(out, I32P))
+    return out
+
+
 def eig3(a6):
     L = lib()
     a = _f32(a6)

@@ -1433,6 +1433,18 @@ int oracle_seeds_average_normals(const float* xyz, const float* normals,
   return k;
 }
 
+// The sort of ps/mean_shift_segmentation.h:276-280 alone: order_out[k] = position (in the input
+// list) of the element that std::sort (mode 0; this box's libstdc++, quirk Q7) or std::stable_sort
+// (mode 1, patch P2) puts at place k when the list is compared by intensity only.
+void oracle_sort_order(const double* intensities, int n, int sort_mode, int* order_out) {
+  std::vector<std::pair<int, double>> v(n);
+  for (int i = 0; i < n; ++i) v[i] = std::make_pair(i, intensities[i]);
+  auto cmp = [](const std::pair<int, double>& l, const std::pair<int, double>& r) { return l.second < r.second; };
+  if (sort_mode == 1) std::stable_sort(v.begin(), v.end(), cmp);
+  else std::sort(v.begin(), v.end(), cmp);
+  for (int i = 0; i < n; ++i) order_out[i] = v[i].first;
+}
+
 // FindSeedPointsFromLastPlanarRegions, ps/planar_region.h:478-519.  prev_* describe the previous
 // regions (inlier_indices().size(), centroid(), plane().normal()); the multimap orders them by
 // inlier count, insertion order within a count.  Returns the number of seeds appended.

@@ -130,6 +130,10 @@ int oracle_seeds_average_normals(const float* xyz, const float* normals,
                                  float min_avg_normal_length, int* seeds_out,
                                  int cap);
 
+/* The std::sort call of ps/mean_shift_segmentation.h:276-280 on its own (port library only):
+ * order_out[k] = input position of the element sorted to place k; sort_mode as above. */
+void oracle_sort_order(const double* intensities, int n, int sort_mode, int* order_out);
+
 /* ps/planar_region.h:478-519 FindSeedPointsFromLastPlanarRegions; previous regions given by
  * inlier count, centroid and plane normal; pose = current_pose_prev (Pose3f).  seeds_out has room
  * for n_prev entries; returns the number appended. */

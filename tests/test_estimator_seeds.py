@@ -221,7 +221,12 @@ def test_cuda_fit_planes_csr(ctx, weighted):
     q, st = ctx.fit_planes(xyz, offsets, indices, weights=w, hints=hints, want_state=True)
     with checker():
         want = oracle.fit_planes_csr(xyz, offsets, indices, hints=hints, weights=w)
-    assert np.array_equal(bits(q), bits(want))
+    nonempty = np.diff(offsets) > 0
+    assert np.array_equal(bits(q[nonempty]), bits(want[nonempty]))
+    # an empty region is the state right after Clear() + SetNormalOrientation: invalid, plane = (hint, 0);
+    # the reference's Centroid()/Curvature() return uninitialised members there, so only these are compared
+    assert np.all(q[~nonempty][:, 0] == 0) and np.array_equal(bits(q[~nonempty][:, 5:8]), bits(hints[~nonempty]))
+    assert np.all(q[~nonempty][:, 8:] == 0)
     assert np.array_equal(bits(st[:, 9]), bits(want[:, 9]))
     # Transform / Merge of the exported states against the class replayed op by op
     rng = np.random.default_rng(5)

@@ -33,8 +33,13 @@ def check_regions(r, f, prefix, kind):
     for k in ("inlier_offsets", "inlier_indices", "label_ids"):
         assert np.array_equal(getattr(r, k), f[prefix + k]), k
     if kind == "planar":
-        for k in ("seed_indices", "boundary_offsets", "boundary_indices", "disc_offsets", "disc_indices", "hull_offsets"):
+        for k in ("seed_indices", "boundary_offsets", "boundary_indices", "disc_offsets", "hull_offsets"):
             assert np.array_equal(getattr(r, k), f[prefix + k]), k
+        # the discontinuity output is a set (absl::flat_hash_set, ps/planar_region.h:462): the fixture lists it
+        # by cloud index, the CUDA path in inlier order (what CreatePlanarDetectedObjectProto walks)
+        for i in range(r.n):
+            a, b = r.disc_offsets[i], r.disc_offsets[i + 1]
+            assert np.array_equal(np.sort(r.disc_indices[a:b]), np.sort(f[prefix + "disc_indices"][a:b])), "disc_indices"
         for k in ("planes", "centroids", "areas", "estimators", "hull_points"):
             assert close(getattr(r, k), f[prefix + k]), k
 

@@ -544,6 +544,11 @@ int get_scratch(pcseg_ctx* c, int rows, int cols, pcseg_batch** out) {
   if (!c->scratch) {
     int st = pcseg_batch_create(c, 1, rows, cols, &c->scratch);
     if (st) return st;
+    // the single-frame entry points issue their copies on the context's stream: the cached
+    // workspace must launch there too (S / SIn / SOut fall back to the context's streams)
+    pcseg_batch* b = c->scratch;
+    for (cudaStream_t* s : {&b->own_stream, &b->own_copy_in, &b->own_copy_out})
+      if (*s) { cudaStreamSynchronize(*s); cudaStreamDestroy(*s); *s = nullptr; }
   }
   *out = c->scratch;
   return PCSEG_OK;

@@ -30,13 +30,17 @@ constexpr int kSeedMaxKeys = 1024;
 
 __global__ void __launch_bounds__(256) seed_support_count_kernel(SeedArgs a) {
   const int N = a.rows * a.cols;
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= N) return;
+  const int tt = blockIdx.x * blockDim.x + threadIdx.x;
+  if (tt >= N) return;
   const int f = blockIdx.y;
   const float* xyz = a.xyz + (size_t)f * N * 3;
   const float* nrm = a.normals + (size_t)f * N * 3;
   const int rows = a.rows, cols = a.cols;
-  const int row = t % rows, col = t / rows;   // loop variables of the reference
+  // loop variables of the reference; a warp takes 32 consecutive `col` of one `row`: the elements
+  // the reference actually reads (quirk Q1: data[support_row * Rows + support_col]) are then
+  // consecutive in memory across the warp
+  const int row = tt / cols, col = tt % cols;
+  const int t = col * rows + row;
   int result = -1;
   if (rows >= a.nbhd && cols >= a.nbhd) {     // :202-204
     const int ti = row * rows + col;          // AtUnsafe(col, row) -> data[row*Rows + col]
