@@ -138,9 +138,17 @@ int pcseg_mean_shift_from_modes(pcseg_ctx*, const float* xyz, int rows, int cols
                                 int initial_region_id_offset, int sort_mode,
                                 int* labels, pcseg_regions** out);
 
+/* The sort of ps/mean_shift_segmentation.h:262-280 on its own: intensities[i] >= 0 marks element i
+ * as a valid seed (window counts: integers <= 255); order_out receives the positions of the valid
+ * seeds in sorted order, *n_out their number.  sort_mode 0 = the permutation of the reference's
+ * std::sort call for libstdc++ (introsort replayed on the device); 1 = stable.
+ * PCSEG_ERR_UNSUPPORTED if std::sort would enter its heapsort fall-back (depth limit 2*log2 n). */
+int pcseg_mean_shift_sort_order(pcseg_ctx*, const float* intensities, int n, int sort_mode,
+                                int* order_out, int* n_out);
+
 /* Replaces ps/mean_shift_segmentation.h:207-330 SlidingMeanShift (iteration
  * phase + sort + growth).  sort_mode 0 = the reference's std::sort permutation
- * (libstdc++ introsort replayed on (intensity, seed order) keys), 1 = stable. */
+ * (libstdc++ introsort replayed on the device), 1 = stable.  Everything runs on the device. */
 int pcseg_mean_shift(pcseg_ctx*, const float* xyz, int rows, int cols,
                      const pcseg_cluster_config* cfg, int iterations,
                      int initial_region_id_offset, int sort_mode, int* labels,

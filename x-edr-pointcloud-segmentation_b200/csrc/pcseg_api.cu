@@ -21,6 +21,7 @@
 #include "seeds.cuh"
 #include "results_pack.cuh"
 #include "plane_estimator.cuh"
+#include "msort.cuh"
 
 using namespace pcseg;
 
@@ -1095,47 +1096,150 @@ int pcseg_mean_shift_modes(pcseg_ctx* c, const float* xyz, int rows, int cols, c
 }
 
 namespace {
+// Device-wide inclusive scan of n packed 64-bit counters (msort.cuh); tiles = scratch of ceil(n / kScanTile) words.
+int scan64(pcseg_ctx* c, const unsigned long long* v, int n, unsigned long long* out, DevBuf* tiles) {
+  if (n <= 0) return PCSEG_OK;
+  const int n_tiles = (n + kScanTile - 1) / kScanTile;
+  CU_TRY(c, tiles->ensure((size_t)n_tiles * sizeof(unsigned long long)));
+  scan64_reduce_kernel<<<n_tiles, kScanBlock, 0, c->stream>>>(v, n, tiles->as<unsigned long long>());
+  scan64_tiles_kernel<<<1, kScanBlock, 0, c->stream>>>(tiles->as<unsigned long long>(), n_tiles);
+  scan64_apply_kernel<<<n_tiles, kScanBlock, 0, c->stream>>>(v, n, tiles->as<unsigned long long>(), out);
+  c->launches += 3;
+  CU_TRY(c, cudaGetLastError());
+  return PCSEG_OK;
+}
+
+// The sort of ps/mean_shift_segmentation.h:262-280 on the device (msort.cuh): intensities of the n
+// cells (< 0: not a valid seed) -> cell ids of the valid seeds in the order the reference's
+// std::sort (sort_mode 0, libstdc++ introsort replayed level by level) or std::stable_sort
+// (sort_mode 1) leaves them.  *S_out = number of valid seeds.
+int ms_sort_device(pcseg_ctx* c, const float* d_intensity, int n, int sort_mode, DevBuf* d_cells, int* S_out) {
+  *S_out = 0;
+  if (n <= 0) return PCSEG_OK;
+  cudaStream_t st = c->stream;
+  DevBuf d_v, d_incl, d_tiles, d_key, d_idx, d_seg, d_posL, d_posR, d_segs[2], d_cnt, d_hist, d_hincl;
+  CU_TRY(c, d_v.ensure((size_t)n * 8));
+  CU_TRY(c, d_incl.ensure((size_t)n * 8));
+  CU_TRY(c, d_cnt.ensure(4 * sizeof(int)));  // [0] next segment count, [1] overflow / bad-key flags
+  CU_TRY(c, cudaMemsetAsync(d_cnt.p, 0, 4 * sizeof(int), st));
+  unsigned long long* v = d_v.as<unsigned long long>();
+  unsigned long long* incl = d_incl.as<unsigned long long>();
+  int* cnt = d_cnt.as<int>();
+  const int gb = (n + 255) / 256;
+  msort_valid_flag_kernel<<<gb, 256, 0, st>>>(d_intensity, n, v, cnt + 1);
+  ++c->launches;
+  int rc = scan64(c, v, n, incl, &d_tiles);
+  if (rc) return rc;
+  unsigned long long total = 0;
+  int h_cnt[4];
+  CU_TRY(c, cudaMemcpyAsync(&total, incl + (n - 1), 8, cudaMemcpyDeviceToHost, st));
+  CU_TRY(c, cudaMemcpyAsync(h_cnt, cnt, sizeof(h_cnt), cudaMemcpyDeviceToHost, st));
+  CU_TRY(c, cudaStreamSynchronize(st));
+  if (h_cnt[1]) {
+    c->last_error = "mean-shift intensities are not integers in [0, 255] (window counts expected)";
+    return PCSEG_ERR_UNSUPPORTED;
+  }
+  const int S = (int)total;
+  *S_out = S;
+  if (S == 0) return PCSEG_OK;
+  CU_TRY(c, d_key.ensure((size_t)S));
+  CU_TRY(c, d_idx.ensure((size_t)S * sizeof(int)));
+  CU_TRY(c, d_seg.ensure((size_t)S * sizeof(int)));
+  CU_TRY(c, d_cells->ensure((size_t)S * sizeof(int)));
+  unsigned char* key = d_key.as<unsigned char>();
+  int* idx = d_idx.as<int>();
+  int* seg = d_seg.as<int>();
+  msort_compact_kernel<<<gb, 256, 0, st>>>(d_intensity, n, incl, key, idx, seg);
+  ++c->launches;
+  if (sort_mode == 0 && S > kSortThreshold) {
+    // __introsort_loop, one level per iteration (stl_algo.h:1918-1936)
+    const int seg_cap = S / (kSortThreshold + 1) + 2;
+    CU_TRY(c, d_segs[0].ensure((size_t)seg_cap * sizeof(SortSeg)));
+    CU_TRY(c, d_segs[1].ensure((size_t)seg_cap * sizeof(SortSeg)));
+    CU_TRY(c, d_posL.ensure(((size_t)S + 1) * sizeof(int)));
+    CU_TRY(c, d_posR.ensure(((size_t)S + 1) * sizeof(int)));
+    SortSeg first{};
+    first.lo = 0; first.hi = S;
+    CU_TRY(c, cudaMemcpyAsync(d_segs[0].p, &first, sizeof(SortSeg), cudaMemcpyHostToDevice, st));
+    int depth_limit = 0;
+    while ((2 << depth_limit) <= S) ++depth_limit;  // std::__lg(n)
+    depth_limit *= 2;
+    int n_cur = 1, cur = 0;
+    const int sb = (S + 255) / 256;
+    for (int level = 0; n_cur > 0; ++level) {
+      if (level >= depth_limit) {
+        c->last_error = "std::sort would fall back to heapsort on this input (introsort depth limit): not replayed";
+        return PCSEG_ERR_UNSUPPORTED;
+      }
+      SortSeg* segs = d_segs[cur].as<SortSeg>();
+      SortSeg* next = d_segs[cur ^ 1].as<SortSeg>();
+      const int gs = (n_cur + 255) / 256;
+      msort_pivot_kernel<<<gs, 256, 0, st>>>(segs, n_cur, key, idx);
+      msort_flag_kernel<<<sb, 256, 0, st>>>(segs, seg, key, S, v);
+      c->launches += 2;
+      if ((rc = scan64(c, v, S, incl, &d_tiles))) return rc;
+      msort_pos_kernel<<<sb, 256, 0, st>>>(v, incl, S, d_posL.as<int>(), d_posR.as<int>());
+      CU_TRY(c, cudaMemsetAsync(cnt, 0, sizeof(int), st));
+      msort_cut_kernel<<<gs, 256, 0, st>>>(segs, n_cur, incl, d_posL.as<int>(), d_posR.as<int>(), next, cnt, seg_cap, cnt + 1);
+      msort_swap_kernel<<<sb, 256, 0, st>>>(segs, seg, v, incl, d_posR.as<int>(), S, key, idx);
+      c->launches += 3;
+      CU_TRY(c, cudaGetLastError());
+      CU_TRY(c, cudaMemcpyAsync(h_cnt, cnt, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+      CU_TRY(c, cudaStreamSynchronize(st));
+      if (h_cnt[1]) { c->last_error = "sort segment table overflow"; return PCSEG_ERR_CAPACITY; }
+      n_cur = h_cnt[0];
+      cur ^= 1;
+    }
+  }
+  // __final_insertion_sort == the stable sort of what the loop left (sort_mode 1: of the seed order)
+  const int n_chunks = (S + kCountChunk - 1) / kCountChunk;
+  const int hn = 256 * n_chunks;
+  CU_TRY(c, d_hist.ensure((size_t)hn * 8));
+  CU_TRY(c, d_hincl.ensure((size_t)hn * 8));
+  const int hb = (n_chunks + kCountWarps - 1) / kCountWarps;
+  msort_hist_kernel<<<hb, 32 * kCountWarps, 0, st>>>(key, S, n_chunks, d_hist.as<unsigned long long>());
+  ++c->launches;
+  if ((rc = scan64(c, d_hist.as<unsigned long long>(), hn, d_hincl.as<unsigned long long>(), &d_tiles))) return rc;
+  msort_scatter_kernel<<<hb, 32 * kCountWarps, 0, st>>>(key, idx, S, n_chunks, d_hist.as<unsigned long long>(),
+                                                        d_hincl.as<unsigned long long>(), d_cells->as<int>());
+  ++c->launches;
+  CU_TRY(c, cudaGetLastError());
+  CU_TRY(c, cudaStreamSynchronize(st));  // the temporaries die with this scope
+  return PCSEG_OK;
+}
+
 // Sort + growth phase on device-resident mode records (ps/mean_shift_segmentation.h:262-329).
 int mean_shift_finish(pcseg_ctx* c, const float* xyz_dev, int rows, int cols, const ModeRecord* modes_dev,
                       const pcseg_cluster_config* cfg, int id_offset, int sort_mode, int* labels_dev,
                       pcseg_regions** out) {
   const size_t N = (size_t)rows * cols;
   // (1) intensities of the valid seeds, in seed order (ascending cloud index, :219-229,267-274)
-  DevBuf d_int;
+  DevBuf d_int, d_cells;
   CU_TRY(c, d_int.ensure(N * sizeof(float)));
   ms_intensity_kernel<<<(unsigned)((N + 255) / 256), 256, 0, c->stream>>>(modes_dev, (int)N, d_int.as<float>());
   ++c->launches;
-  std::vector<float> h_int(N);
-  CU_TRY(c, cudaMemcpyAsync(h_int.data(), d_int.p, N * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
-  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  // (2) the reference's sort call, :276-280, replayed on the device (msort.cuh; quirk Q7).
+  // sort_mode 1 = stable (documented patch P2).
+  int S = 0;
+  {
+    const int rc = ms_sort_device(c, d_int.as<float>(), (int)N, sort_mode, &d_cells, &S);
+    if (rc) return rc;
+  }
   d_int.release();
-  // (2) the reference's own sort call on (intensity) keys, :276-280.  The permutation of an
-  // unstable sort depends only on the comparison outcomes, so sorting (cell, intensity) pairs
-  // with the same comparator reproduces the permutation of the reference's records (for the
-  // same standard library; quirk Q7).  sort_mode 1 = stable (documented patch P2).
-  std::vector<std::pair<int, double>> keys;
-  keys.reserve(N);
-  for (size_t i = 0; i < N; ++i)
-    if (h_int[i] >= 0.0f) keys.emplace_back((int)i, (double)h_int[i]);
-  auto cmp = [](const std::pair<int, double>& l, const std::pair<int, double>& r) { return l.second < r.second; };
-  if (sort_mode == 0) std::sort(keys.begin(), keys.end(), cmp);
-  else std::stable_sort(keys.begin(), keys.end(), cmp);
-  const int S = (int)keys.size();
   pcseg_regions* res = new pcseg_regions();
-  *out = res;
-  if (S == 0) return PCSEG_OK;
-  std::vector<int> h_cells(S);
-  for (int i = 0; i < S; ++i) h_cells[i] = keys[i].first;
+  if (S == 0) { *out = res; return PCSEG_OK; }
+  struct ResGuard {  // the result reaches the caller only on success (no live handle beside an error status)
+    pcseg_regions* r; pcseg_regions** out; bool ok = false;
+    ~ResGuard() { if (ok) *out = r; else delete r; }
+  } guard{res, out};
   // (3) growth on the device
   const int rcap = (int)std::min<size_t>(N / (size_t)std::max(cfg->min_region_inliers, 1) + 1, (size_t)1 << 22);
-  DevBuf d_cells, d_seeds, d_claim, d_inl, d_meta, d_out;
-  CU_TRY(c, d_cells.ensure((size_t)S * sizeof(int)));
+  DevBuf d_seeds, d_claim, d_inl, d_meta, d_out;
   CU_TRY(c, d_seeds.ensure((size_t)S * sizeof(MsSeedRec)));
   CU_TRY(c, d_claim.ensure(N * sizeof(int)));
   CU_TRY(c, d_inl.ensure(N * sizeof(int)));
   CU_TRY(c, d_meta.ensure((size_t)rcap * sizeof(MsRegionMeta)));
   CU_TRY(c, d_out.ensure(4 * sizeof(int)));
-  CU_TRY(c, cudaMemcpyAsync(d_cells.p, h_cells.data(), (size_t)S * sizeof(int), cudaMemcpyHostToDevice, c->stream));
   CU_TRY(c, cudaMemsetAsync(d_out.p, 0, 4 * sizeof(int), c->stream));
   ms_gather_kernel<<<(unsigned)((S + 255) / 256), 256, 0, c->stream>>>(modes_dev, d_cells.as<int>(), S, rows,
                                                                         d_seeds.as<MsSeedRec>());
@@ -1164,9 +1268,32 @@ int mean_shift_finish(pcseg_ctx* c, const float* xyz_dev, int rows, int cols, co
   }
   d_cells.release(); d_seeds.release(); d_claim.release(); d_inl.release(); d_meta.release(); d_out.release();
   if (h_out[1]) { c->last_error = "mean-shift region table overflow"; return PCSEG_ERR_CAPACITY; }
+  guard.ok = true;
   return PCSEG_OK;
 }
 }  // namespace
+
+int pcseg_mean_shift_sort_order(pcseg_ctx* c, const float* intensities, int n, int sort_mode, int* order_out,
+                                int* n_out) {
+  if (!c || !intensities || !order_out || !n_out) return PCSEG_ERR_NULL;
+  if (n < 0) return PCSEG_ERR_DIMS;
+  *n_out = 0;
+  if (n == 0) return PCSEG_OK;
+  cudaSetDevice(c->device);
+  DevBuf si, d_cells;
+  const void* int_dev;
+  int st = to_device(c, intensities, (size_t)n * sizeof(float), &si, &int_dev);
+  if (st) return st;
+  int S = 0;
+  if ((st = ms_sort_device(c, (const float*)int_dev, n, sort_mode, &d_cells, &S))) return st;
+  *n_out = S;
+  if (S > 0) {
+    cudaMemcpyKind k = is_device_ptr(order_out) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+    CU_TRY(c, cudaMemcpyAsync(order_out, d_cells.p, (size_t)S * sizeof(int), k, c->stream));
+    CU_TRY(c, cudaStreamSynchronize(c->stream));
+  }
+  return PCSEG_OK;
+}
 
 int pcseg_mean_shift_from_modes(pcseg_ctx* c, const float* xyz, int rows, int cols, const float* modes,
                                 const pcseg_cluster_config* cfg, int id_offset, int sort_mode, int* labels,

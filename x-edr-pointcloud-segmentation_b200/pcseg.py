@@ -104,7 +104,7 @@ pcseg_default_cluster_config pcseg_create pcseg_destroy pcseg_status_string
 pcseg_last_error pcseg_launch_count pcseg_stream pcseg_prepare_unlabeled_labels
 pcseg_normals_organized pcseg_segment_planar pcseg_segment_cluster
 pcseg_mean_shift_modes pcseg_mean_shift_modes_range pcseg_mean_shift_from_modes
-pcseg_mean_shift pcseg_seeds_plane_support pcseg_seeds_average_normals pcseg_seeds_last_planar_regions
+pcseg_mean_shift pcseg_mean_shift_sort_order pcseg_seeds_plane_support pcseg_seeds_average_normals pcseg_seeds_last_planar_regions
 pcseg_fit_planes pcseg_plane_estimator_replay pcseg_plane_estimators_transform pcseg_plane_estimators_merge
 pcseg_batch_submit_regions pcseg_transform_in_place pcseg_gather_points
 pcseg_batch_create pcseg_batch_destroy pcseg_batch_run pcseg_batch_submit pcseg_batch_wait pcseg_batch_stream pcseg_batch_frame_stats
@@ -368,6 +368,14 @@ class Context:
         self._check(self.L.pcseg_seeds_plane_support(
             self.h, _addr(xyz), _addr(normals), rows, cols, neighborhood_size,
             C.c_float(max_plane_distance), min_support, _addr(out), out.size, C.byref(n)))
+        return out[:n.value].copy()
+
+    def mean_shift_sort_order(self, intensities, sort_mode=0):
+        """Positions of the valid seeds (intensity >= 0) in the order of the reference's sort."""
+        v = _f32(intensities).reshape(-1)
+        out = np.zeros(max(v.size, 1), np.int32)
+        n = C.c_int(0)
+        self._check(self.L.pcseg_mean_shift_sort_order(self.h, _addr(v), v.size, int(sort_mode), _addr(out), C.byref(n)))
         return out[:n.value].copy()
 
     def seeds_average_normals(self, xyz, normals, rows, cols, neighborhood_size=5,
