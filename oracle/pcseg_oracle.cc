@@ -942,6 +942,9 @@ class ClusterRegion {
 // ---------------------------------------------------------------------------
 // SegmentRegions driver, ps/segmentation.h:239-292
 // ---------------------------------------------------------------------------
+// diagnostics: growth attempts of the last SegmentRegions calls by inlier-count bucket
+// (0, 1, 2-7, 8-31, 32-255, 256-4095, >= 4096) and queue pops per bucket
+static long long g_attempt_hist[16];
 template <typename RegionT, typename InputT, typename NeighborT, typename CfgT>
 void SegmentRegions(const InputT& input, const int* seeds, int n_seeds,
                     const CfgT& cfg, oracle_regions* regions, int* labels,
@@ -954,13 +957,21 @@ void SegmentRegions(const InputT& input, const int* seeds, int n_seeds,
     --num_seed_points;
     if (labels[seed] != kUnlabeled) continue;
     region.Init(input, seed, &unexamined);
+    long long pops = 0;
     while (!unexamined.empty()) {
       const NeighborT cand = unexamined.front();
       unexamined.pop();
+      ++pops;
       if (region.CheckInlierAndUpdate(input, cand, labels,
                                       regions->count() + initial_id_offset)) {
         region.AddNeighbors(input, cand, labels, &unexamined);
       }
+    }
+    {
+      const size_t ni = region.inlier_indices().size();
+      const int b = ni == 0 ? 0 : ni == 1 ? 1 : ni < 8 ? 2 : ni < 32 ? 3 : ni < 256 ? 4 : ni < 4096 ? 5 : 6;
+      ++g_attempt_hist[b];
+      g_attempt_hist[8 + b] += pops;
     }
     bool ok;
     if constexpr (std::is_same<RegionT, PlanarRegion>::value)
@@ -1154,6 +1165,11 @@ float oracle_polygon_area(const float* xyz, int n_points, const int* indices,
 
 void oracle_prepare_unlabeled_labels(int* labels, int n) {
   for (int i = 0; i < n; ++i) labels[i] = kUnlabeled;
+}
+
+void oracle_debug_attempt_hist(long long out[16], int reset) {
+  for (int i = 0; i < 16; ++i) out[i] = g_attempt_hist[i];
+  if (reset) for (int i = 0; i < 16; ++i) g_attempt_hist[i] = 0;
 }
 
 int oracle_segment_planar(const float* xyz, const float* normals, int rows,

@@ -102,6 +102,9 @@ int oracle_segment_planar(const float* xyz, const float* normals, int rows,
                           const oracle_planar_config* cfg, int id_offset,
                           int* labels, oracle_regions** out);
 
+/* diagnostics: growth attempts / queue pops by inlier-count bucket since the last reset */
+void oracle_debug_attempt_hist(long long out[16], int reset);
+
 /* ps/segmentation.h:239-292 with RegionT = ClusterRegion (ps/cluster_region.h). */
 int oracle_segment_cluster(const float* xyz, int rows, int cols,
                            const int* seeds, int n_seeds,

@@ -26,6 +26,7 @@ constexpr int kRejBase = -1000;                     // transient, never escapes 
 constexpr int kErrRegionCap = 1;    // more accepted regions than meta slots
 constexpr int kErrBoundaryCap = 2;  // boundary buffer overflow
 constexpr int kErrTraceCheck = 4;   // reference CHECK_GE(new_direction_index, 0) would abort
+constexpr int kErrWatchdog = 8;     // a growth loop exceeded its iteration bound (internal error)
 
 struct FrameStats {
   int n_planar, n_cluster, planar_inliers, cluster_inliers;

@@ -46,6 +46,7 @@ struct PlanarArgs {
   long long* prof;       // nullable: [F][16] clock64 totals / counters (diagnostics)
   int ring;              // smem ring entries (power of two) for the shared-memory path
   int mask_words;        // ceil(N / 32)
+  int nstage;            // staged-inlier ring slots (power of two), grow_planar_wave2.cuh
 };
 
 #ifdef PCSEG_PROFILE

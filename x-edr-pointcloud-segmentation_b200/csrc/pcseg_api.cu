@@ -32,7 +32,15 @@ constexpr int kGrowBlock = 256;
 #define PCSEG_CLUSTER_BLOCK 512
 #endif
 constexpr int kClusterBlock = PCSEG_CLUSTER_BLOCK;  // queue entries evaluated per step of cluster growth
-constexpr int kPipeBlock = 32 * kPipeWarps;  // planar fast path (grow_planar_pipe.cuh)
+constexpr int kPipeBlock = 32 * kPipeWarps;  // planar pipeline path (grow_planar_pipe.cuh)
+#ifndef PCSEG_WAVE_BLOCK
+#define PCSEG_WAVE_BLOCK 512
+#endif
+#ifndef PCSEG_WAVE2_BLOCK
+#define PCSEG_WAVE2_BLOCK 288
+#endif
+constexpr int kWave2Block = PCSEG_WAVE2_BLOCK;  // planar fast path (grow_planar_wave2.cuh): W = kWave2Block - 64
+constexpr int kWaveBlock = PCSEG_WAVE_BLOCK;  // planar fast path (grow_planar_wave.cuh): W = kWaveBlock - 32 entries per window
 constexpr int kInvCap = 4096;
 
 struct DevBuf {
@@ -314,33 +322,85 @@ int run_planar(pcseg_batch* b, const float* xyz_dev, const float* normals_dev, c
   a.meta = b->meta_planar.as<PlanarMeta>(); a.rcap = b->rcap_planar;
   a.stats = b->stats.as<FrameStats>();
   a.prof = b->prof.as<long long>();
-  // shared-memory fast path when the 1-bit/cell mask and the FIFO ring fit
   a.mask_words = (int)((b->N + 31) / 32);
+  const char* mode_env = getenv("PCSEG_PLANAR_MODE");  // diagnostics: "pipe" / "global" force the older paths
+  const bool force_global = getenv("PCSEG_FORCE_GLOBAL_PATH") || (mode_env && !strcmp(mode_env, "global"));
+  const bool want_pipe = mode_env && !strcmp(mode_env, "pipe");
+  cudaFuncAttributes fattr;
+  const bool want_wave1 = mode_env && !strcmp(mode_env, "wave1");
+  a.nstage = 0;
+  // ---- window-parallel fast path with asynchronous re-fits (grow_planar_wave2.cuh)
+  if (!force_global && !want_pipe && !want_wave1 && b->N < (size_t)kW2MaxCells) {
+    CU_TRY(c, cudaFuncGetAttributes(&fattr, planar_grow_kernel<kWave2Block, 3, false>));
+    const size_t st = fattr.sharedSizeBytes;
+    const int nstage = 512;
+    const size_t fixed = (size_t)nstage * 40 + kW2Hash * 4 + kW2Rej * 4 + 16;
+    const size_t smem_max = 227 * 1024 - st;
+    // as many frames per SM as the mask allows (228 KB per SM, 1 KB reserved per CTA): 3, 2 or 1
+    int ring = 0;
+    for (int per_sm = 3; per_sm >= 1 && !ring; --per_sm) {
+      const size_t lim = per_sm == 1 ? smem_max : (228 * 1024) / per_sm - 1024 - st;
+      for (int r = (per_sm == 3 ? 512 : 2048); r >= 256 && !ring; r /= 2)
+        if ((size_t)a.mask_words * 4 + (size_t)r * 20 + fixed <= lim) ring = r;
+    }
+    if (ring) {
+      const size_t smem = (size_t)a.mask_words * 4 + (size_t)ring * 20 + fixed;
+      a.ring = ring;
+      a.nstage = nstage;
+      CU_TRY(c, cudaFuncSetAttribute(planar_grow_kernel<kWave2Block, 3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      planar_grow_kernel<kWave2Block, 3, false><<<b->n_frames, kWave2Block, smem, stream>>>(a, ClusterArgs{});
+      ++c->launches;
+      CU_TRY(c, cudaGetLastError());
+      return PCSEG_OK;
+    }
+  }
+  // ---- window-parallel path with in-window re-fits (grow_planar_wave.cuh) when mask + ring + tables fit
+  if (!force_global && !want_pipe && b->N < (size_t)kWaveMaxCells) {
+    CU_TRY(c, cudaFuncGetAttributes(&fattr, planar_grow_kernel<kWaveBlock, 2, false>));
+    const size_t st = fattr.sharedSizeBytes;
+    const size_t fixed = (size_t)(kWaveBlock - 32) * 40 + kWaveHash * 4 + kWaveRej * 4 + 16;
+    const size_t smem_two = (228 * 1024) / 2 - 1024 - st;   // two frames per SM (1 KB reserved per CTA)
+    const size_t smem_max = 227 * 1024 - st;
+    int ring = 4096;
+    while (ring > 512 && (size_t)a.mask_words * 4 + (size_t)ring * 20 + fixed > smem_two) ring /= 2;
+    if ((size_t)a.mask_words * 4 + (size_t)ring * 20 + fixed > smem_two) {  // one frame per SM
+      ring = 4096;
+      while (ring > 512 && (size_t)a.mask_words * 4 + (size_t)ring * 20 + fixed > smem_max) ring /= 2;
+    }
+    const size_t smem = (size_t)a.mask_words * 4 + (size_t)ring * 20 + fixed;
+    if (smem <= smem_max) {
+      a.ring = ring;
+      CU_TRY(c, cudaFuncSetAttribute(planar_grow_kernel<kWaveBlock, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      planar_grow_kernel<kWaveBlock, 2, false><<<b->n_frames, kWaveBlock, smem, stream>>>(a, ClusterArgs{});
+      ++c->launches;
+      CU_TRY(c, cudaGetLastError());
+      return PCSEG_OK;
+    }
+  }
+  // ---- warp-specialised pipeline path when the 1-bit/cell mask and the FIFO ring fit
   a.ring = 2048;
   const size_t smem_fixed = 32 * 11 * sizeof(float) + kHashSize * sizeof(unsigned);
   size_t smem = (size_t)a.mask_words * 4 + (size_t)a.ring * 20 + smem_fixed;
-  cudaFuncAttributes fattr;
-  CU_TRY(c, cudaFuncGetAttributes(&fattr, planar_grow_kernel<kPipeBlock, true, false>));
+  CU_TRY(c, cudaFuncGetAttributes(&fattr, planar_grow_kernel<kPipeBlock, 1, false>));
   const size_t smem_static = fattr.sharedSizeBytes;
   // two frames per SM when they fit (228 KB per SM, 1 KB reserved per CTA), else one
   const size_t smem_two = (228 * 1024) / 2 - 1024 - smem_static;
   const size_t smem_max = 227 * 1024 - smem_static;
-  bool use_smem = b->N < (1u << 24) && (size_t)a.mask_words * 4 + 256 * 20 + smem_fixed <= smem_max &&
-                  !getenv("PCSEG_FORCE_GLOBAL_PATH");
+  bool use_smem = b->N < (1u << 23) && (size_t)a.mask_words * 4 + 256 * 20 + smem_fixed <= smem_max && !force_global;
   if (use_smem) {
     if (smem > smem_two && (size_t)a.mask_words * 4 + 1024 * 20 + smem_fixed <= smem_two) a.ring = 1024;
     smem = (size_t)a.mask_words * 4 + (size_t)a.ring * 20 + smem_fixed;
     while (smem > smem_max) { a.ring /= 2; smem = (size_t)a.mask_words * 4 + (size_t)a.ring * 20 + smem_fixed; }
     if (fuse_cluster && getenv("PCSEG_FUSE")) {  // opt-in: measured slower (the extra code thrashes the instruction cache)
-      CU_TRY(c, cudaFuncSetAttribute(planar_grow_kernel<kPipeBlock, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      planar_grow_kernel<kPipeBlock, true, true><<<b->n_frames, kPipeBlock, smem, stream>>>(a, *fuse_cluster);
+      CU_TRY(c, cudaFuncSetAttribute(planar_grow_kernel<kPipeBlock, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      planar_grow_kernel<kPipeBlock, 1, true><<<b->n_frames, kPipeBlock, smem, stream>>>(a, *fuse_cluster);
       if (fused) *fused = true;
     } else {
-      CU_TRY(c, cudaFuncSetAttribute(planar_grow_kernel<kPipeBlock, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      planar_grow_kernel<kPipeBlock, true, false><<<b->n_frames, kPipeBlock, smem, stream>>>(a, ClusterArgs{});
+      CU_TRY(c, cudaFuncSetAttribute(planar_grow_kernel<kPipeBlock, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      planar_grow_kernel<kPipeBlock, 1, false><<<b->n_frames, kPipeBlock, smem, stream>>>(a, ClusterArgs{});
     }
   } else {
-    planar_grow_kernel<kGrowBlock, false, false><<<b->n_frames, kGrowBlock, 0, stream>>>(a, ClusterArgs{});
+    planar_grow_kernel<kGrowBlock, 0, false><<<b->n_frames, kGrowBlock, 0, stream>>>(a, ClusterArgs{});
   }
   ++c->launches;
   CU_TRY(c, cudaGetLastError());

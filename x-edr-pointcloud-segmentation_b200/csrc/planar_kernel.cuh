@@ -4,23 +4,31 @@
 #include "grow_planar.cuh"
 #include "grow_planar_smem.cuh"
 #include "grow_planar_pipe.cuh"
+#include "grow_planar_wave.cuh"
+#include "grow_planar_wave2.cuh"
+#include <type_traits>
 #include "grow_cluster.cuh"
 
 namespace pcseg {
 
-// SMEM = true : labels mirrored as a 1-bit/cell mask + FIFO ring in dynamic
-//               shared memory (planar_grow_warp_smem); needs
-//               mask_words*4 + ring*20 + 32*11*4 + kHashSize*4 bytes.
-// SMEM = false: everything through L2 (planar_grow_warp); any cloud size.
+// MODE = 3 : window-parallel growth with asynchronous re-fit warps and speculative commit
+//            (grow_planar_wave2.cuh); BLOCK = W + 64; mask_words*4 + ring*20 + nstage*40 +
+//            kW2Hash*4 + kW2Rej*4 bytes of dynamic shared memory.
+// MODE = 2 : window-parallel speculative growth by the whole CTA (grow_planar_wave.cuh): labels
+//            mirrored as a 1-bit/cell mask + FIFO ring + claim tables in dynamic shared memory
+//            (mask_words*4 + ring*20 + W*40 + kWaveHash*4 + kWaveRej*4 bytes); BLOCK = W + 32.
+// MODE = 1 : warp-specialised pipeline on chunks of 32 entries (grow_planar_pipe.cuh), same
+//            mask + ring (mask_words*4 + ring*20 + 32*11*4 + kHashSize*4 bytes).
+// MODE = 0 : everything through L2 (planar_grow_warp); any cloud size.
 // FUSE = true : the frame's CTA goes on with SegmentRegions<ClusterRegion<>> (seeds all
 //               descending or ca.seeds, id offset = the frame's plane count) as soon as its
 //               own planar stage is done, instead of waiting for the slowest frame of the batch.
 #ifdef PLANAR_MAXNREG
 #define PLANAR_REG_ATTR __maxnreg__(PLANAR_MAXNREG)
 #else
-#define PLANAR_REG_ATTR __launch_bounds__(SMEM ? 384 : BLOCK, SMEM ? 2 : 1)  // register budget of the 12-warp CTA (<= 85) for every warp count
+#define PLANAR_REG_ATTR __launch_bounds__(MODE == 1 ? 384 : BLOCK, MODE ? 2 : 1)  // pipeline: register budget of the 12-warp CTA (<= 85) for every warp count
 #endif
-template <int BLOCK, bool SMEM, bool FUSE>
+template <int BLOCK, int MODE, bool FUSE>
 __global__ void PLANAR_REG_ATTR planar_grow_kernel(PlanarArgs a, ClusterArgs ca) {
   extern __shared__ __align__(16) unsigned char dyn_smem[];
   const int f = blockIdx.x;
@@ -48,15 +56,50 @@ __global__ void PLANAR_REG_ATTR planar_grow_kernel(PlanarArgs a, ClusterArgs ca)
   __shared__ TraceResult s_trace;
   __shared__ float s_area;
   __shared__ float s_cross[3 * BLOCK];
-  __shared__ double s_ax[BLOCK], s_ay[BLOCK], s_bx[BLOCK], s_by[BLOCK];
+  __shared__ double s_ext[4][BLOCK / 32];
+  constexpr bool SMEM = MODE != 0;
 
   PlanarSmem sm;
+  WaveSmem wsm;
   int tag_base = 0;
   int refit_last = 0;  // warp R: newest ticket seen on its slot
-  __shared__ PipeCtl s_ctl;
-  static_assert(!SMEM || BLOCK == 32 * kPipeWarps, "pipeline roles: warp 0 = A, 1 = S, 4-7 = B, 2-3 and 8.. = re-fit");
-  __shared__ PipeBShared s_bsh;
-  if constexpr (SMEM) {
+  W2Smem w2sm;
+  __shared__ std::conditional_t<MODE == 3, W2Ctl, std::conditional_t<MODE == 2, WaveCtl, PipeCtl>> s_ctl;
+  (void)w2sm;
+  if constexpr (MODE == 3) {
+    w2sm.mask = reinterpret_cast<unsigned*>(dyn_smem);
+    w2sm.q_tag = reinterpret_cast<int*>(w2sm.mask + a.mask_words);
+    w2sm.q_cell = w2sm.q_tag + a.ring;
+    w2sm.q_xyz = reinterpret_cast<float*>(w2sm.q_cell + a.ring);
+    w2sm.stage = w2sm.q_xyz + 3 * a.ring + ((a.mask_words + 5 * a.ring) & 1);  // 8-byte aligned
+    w2sm.htab = reinterpret_cast<unsigned*>(w2sm.stage + 10 * a.nstage);
+    w2sm.rej = w2sm.htab + kW2Hash;
+    w2sm.ring = a.ring;
+    w2sm.nstage = a.nstage;
+    sm.mask = w2sm.mask;
+    for (int i = tid; i < a.ring; i += BLOCK) w2sm.q_tag[i] = -1;
+    for (int i = tid; i < kW2Hash; i += BLOCK) w2sm.htab[i] = kHashEmpty;
+    for (int i = tid; i < kW2Rej; i += BLOCK) w2sm.rej[i] = kHashEmpty;
+  }
+  static_assert(MODE != 1 || BLOCK == 32 * kPipeWarps, "pipeline roles: warp 0 = A, 1 = S, 4-7 = B, 2-3 and 8.. = re-fit");
+  static_assert(MODE != 2 || (BLOCK % 32 == 0 && (BLOCK - 32) * 4 <= (1 << kWaveKeyBits)), "wave: claim key bits");
+  __shared__ std::conditional_t<MODE == 1, PipeBShared, int> s_bsh;
+  (void)wsm; (void)refit_last; (void)s_bsh;
+  if constexpr (MODE == 2) {
+    wsm.mask = reinterpret_cast<unsigned*>(dyn_smem);
+    wsm.q_tag = reinterpret_cast<int*>(wsm.mask + a.mask_words);
+    wsm.q_cell = wsm.q_tag + a.ring;
+    wsm.q_xyz = reinterpret_cast<float*>(wsm.q_cell + a.ring);
+    wsm.stage = wsm.q_xyz + 3 * a.ring + ((a.mask_words + 5 * a.ring) & 1);  // 8-byte aligned
+    wsm.htab = reinterpret_cast<unsigned*>(wsm.stage + 10 * (BLOCK - 32));
+    wsm.rej = wsm.htab + kWaveHash;
+    wsm.ring = a.ring;
+    sm.mask = wsm.mask;
+    for (int i = tid; i < a.ring; i += BLOCK) wsm.q_tag[i] = -1;
+    for (int i = tid; i < kWaveHash; i += BLOCK) wsm.htab[i] = kHashEmpty;
+    for (int i = tid; i < kWaveRej; i += BLOCK) wsm.rej[i] = kHashEmpty;
+  }
+  if constexpr (MODE == 1) {
     if (tid == 0) {
       s_ctl.ticket = 0;
       for (int i = 0; i < kPipeDW; ++i) { s_ctl.req_ticket[i] = 0; s_ctl.res_ticket[i] = 0; s_ctl.req_expect[i] = 0; }
@@ -70,6 +113,8 @@ __global__ void PLANAR_REG_ATTR planar_grow_kernel(PlanarArgs a, ClusterArgs ca)
     sm.ring = a.ring;
     for (int i = tid; i < a.ring; i += BLOCK) sm.q_tag[i] = -1;
     for (int i = tid; i < kHashSize; i += BLOCK) sm.htab[i] = kHashEmpty;
+  }
+  if constexpr (SMEM) {
     // mask bit <=> labels[cell] == kUnlabeled
     const int lane = tid & 31;
     for (int b0 = (tid >> 5) * 32; b0 < a.mask_words * 32; b0 += BLOCK) {
@@ -125,7 +170,13 @@ __global__ void PLANAR_REG_ATTR planar_grow_kernel(PlanarArgs a, ClusterArgs ca)
     const int label_id = nreg + a.id_offset;
     const int base = inl_total;
 
-    if constexpr (SMEM) {
+    if constexpr (MODE == 3) {
+      planar_grow_wave2<BLOCK>(a, xyz, nrm, a.labels + (size_t)f * N, a.queue + (size_t)f * a.qcap * 2, inliers, seed,
+                               label_id, base, tag_base, w2sm, s_ctl, &s_res);
+    } else if constexpr (MODE == 2) {
+      planar_grow_wave<BLOCK>(a, xyz, nrm, a.labels + (size_t)f * N, a.queue + (size_t)f * a.qcap * 2, inliers, seed,
+                              label_id, base, tag_base, wsm, s_ctl, &s_res);
+    } else if constexpr (MODE == 1) {
       int* gqueue = a.queue + (size_t)f * a.qcap * 2;
       if (tid == 0) {
         const V3 sp = ld3(xyz, seed);
@@ -157,6 +208,7 @@ __global__ void PLANAR_REG_ATTR planar_grow_kernel(PlanarArgs a, ClusterArgs ca)
     __syncthreads();
     const int ninl = s_res.ninl;
     tag_base += s_res.tail;
+    if (s_res.steps < 0) { err |= kErrWatchdog; break; }
     steps += s_res.steps;
     refits += s_res.refits;
 
@@ -202,20 +254,24 @@ __global__ void PLANAR_REG_ATTR planar_grow_kernel(PlanarArgs a, ClusterArgs ca)
         if (x < ax || (x == ax && y < ay)) { ax = x; ay = y; }
         if (x > bx || (x == bx && y > by)) { bx = x; by = y; }
       }
-      s_ax[tid] = ax; s_ay[tid] = ay; s_bx[tid] = bx; s_by[tid] = by;
-      __syncthreads();
-      for (int s = 256; s > 0; s >>= 1) {  // BLOCK <= 512, any multiple of 32
-        if (tid < s && tid + s < BLOCK) {
-          if (s_ax[tid + s] < s_ax[tid] || (s_ax[tid + s] == s_ax[tid] && s_ay[tid + s] < s_ay[tid])) {
-            s_ax[tid] = s_ax[tid + s]; s_ay[tid] = s_ay[tid + s];
-          }
-          if (s_bx[tid + s] > s_bx[tid] || (s_bx[tid + s] == s_bx[tid] && s_by[tid + s] > s_by[tid])) {
-            s_bx[tid] = s_bx[tid + s]; s_by[tid] = s_by[tid + s];
-          }
-        }
-        __syncthreads();
+      // lexicographic min / max over the CTA: warp shuffles, then one value per warp
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const double oax = __shfl_xor_sync(0xffffffffu, ax, o), oay = __shfl_xor_sync(0xffffffffu, ay, o);
+        const double obx = __shfl_xor_sync(0xffffffffu, bx, o), oby = __shfl_xor_sync(0xffffffffu, by, o);
+        if (oax < ax || (oax == ax && oay < ay)) { ax = oax; ay = oay; }
+        if (obx > bx || (obx == bx && oby > by)) { bx = obx; by = oby; }
       }
-      ax = s_ax[0]; ay = s_ay[0]; bx = s_bx[0]; by = s_by[0];
+      if ((tid & 31) == 0) {
+        s_ext[0][tid >> 5] = ax; s_ext[1][tid >> 5] = ay; s_ext[2][tid >> 5] = bx; s_ext[3][tid >> 5] = by;
+      }
+      __syncthreads();
+      ax = s_ext[0][0]; ay = s_ext[1][0]; bx = s_ext[2][0]; by = s_ext[3][0];
+      for (int w = 1; w < BLOCK / 32; ++w) {
+        const double oax = s_ext[0][w], oay = s_ext[1][w], obx = s_ext[2][w], oby = s_ext[3][w];
+        if (oax < ax || (oax == ax && oay < ay)) { ax = oax; ay = oay; }
+        if (obx > bx || (obx == bx && oby > by)) { bx = obx; by = oby; }
+      }
       int off_line = 0;
       for (int k = tid; k < nb; k += BLOCK) {
         double x, y;
