@@ -10,8 +10,8 @@ import pcseg, bench
 frames = bench.gen_frames(list(range(256)))
 ctx = pcseg.Context(0)
 params = pcseg.pipeline_params(seed_mode=pcseg.SEEDS_ALL_DESCENDING, run_cluster=True)
-names = ["verify(top)", "eval(->B1)", "scan+expand+commit", "leader.poll", "iteration", "rollbacks", "windows", "-",
-         "-", "-", "-", "entries", "refits", "seed_scan", "finalize", "planar_cycles"]
+names = ["verify(top)", "eval(->B1)", "scan+expand+commit", "leader.poll", "iteration", "rollbacks", "windows", "scan+stage+rec",
+         "nbr tests+loads", "claims loop", "commit", "entries", "refits", "seed_scan", "finalize", "planar_cycles"]
 for F in [int(x) for x in (sys.argv[1:] or ["1", "16", "256"])]:
     b = pcseg.Batch(ctx, F, 480, 640)
     for _ in range(2):

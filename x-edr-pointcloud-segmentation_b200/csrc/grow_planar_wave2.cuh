@@ -68,8 +68,8 @@ struct W2Ctl {
   float cur_s[10];          // warp S: sums after the last consumed window
   W2Rec rec[kW2Rec];
   // entry-side scratch
-  unsigned wacc[8];
-  int wtot[8];
+  alignas(16) unsigned wacc[8];   // accept ballots per entry warp (read as two uint4)
+  alignas(16) int wtot[8];        // winners per entry warp
   volatile int unres[2];
   int tstar;
   volatile int wd;          // a bounded wait of the leader ran out (internal error): everyone leaves
@@ -366,13 +366,16 @@ __device__ __forceinline__ void planar_grow_wave2(const PlanarArgs& a, const flo
       // (a growth that does not end is a bug, never an input property: leave instead of hanging the GPU)
       if (++it > it_limit) { watchdog = true; break; }
       int* bc = ctl.bcast[it & 1];
-      // ---- verification of the oldest unverified window once its planes are final
+      if (head == tail && k == kv) break;
+
+      // ---- phase 1 (up to barrier B1): verification compare of the oldest open window (its planes
+      // are final), and of the next window: entry, plane test, neighbour mask tests, first claims
+      bool bad = false;
       if (ready) {
         const int age = k - kv;  // 1 .. 3
         const W2Saved sv = age == 1 ? s1 : (age == 2 ? s2 : s3);
         const int used = age == 1 ? used1 : (age == 2 ? used2 : used3);
         const W2Rec& rv = ctl.rec[kv & (kW2Rec - 1)];
-        bool bad = false;
         if (sv.meta & 2) {
           const int ver = rv.g0 + (sv.meta >> 2);
           if (ver != used) {
@@ -385,122 +388,156 @@ __device__ __forceinline__ void planar_grow_wave2(const PlanarArgs& a, const flo
 #endif
           if (bad) atomicMin(&ctl.tstar, tid);
         }
-        const bool any = w2_bar_or(1, W, bad);
-        if (!any) {
-          ++kv;
-        } else {
-          // ---- mis-speculation: undo windows k-1 .. kv in reverse order, resume at window kv cut at t*
-          PROF_CNT(5, 1);
-          const int tstar = ctl.tstar;
-#ifdef PCSEG_FORCE_ROLLBACK
-          forced_k = kv;
-#endif
-          const int tail_old = tail;
-          for (int r = k - 1; r >= kv; --r) {
-            const int ag = k - r;
-            const W2Saved su = ag == 1 ? s1 : (ag == 2 ? s2 : s3);
-            const W2Rec& ru = ctl.rec[r & (kW2Rec - 1)];
-            // cells this window appended: unlabeled again
-            for (int i = tid; i < ru.nwin; i += W) {
-              const int qp = ru.tailb + i;
-              const int n = *(volatile int*)(gqueue + (qp & (a.qcap - 1)));
-              atomicOr(&sm.mask[n >> 5], 1u << (n & 31));
-            }
-            w2_bar(1, W);
-            // its rejected entries are queued again, its accepted entries lose their label
-            if (su.meta & 2) {
-              if (su.meta & 1) labels[su.cand] = kUnlabeled;
-              else atomicAnd(&sm.mask[su.cand >> 5], ~(1u << (su.cand & 31)));
-            }
-            w2_bar(1, W);
-          }
-          const W2Rec& rj = ctl.rec[kv & (kW2Rec - 1)];
-          head = rj.head; tail = rj.tailb; ninl = rj.ninl0; inper = rj.inper0; gtot = rj.g0;
-          // ring slots of the dropped queue positions must never match again
-          for (int qp = tail + tid; qp < tail_old; qp += W)
-            if (sm.q_tag[qp & (R - 1)] == tag_base + qp) sm.q_tag[qp & (R - 1)] = -1;
-          k = kv;
-          force_lim = max(tstar, 1);   // entry 0 is evaluated with the exact plane in the redo
-          ++epoch;
-          if (tid == 0) {
-            ctl.e_pub = kv;
-            ctl.rb_k = kv;
-            ctl.rb_g = gtot;
-            __threadfence_block();
-            ctl.rb_epoch = epoch;
-            for (int spin = 0; ctl.s_ack != epoch || ctl.r_ack != epoch; ++spin) {
-              if (spin > (1 << 22)) { ctl.wd = 1; break; }
-              __nanosleep(20);
-            }
-            __threadfence_block();
-            ctl.tstar = INT_MAX;
-          }
-          w2_bar(1, W);
-          if (ctl.wd) { watchdog = true; break; }
-          ready = 0;
-          vcur = gtot;
-          continue;
-        }
       }
-      PROF_T(w1);
-      PROF_ACC(0, w0, w1);
-      if (head == tail && k == kv) break;
-
-      // ---- the next window
       int m = 0;
-      if (head < tail && k - kv < 3) {
+      if (head < tail && k - kv < 3 + (ready ? 1 : 0)) {
         m = min(min(W, tail - head), force_lim);
-        if (capl - inper < m) m = (int)(capl - inper);
+        if (capl - inper < m) m = (int)(capl - inper);  // at most kW2MaxJ re-fits inside a window
       }
-      int na = 0, J = 0, nwin = 0;
+      const int aw = (m + 31) >> 5;      // entry warps that hold entries of this window
+      const bool active = warp < aw;
+      const bool mine = tid < m;
       W2Saved cur;
       cur.cand = -1; cur.meta = 0; cur.p = V3{0.0f, 0.0f, 0.0f};
-      if (m > 0) {
-        const int aw = (m + 31) >> 5;      // entry warps that hold entries of this window
-        const bool active = warp < aw;
-        const bool mine = tid < m;
-        // ---- evaluate with the newest published plane (ps/planar_region.h:168)
+      bool acc = false;
+      int rej_slot = -1;
+      bool win[4] = {false, false, false, false};
+      bool unres[4] = {false, false, false, false};
+      bool tried[4] = {false, false, false, false};   // mask test done and negative
+      int nb[4] = {-1, -1, -1, -1};
+      int probe[4] = {0, 0, 0, 0};
+      V3 nx[4];
+      if (mine) {
+        // evaluate with the newest published plane (ps/planar_region.h:168)
         const float* pc = ctl.planes[vcur & (kW2Ver - 1)];
         const Plane P{V3{pc[0], pc[1], pc[2]}, pc[3]};
-        bool acc = false;
-        int rej_slot = -1;
-        if (mine) {
-          const int pos = head + tid;
-          const int slot = pos & (R - 1);
-          if (sm.q_tag[slot] == tag_base + pos) {
-            cur.cand = sm.q_cell[slot];
-            cur.p = V3{sm.q_xyz[3 * slot], sm.q_xyz[3 * slot + 1], sm.q_xyz[3 * slot + 2]};
-          } else {
-            cur.cand = *(volatile int*)(gqueue + (pos & (a.qcap - 1)));
-            cur.p = ld3(xyz, cur.cand);
-          }
-          acc = plane_abs_distance(P, cur.p) < thr;
-          if (!acc) {  // rejected: unlabeled again for LATER entries only (:181)
-            unsigned h = w2_hash(cur.cand, kW2Rej - 1);
-            const unsigned v = ((unsigned)cur.cand << kW2KeyBits) | (unsigned)tid;
-            while (atomicCAS(&sm.rej[h], kHashEmpty, v) != kHashEmpty) h = (h + 1) & (kW2Rej - 1);
-            rej_slot = (int)h;
-          }
+        const int pos = head + tid;
+        const int slot = pos & (R - 1);
+        if (sm.q_tag[slot] == tag_base + pos) {
+          cur.cand = sm.q_cell[slot];
+          cur.p = V3{sm.q_xyz[3 * slot], sm.q_xyz[3 * slot + 1], sm.q_xyz[3 * slot + 2]};
+        } else {
+          cur.cand = *(volatile int*)(gqueue + (pos & (a.qcap - 1)));
+          cur.p = ld3(xyz, cur.cand);
         }
-        if (active) {
-          const unsigned b = __ballot_sync(FULL, acc);
-          if (lane == 0) ctl.wacc[warp] = b;
+        const int cand = cur.cand;
+        acc = plane_abs_distance(P, cur.p) < thr;
+        if (acc) {
+          // AddNeighbors, ps/planar_region.h:229-255: (c-1,r), (c,r-1), (c,r+1), (c+1,r)
+          int row, col;
+          fast_divmod(fdrows, cand, &col, &row);
+          if (col > 0) nb[0] = cand - rows;
+          if (row > 0) nb[1] = cand - 1;
+          if (row < rows - 1) nb[2] = cand + 1;
+          if (col < cols - 1) nb[3] = cand + rows;
+#pragma unroll
+          for (int s = 0; s < 4; ++s) {
+            if (nb[s] < 0) continue;
+            if (mask_test(sm.mask, nb[s])) {
+              unres[s] = true;
+              nx[s] = ld3(xyz, nb[s]);  // in flight during the claims; the winner stores it into the ring
+              probe[s] = (int)w2_hash(nb[s], kW2Hash - 1);
+              // the smallest (entry, slot) key per neighbour cell wins the enqueue
+              atomicMin(&sm.htab[probe[s]], ((unsigned)nb[s] << kW2KeyBits) | (unsigned)(tid * 4 + s));
+            } else {
+              tried[s] = true;
+            }
+          }
+        } else {  // rejected: unlabeled again for LATER entries only (:181)
+          unsigned h = w2_hash(cand, kW2Rej - 1);
+          const unsigned v = ((unsigned)cand << kW2KeyBits) | (unsigned)tid;
+          while (atomicCAS(&sm.rej[h], kHashEmpty, v) != kHashEmpty) h = (h + 1) & (kW2Rej - 1);
+          rej_slot = (int)h;
         }
-        w2_bar(1, W);  // B1
-        PROF_T(w2);
-        PROF_ACC(1, w1, w2);
-        // ---- scan
+      }
+      if (active) {
+        const unsigned b = __ballot_sync(FULL, acc);
+        if (lane == 0) ctl.wacc[warp] = b;
+      }
+      PROF_T(w1);
+      PROF_ACC(1, w0, w1);
+      const bool any_bad = w2_bar_or(1, W, bad);  // B1
+      PROF_T(w2);
+      PROF_ACC(0, w1, w2);
+      if (any_bad) {
+        // ---- mis-speculation in window kv.  Withdraw what phase 1 did for the next window, undo the
+        // open windows k-1 .. kv in reverse order, resume at window kv cut at the first differing entry
+        PROF_CNT(5, 1);
+#pragma unroll
+        for (int s = 0; s < 4; ++s)
+          if (unres[s]) sm.htab[probe[s]] = kHashEmpty;
+        if (rej_slot >= 0) sm.rej[rej_slot] = kHashEmpty;
+        const int tstar = ctl.tstar;
+#ifdef PCSEG_FORCE_ROLLBACK
+        forced_k = kv;
+#endif
+        const int tail_old = tail;
+        for (int r = k - 1; r >= kv; --r) {
+          const int ag = k - r;
+          const W2Saved su = ag == 1 ? s1 : (ag == 2 ? s2 : s3);
+          const W2Rec& ru = ctl.rec[r & (kW2Rec - 1)];
+          // cells this window appended: unlabeled again
+          for (int i = tid; i < ru.nwin; i += W) {
+            const int qp = ru.tailb + i;
+            const int n = *(volatile int*)(gqueue + (qp & (a.qcap - 1)));
+            atomicOr(&sm.mask[n >> 5], 1u << (n & 31));
+          }
+          w2_bar(1, W);
+          // its rejected entries are queued again, its accepted entries lose their label
+          if (su.meta & 2) {
+            if (su.meta & 1) labels[su.cand] = kUnlabeled;
+            else atomicAnd(&sm.mask[su.cand >> 5], ~(1u << (su.cand & 31)));
+          }
+          w2_bar(1, W);
+        }
+        const W2Rec& rj = ctl.rec[kv & (kW2Rec - 1)];
+        head = rj.head; tail = rj.tailb; ninl = rj.ninl0; inper = rj.inper0; gtot = rj.g0;
+        // ring slots of the dropped queue positions must never match again
+        for (int qp = tail + tid; qp < tail_old; qp += W)
+          if (sm.q_tag[qp & (R - 1)] == tag_base + qp) sm.q_tag[qp & (R - 1)] = -1;
+        k = kv;
+        force_lim = max(tstar, 1);   // entry 0 is evaluated with the exact plane in the redo
+        ++epoch;
+        if (tid == 0) {
+          ctl.e_pub = kv;
+          ctl.rb_k = kv;
+          ctl.rb_g = gtot;
+          __threadfence_block();
+          ctl.rb_epoch = epoch;
+          for (int spin = 0; ctl.s_ack != epoch || ctl.r_ack != epoch; ++spin) {
+            if (spin > (1 << 22)) { ctl.wd = 1; break; }
+            __nanosleep(20);
+          }
+          __threadfence_block();
+          ctl.tstar = INT_MAX;
+        }
+        w2_bar(1, W);
+        if (ctl.wd) { watchdog = true; break; }
+        ready = 0;
+        vcur = gtot;   // version g0 of the failed window: final and verified
+        continue;
+      }
+      if (ready) ++kv;   // window kv is exact
+
+      int na = 0, J = 0, nwin = 0;
+      if (m > 0) {
+        // ---- phase 2: scan of the accept bits, staging, claim resolution
+        const uint4 wa0 = *reinterpret_cast<const uint4*>(&ctl.wacc[0]);
+        const uint4 wa1 = *reinterpret_cast<const uint4*>(&ctl.wacc[4]);
+        const unsigned wv[8] = {wa0.x, wa0.y, wa0.z, wa0.w, wa1.x, wa1.y, wa1.z, wa1.w};
         int excl = 0;
-        for (int w = 0; w < aw; ++w) {
-          const int c = __popc(ctl.wacc[w]);
+#pragma unroll
+        for (int w = 0; w < 8; ++w) {
+          const int c = w < aw ? __popc(wv[w]) : 0;
           if (w < warp) excl += c;
+          if (w == warp) excl += __popc(wv[w] & ((1u << lane) - 1u));
           na += c;
         }
-        if (active) excl += __popc(ctl.wacc[warp] & ((1u << lane) - 1u));
-        J = __float2int_rz(((float)(inper + na) + 0.5f) * inv_period);          // re-fits inside the window
+        J = __float2int_rz(((float)(inper + na) + 0.5f) * inv_period);               // re-fits inside the window
         const int jt = __float2int_rz(((float)(inper + excl) + 0.5f) * inv_period);  // re-fits before this entry
         cur.meta = (acc ? 1 : 0) | (mine ? 2 : 0) | (jt << 2);
         const bool any_rej = na < m;
+        const int cand = cur.cand;
         if (acc) {  // plane_estimator_.AddPoint terms (ps/plane_estimator.cc:55-65); summed by warp S
           float2* st = reinterpret_cast<float2*>(sm.stage + 10 * ((ninl + excl) & (NS - 1)));
           const V3 p = cur.p;
@@ -509,70 +546,53 @@ __device__ __forceinline__ void planar_grow_wave2(const PlanarArgs& a, const flo
           st[2] = make_float2(p.y * p.z, p.z * p.z);
           st[3] = make_float2(p.x, p.y);
           st[4] = make_float2(p.z, 1.0f);
+          labels[cand] = label_id;                 // :177  (speculative until the window is verified)
+          inliers[base + ninl + excl] = cand;      // :169
+          // only the seed can still have its bit set when it is accepted
+          if (k == 0 && tid == 0) atomicAnd(&sm.mask[cand >> 5], ~(1u << (cand & 31)));
         }
         if (tid < 8) {
           W2Rec& rc = ctl.rec[k & (kW2Rec - 1)];
-          rc.accb[tid] = tid < aw ? ctl.wacc[tid] : 0u;
+          rc.accb[tid] = tid < aw ? wv[tid] : 0u;
           if (tid == 0) {
             rc.head = head; rc.m = m; rc.tailb = tail; rc.ninl0 = ninl; rc.inper0 = inper; rc.g0 = gtot; rc.J = J;
           }
         }
+        PROF_T(x0);
+        PROF_ACC(7, w2, x0);
         if (active) {
-          // ---- AddNeighbors, ps/planar_region.h:229-255: (c-1,r), (c,r-1), (c,r+1), (c+1,r)
-          bool win[4] = {false, false, false, false};
-          bool unres[4] = {false, false, false, false};
-          int nb[4] = {-1, -1, -1, -1};
-          int probe[4] = {0, 0, 0, 0};
-          V3 nx[4];
-          const int cand = cur.cand;
-          if (acc) {
-            int row, col;
-            fast_divmod(fdrows, cand, &col, &row);
-            if (col > 0) nb[0] = cand - rows;
-            if (row > 0) nb[1] = cand - 1;
-            if (row < rows - 1) nb[2] = cand + 1;
-            if (col < cols - 1) nb[3] = cand + rows;
+          // every mask test of the window is done (B1): its rejected cells are unlabeled again
+          if (rej_slot >= 0) atomicOr(&sm.mask[cand >> 5], 1u << (cand & 31));
+          if (any_rej) {
+            // a neighbour that failed the mask test may have been rejected EARLIER in this window
+            if (acc) {
 #pragma unroll
-            for (int s = 0; s < 4; ++s) {
-              if (nb[s] < 0) continue;
-              bool el = mask_test(sm.mask, nb[s]);
-              if (!el && any_rej) {  // rejected earlier in this window?
+              for (int s = 0; s < 4; ++s) {
+                if (!tried[s]) continue;
                 unsigned h = w2_hash(nb[s], kW2Rej - 1);
                 while (true) {
                   const unsigned v = sm.rej[h];
                   if (v == kHashEmpty) break;
                   if ((int)(v >> kW2KeyBits) == nb[s]) {
-                    el = (int)(v & ((1u << kW2KeyBits) - 1u)) < tid;
+                    if ((int)(v & ((1u << kW2KeyBits) - 1u)) < tid) {
+                      unres[s] = true;
+                      nx[s] = ld3(xyz, nb[s]);
+                      probe[s] = (int)w2_hash(nb[s], kW2Hash - 1);
+                      atomicMin(&sm.htab[probe[s]], ((unsigned)nb[s] << kW2KeyBits) | (unsigned)(tid * 4 + s));
+                    }
                     break;
                   }
                   h = (h + 1) & (kW2Rej - 1);
                 }
               }
-              unres[s] = el;
-              if (el) {
-                nx[s] = ld3(xyz, nb[s]);  // in flight during the claims; the winner stores it into the ring
-                probe[s] = (int)w2_hash(nb[s], kW2Hash - 1);
-              }
             }
+            w2_bar(2, aw * 32);  // B3: the late claims are in, every rejected-table lookup is done
+            if (rej_slot >= 0) sm.rej[rej_slot] = kHashEmpty;
           }
-          // the smallest (entry, slot) key per neighbour cell wins the enqueue
+          PROF_T(x1);
+          PROF_ACC(8, x0, x1);
           int round = 0, woff = 0;
           while (true) {
-#pragma unroll
-            for (int s = 0; s < 4; ++s)
-              if (unres[s]) atomicMin(&sm.htab[probe[s]], ((unsigned)nb[s] << kW2KeyBits) | (unsigned)(tid * 4 + s));
-            w2_bar(2, aw * 32);  // B3
-            if (round == 0) {
-              // every mask test and rejected-table lookup of the window is done
-              if (rej_slot >= 0) {
-                atomicOr(&sm.mask[cand >> 5], 1u << (cand & 31));
-                sm.rej[rej_slot] = kHashEmpty;
-              }
-              if (tid == 0) {  // the staged terms and the record are complete: warp S may take the window
-                __threadfence_block();
-                ctl.e_pub = k + 1;
-              }
-            }
             bool left = false;
 #pragma unroll
             for (int s = 0; s < 4; ++s) {
@@ -581,7 +601,7 @@ __device__ __forceinline__ void planar_grow_wave2(const PlanarArgs& a, const flo
                 if ((int)(v >> kW2KeyBits) == nb[s]) {
                   win[s] = (v & ((1u << kW2KeyBits) - 1u)) == (unsigned)(tid * 4 + s);
                   unres[s] = false;
-                } else {
+                } else {  // slot taken by a smaller cell: next slot, one more round
                   probe[s] = (probe[s] + 1) & (kW2Hash - 1);
                   left = true;
                 }
@@ -601,20 +621,31 @@ __device__ __forceinline__ void planar_grow_wave2(const PlanarArgs& a, const flo
             if (tid == 0) ctl.unres[(round + 1) & 1] = 0;
             if (!again) break;
             ++round;
+#pragma unroll
+            for (int s = 0; s < 4; ++s)
+              if (unres[s]) atomicMin(&sm.htab[probe[s]], ((unsigned)nb[s] << kW2KeyBits) | (unsigned)(tid * 4 + s));
+            w2_bar(2, aw * 32);
           }
-          if (tid == 0) { ctl.unres[0] = 0; ctl.unres[1] = 0; }
-          for (int w = 0; w < aw; ++w) {
-            const int c = ctl.wtot[w];
-            if (w < warp) woff += c;
-            nwin += c;
+          if (tid == 0) {
+            ctl.unres[0] = 0; ctl.unres[1] = 0;
+            // the staged terms and the record are complete (B4): warp S may take the window
+            __threadfence_block();
+            ctl.e_pub = k + 1;
           }
-          // ---- commit (speculative until the window is verified; undone from the record otherwise)
-          if (acc) {
-            labels[cand] = label_id;                 // :177
-            inliers[base + ninl + excl] = cand;      // :169
-            // only the seed can still have its bit set when it is accepted
-            if (k == 0 && tid == 0) atomicAnd(&sm.mask[cand >> 5], ~(1u << (cand & 31)));
+          PROF_T(x2);
+          PROF_ACC(9, x1, x2);
+          {
+            const int4 t0 = *reinterpret_cast<const int4*>(&ctl.wtot[0]);
+            const int4 t1 = *reinterpret_cast<const int4*>(&ctl.wtot[4]);
+            const int tv[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
+#pragma unroll
+            for (int w = 0; w < 8; ++w) {
+              const int c = w < aw ? tv[w] : 0;
+              if (w < warp) woff += c;
+              nwin += c;
+            }
           }
+          // ---- phase 3: ordered append of the winners (undone from the record on a roll-back)
           int qp = tail + woff;
 #pragma unroll
           for (int s = 0; s < 4; ++s) {
@@ -636,14 +667,14 @@ __device__ __forceinline__ void planar_grow_wave2(const PlanarArgs& a, const flo
             ctl.rec[k & (kW2Rec - 1)].nwin = nwin;
             bc[1] = nwin;
           }
+          PROF_T(x3);
+          PROF_ACC(10, x2, x3);
         }
-        PROF_T(w3);
-        PROF_ACC(2, w2, w3);
         PROF_CNT(6, 1);
         PROF_CNT(11, m);
         PROF_CNT(12, J);
       }
-      // ---- leader: what the next iteration can do (planes of the oldest unverified window final?)
+      // ---- leader: what the next iteration can do (planes of the oldest open window final?)
       const int k_next = k + (m > 0 ? 1 : 0);
       const int g_next = gtot + J;
       if (tid == 0) {
