@@ -10,8 +10,10 @@
 
 #include "pcseg_host.h"
 
-using mobility::b200::CloudRef;
-using mobility::b200::Float3;
+namespace B = mobility::b200;
+
+using B::CloudRef;
+using B::Float3;
 
 namespace {
 constexpr int kRows = 10, kCols = 10;
@@ -60,17 +62,17 @@ int g_failures = 0;
 }  // namespace
 
 int main() {
-  mobility::b200::Context ctx(0);
+  B::Context ctx(0);
   std::vector<Float3> data = PointCloudData();
   CloudRef<Float3> points(data.data(), kRows, kCols);
   std::vector<int> seeds(kRows * kCols);
   for (int i = 0; i < kRows * kCols; ++i) seeds[kRows * kCols - 1 - i] = i;
 
   // --- ps/clustering_test.cc:115-151 ---
-  std::vector<int> label_store = mobility::PrepareUnlabeledLabels(ctx, points);
+  std::vector<int> label_store = B::PrepareUnlabeledLabels(ctx, points);
   CloudRef<int> labels(label_store.data(), kRows, kCols);
-  std::vector<mobility::ClusterRegion> regions;
-  mobility::SegmentRegions(ctx, points, seeds, mobility::ClusterRegionConfig(), &regions, &labels, 1);
+  std::vector<B::ClusterRegion> regions;
+  B::SegmentRegions(ctx, points, seeds, B::ClusterRegionConfig(), &regions, &labels, 1);
   for (int r = 0; r < kRows; ++r)
     for (int c = 0; c < kCols; ++c) EXPECT(label_store[labels.LinearizeIndex(r, c)] == kExpected[r][c]);
   const size_t sizes[] = {16, 20, 10, 10, 10, 27};
@@ -88,20 +90,20 @@ int main() {
       plane[c * R + r] = {0.03f * c, 0.03f * r, (c < 32 ? 2.0f : 2.6f) + 0.002f * r};
   CloudRef<Float3> pc(plane.data(), R, C), nc(normals.data(), R, C);
   const double sensor[3] = {0, 0, 0};
-  mobility::ComputeNormalsParams np;
+  B::ComputeNormalsParams np;
   np.min_neighbor_distance = 0.02f;
-  mobility::ComputeNormalsOrganized(ctx, sensor, pc, &nc, np);
+  B::ComputeNormalsOrganized(ctx, sensor, pc, &nc, np);
   int finite = 0;
   for (const Float3& n : normals) finite += std::isfinite(n.x) ? 1 : 0;
   EXPECT(finite > R * C / 2);
   EXPECT(normals[10 * R + 10].z < -0.99f);  // oriented towards the sensor at the origin
-  std::vector<int> lab2 = mobility::PrepareUnlabeledLabels(ctx, pc);
+  std::vector<int> lab2 = B::PrepareUnlabeledLabels(ctx, pc);
   CloudRef<int> labels2(lab2.data(), R, C);
-  std::vector<int> seeds2 = mobility::FindSeedPointsFromPlaneSupport(ctx, pc, nc);
+  std::vector<int> seeds2 = B::FindSeedPointsFromPlaneSupport(ctx, pc, nc);
   EXPECT(!seeds2.empty());
-  std::vector<mobility::PlanarRegion> planes;
-  mobility::PlanarRegion::InputData<CloudRef<Float3>, CloudRef<Float3>> in{{0, 0, 0, 1}, pc, nc};
-  mobility::SegmentRegions(ctx, in, seeds2, mobility::PlanarRegionConfig(), &planes, &labels2, 0);
+  std::vector<B::PlanarRegion> planes;
+  B::PlanarRegion::InputData<CloudRef<Float3>, CloudRef<Float3>> in{{0, 0, 0, 1}, pc, nc};
+  B::SegmentRegions(ctx, in, seeds2, B::PlanarRegionConfig(), &planes, &labels2, 0);
   EXPECT(planes.size() == 2);
   for (const auto& p : planes) {
     EXPECT(p.inlier_indices().size() > 1500);
@@ -112,12 +114,64 @@ int main() {
   }
 
   // --- SlidingMeanShift on the same sheet (labels reset) ---
-  std::vector<int> lab3 = mobility::PrepareUnlabeledLabels(ctx, pc);
+  std::vector<int> lab3 = B::PrepareUnlabeledLabels(ctx, pc);
   CloudRef<int> labels3(lab3.data(), R, C);
-  std::vector<mobility::ClusterRegion> ms;
-  mobility::SlidingMeanShift(ctx, pc, mobility::ClusterRegionConfig(), 3, 0, &labels3, &ms);
+  std::vector<B::ClusterRegion> ms;
+  B::SlidingMeanShift(ctx, pc, B::ClusterRegionConfig(), 3, 0, &labels3, &ms);
   EXPECT(!ms.empty());
   for (const auto& m : ms) EXPECT(m.Seed().has_value() && m.inlier_indices().size() >= 7);
+
+  // --- PlaneEstimator: points of the plane z = 1 + 0.1 x (ps/plane_estimator_test.cc:40-74 style) ---
+  {
+    B::PlaneEstimator est(ctx);
+    for (int i = 0; i < 5; ++i)
+      for (int j = 0; j < 5; ++j) est.AddPoint(Float3{0.1f * i, 0.1f * j, 1.0f + 0.01f * i});
+    est.SetNormalOrientation(Float3{0, 0, 1});
+    EXPECT(est.PlaneValid());
+    const float* pl = est.Plane();
+    EXPECT(pl[2] > 0.99f && std::fabs(pl[0] + 0.1f * pl[2]) < 1e-4f && std::fabs(pl[1]) < 1e-4f);
+    const Float3 c = est.Centroid();
+    EXPECT(std::fabs(c.x - 0.2f) < 1e-5f && std::fabs(c.y - 0.2f) < 1e-5f && std::fabs(c.z - 1.02f) < 1e-5f);
+    EXPECT(est.CumulativeWeight() == 25.0f);
+    // the same fit through the batched CSR entry point
+    std::vector<Float3> pts;
+    for (int i = 0; i < 5; ++i)
+      for (int j = 0; j < 5; ++j) pts.push_back(Float3{0.1f * i, 0.1f * j, 1.0f + 0.01f * i});
+    CloudRef<Float3> pcl(pts.data(), 5, 5);
+    std::vector<int> off = {0, 25}, idx(25);
+    for (int i = 0; i < 25; ++i) idx[i] = i;
+    std::vector<float> q;
+    B::FitPlanes(ctx, pcl, off, idx, &q);
+    EXPECT(q.size() == 10 && q[0] == 1.0f && std::fabs(std::fabs(q[7]) - std::fabs(pl[2])) < 1e-6f);
+  }
+  // --- TransformInPlace + DetectedObject geometry gathers ---
+  {
+    std::vector<Float3> tp(plane), tn(normals);
+    CloudRef<Float3> tpc(tp.data(), R, C), tnc(tn.data(), R, C);
+    const double q[4] = {0, 0, 0, 1}, tr[3] = {1.0, -2.0, 0.5};
+    B::TransformInPlace(ctx, q, tr, &tpc, &tnc);
+    EXPECT(std::fabs(tp[5].x - (plane[5].x + 1.0f)) < 1e-6f && std::fabs(tp[5].y - (plane[5].y - 2.0f)) < 1e-6f);
+    if (!planes.empty()) {
+      const B::DetectedObjectGeometry g = B::CreatePlanarDetectedObjectGeometry(ctx, pc, planes[0]);
+      EXPECT(g.points.size() == planes[0].inlier_indices().size());
+      const int i0 = planes[0].inlier_indices()[0];
+      EXPECT(g.points[0].x == plane[i0].x && g.points[0].z == plane[i0].z);
+      EXPECT(g.discontinuous_positions.size() == planes[0].discontinuous_boundary_indices().size());
+    }
+    if (!regions.empty()) {
+      const B::DetectedObjectGeometry g = B::CreateClusterDetectedObjectGeometry(ctx, points, regions[0]);
+      EXPECT(g.points.size() == regions[0].inlier_indices().size());
+    }
+  }
+  // --- the other two seed finders (shape checks; bit parity is pinned by tests/test_estimator_seeds.py) ---
+  {
+    std::vector<int> s_avg = B::FindSeedPointsFromAverageNormals(ctx, pc, nc);
+    EXPECT(!s_avg.empty());
+    std::vector<int> s_last;
+    const float q[4] = {0, 0, 0, 1}, tr[3] = {0, 0, 0};
+    B::FindSeedPointsFromLastPlanarRegions(ctx, pc, nc, planes, q, tr, 0.5f, 0.3f, &s_last);
+    EXPECT(s_last.size() <= planes.size());
+  }
 
   if (g_failures == 0) std::printf("PASS clustering_host_test: %zu clusters, %zu planes, %zu mean-shift regions\n",
                                    regions.size(), planes.size(), ms.size());

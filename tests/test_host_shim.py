@@ -18,6 +18,20 @@ def test_host_shim_compiles_and_links():
     assert "libpcseg_b200.so" in out and "not found" not in out.split("libpcseg_b200.so")[1].split("\n")[0]
 
 
+def test_shim_compiles_beside_the_reference_headers(tmp_path):
+    """ADVICE r1: the mirror lives in mobility::b200, so one translation unit can include it together with
+    the reference's planar_region.h / cluster_region.h / algorithms.h (built against the oracle's shims)."""
+    ref = "/root/reference"
+    if not os.path.isdir(os.path.join(ref, "pointcloud_segmentation")):
+        pytest.skip("reference tree not present on this machine")
+    src = os.path.join(ROOT, "tests", "host", "include_beside_reference.cc")
+    subprocess.check_call([os.environ.get("CXX", "g++"), "-std=c++17", "-fsyntax-only", "-Wno-return-type", "-Wno-unused",
+                           "-I" + os.path.join(ROOT, "include"),
+                           "-I" + os.path.join(ROOT, "x-edr-pointcloud-segmentation_b200", "host"),
+                           "-I" + os.path.join(ROOT, "oracle", "_ref", "patched"),
+                           "-I" + os.path.join(ROOT, "oracle", "shims"), "-I" + ref, src])
+
+
 @pytest.mark.gpu
 def test_host_shim_known_answers():
     assert os.path.exists(BIN), "run `make host_test` (build() does) before the GPU tests"
