@@ -224,6 +224,140 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def run_c5(args, rank, local_rank, world):
+    """--config c5: SlidingMeanShift of ONE 10 M-point cloud.  The only path with a
+    real exchange step: cloud + labels replicated, the seed cells of the iteration
+    phase sharded by contiguous linear-index ranges over the ranks, mode records all-gathered with
+    NCCL, sort + growth once on rank 0.  Total work is fixed: strong scaling."""
+    import ctypes as C
+    import torch
+    import torch.distributed as dist
+    import parallel
+    import pcseg
+    import synth
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    rows, cols, iters = args.c5_rows, args.c5_cols, 5
+    n = rows * cols
+    xyz = synth.c5_full(rows, cols)                   # the same seeded cloud on every rank
+    host_xyz = torch.from_numpy(xyz).pin_memory()
+    host_lab = torch.full((n,), -1, dtype=torch.int32).pin_memory()
+    d_xyz = host_xyz.cuda()
+    d_lab = host_lab.cuda()
+    out_lab = torch.empty((n,), dtype=torch.int32).pin_memory()
+    ctx = pcseg.Context(local_rank)
+    n_seeds = int((~np.isnan(xyz[:, 0])).sum())
+    state = {}
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world > 1:
+            t = torch.tensor([x], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        return x
+
+    def step(e2e):
+        if e2e:   # the cloud and the labels come from (pinned) host memory every step
+            d_xyz.copy_(host_xyz, non_blocking=True)
+            d_lab.copy_(host_lab, non_blocking=True)
+        t0 = time.perf_counter()
+        labels, regs = parallel.sharded_mean_shift(ctx, d_xyz, rows, cols, d_lab, rank, world, iterations=iters,
+                                                   labels_out=out_lab if e2e else None)
+        state["t_ms"] = (time.perf_counter() - t0) * 1e3
+        if rank == 0:
+            state["regions"], state["labels"] = regs, labels
+
+    def timed(e2e, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record()
+        for _ in range(steps):
+            step(e2e)
+        e1.record()
+        e1.synchronize()
+        wall = (time.perf_counter() - t0) * 1e3
+        barrier()
+        # the library calls block the host until their stream is idle, so the events bracket them
+        return max_over_ranks(max(e0.elapsed_time(e1), wall)) / steps
+
+    for _ in range(max(args.warmup, 3)):
+        step(False)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    l0 = ctx.launches
+    ms = timed(False, args.steps)
+    launches = ctx.launches - l0
+    clocks = sampler.stop() if rank == 0 else None
+    step(True)
+    e2e_ms = timed(True, args.steps)
+    # iteration phase alone (modes kernel + all-gather)
+    def modes_fn(b, e, out):
+        ctx._check(ctx.L.pcseg_mean_shift_modes_range(ctx.h, C.c_void_p(d_xyz.data_ptr()), rows, cols,
+                                                      C.c_void_p(d_lab.data_ptr()), iters, b, e, C.c_void_p(out.data_ptr())))
+    it_ms = []
+    for _ in range(5):
+        barrier()
+        t0 = time.perf_counter()
+        parallel.sharded_mean_shift_modes(modes_fn, n, rank, world, device=d_xyz.device)
+        torch.cuda.synchronize()
+        it_ms.append(max_over_ranks((time.perf_counter() - t0) * 1e3))
+    it_ms = statistics.median(it_ms)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    regs = state["regions"]
+    # CPU baseline + parity on a bounded sample: a crop of whole tiles of the same cloud
+    cr, cc = min(rows, 5 * max(rows // 20, 16)), min(cols, 5 * max(cols // 20, 16))
+    crop = np.ascontiguousarray(xyz.reshape(cols, rows, 3)[:cc, :cr].reshape(-1, 3))
+    import oracle
+    t0 = time.perf_counter()
+    o_lab, o_r, _ = oracle.mean_shift(crop, cr, cc, np.full(cr * cc, -1, np.int32), iterations=iters)
+    cpu_s = time.perf_counter() - t0
+    g_lab, g_r = ctx.mean_shift(crop, cr, cc, np.full(cr * cc, -1, np.int32), iterations=iters)
+    same = bool(np.array_equal(o_lab, g_lab)) and o_r.n == g_r.n and \
+        all(np.array_equal(o_r.inliers[k], g_r.inliers[k]) for k in range(min(o_r.n, g_r.n)))
+    peak, peak_kind = measured_peak_gbs()
+    alg = 44.0 * n_seeds   # 12 B point + 4 B label read, 28 B mode record written per seed (SURVEY.md 8d)
+    line = {
+        "metric": METRIC, "value": n / (ms * 1e-3) / 1e6, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic (SURVEY.md 8d C5: blobs on a tiled ground sheet, seeded)",
+        "config": {"workload": "C5: SlidingMeanShift of one %dx%d = %.1f M point cloud, %d iterations; seed cells sharded over "
+                               "the ranks, mode records all-gathered (NCCL), sort + growth on rank 0" % (rows, cols, n / 1e6, iters),
+                   "rows": rows, "cols": cols, "seeds": n_seeds, "regions": int(regs.n),
+                   "l2": "inputs larger than L2 (%.0f MB of points)" % (n * 12 / 1e6)},
+        "iteration_phase_ms": it_ms, "allgather_bytes_per_rank": int(-(-n // world) * 32) if world > 1 else 0,
+        "sort_and_growth_ms": ms - it_ms,
+        "e2e": {"value": n / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": e2e_ms,
+                "h2d_bytes_per_step": int(n * 16) * world, "d2h_bytes_per_step": int(n * 4),
+                "outputs": "label grid to pinned host memory on rank 0 (+ region records)"},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "kernel": "meanshift_modes_kernel (iteration phase incl. the all-gather, max over ranks)",
+                     "achieved": alg / (it_ms * 1e-3) / 1e9, "peak": peak * world, "unit": "GB/s",
+                     "frac": alg / (it_ms * 1e-3) / 1e9 / (peak * world), "traffic": None,
+                     "algorithmic_bytes_per_launch": alg, "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs) x n_gpus",
+                     "note": "bound by L1 gathers (121 window cells x 16 B x 5 iterations per seed), SURVEY.md 8d"},
+        "cpu_baseline": {"value": cr * cc / cpu_s / 1e6, "unit": UNIT, "cores": 1, "kind": "port",
+                         "sample": "a %dx%d crop (25 whole tiles) of the same cloud, single-threaded, %.1f s" % (cr, cc, cpu_s)},
+        "parity": {"crop_labels_and_inlier_lists_equal_oracle": same, "crop_regions": int(o_r.n)},
+        "clocks": clocks, "host_cores": os.cpu_count(),
+    }
+    print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -236,6 +370,11 @@ def main():
     ap.add_argument("--depth", type=int, default=4, choices=[1, 2, 3, 4, 6, 8],
                     help="batch workspaces in flight per GPU (2: pcseg_batch_submit/wait, the copies and the "
                          "normals stage of one batch overlap the growth stages of the other; 1: synchronous)")
+    ap.add_argument("--config", default="c2", choices=["c2", "c5"],
+                    help="c2 (default): the headline frame-batch workload; c5: mean shift of one 10 M-point cloud, "
+                         "seed cells sharded over the ranks + NCCL all-gather (the only collective on the path)")
+    ap.add_argument("--c5-rows", type=int, default=2500)
+    ap.add_argument("--c5-cols", type=int, default=4000)
     ap.add_argument("--secondary", action="store_true",
                     help="instead of the bench line: one-frame timings of configs C3, C4, C5 with the CPU "
                          "checker timed beside them (tools/bench_configs.py)")
@@ -254,6 +393,9 @@ def main():
 
     if args.impl == "reference":
         run_reference(args, rank, world)
+        return
+    if args.config == "c5":
+        run_c5(args, rank, local_rank, world)
         return
 
     import torch

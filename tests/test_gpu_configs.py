@@ -68,10 +68,12 @@ def test_c5_meanshift_10m_points_full(ctx):
     8-way seed-cell sharding of the iteration phase (the multi-GPU partition) against the
     unsharded records."""
     rows, cols = 2500, 4000
-    xyz = synth.c5(rows, cols)
+    xyz = synth.c5_full(rows, cols)
     labels = np.full(rows * cols, -1, np.int32)
     o_lab, o_r, o_modes = oracle.mean_shift(xyz, rows, cols, labels, iterations=5)
     g_lab, g_r = ctx.mean_shift(xyz, rows, cols, labels, iterations=5)
+    assert o_r.n >= 200, "the full-size scene must exercise the sort + suppression loop over many regions"
+    assert g_r.n == o_r.n
     assert np.array_equal(g_lab, o_lab)
     assert_regions_equal(g_r, o_r, "cluster")
     assert np.all(np.abs(g_r.seed_points - o_r.seed_points) <= 1e-4)  # 1e-4 of the 1 m bandwidth

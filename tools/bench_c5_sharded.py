@@ -18,7 +18,7 @@ if world > 1:
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 rows, cols, iters = 2500, 4000, 5
 n = rows * cols
-xyz = synth.c5(rows, cols)                       # same seeded cloud on every rank (replicated)
+xyz = synth.c5_full(rows, cols)                     # same seeded cloud on every rank (replicated)
 d_xyz = torch.from_numpy(xyz).cuda()
 d_lab = torch.full((n,), -1, dtype=torch.int32, device="cuda")
 ctx = pcseg.Context(local)

@@ -72,7 +72,7 @@ out["C4_lidar_2M"] = {"points": N, "gpu_ms": {"cluster": t_c}, "cpu_port_ms": {"
                       "gpu_Mpts_s": N / t_c / 1e3, "cpu_Mpts_s": N / c_c / 1e3}
 # ---- C5 ----
 rows, cols = 2500, 4000
-xyz = synth.c5(rows, cols); N = rows * cols
+xyz = synth.c5_full(rows, cols); N = rows * cols
 d_xyz = dev(xyz); labels = np.full(N, -1, np.int32); d_lab = dev(labels)
 d_modes = torch.empty((N, 8), dtype=torch.float32, device="cuda")
 t_m = gpu_ms(lambda: ctx._check(L.pcseg_mean_shift_modes(ctx.h, VP(d_xyz.data_ptr()), rows, cols, VP(d_lab.data_ptr()), 5,

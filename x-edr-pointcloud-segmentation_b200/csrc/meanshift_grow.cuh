@@ -21,7 +21,14 @@
 //       there is no "in queue" state, quirk Q15);
 //     * < min_region_inliers: labels reset to kUnlabeled (:323-327);
 //     * modes whose first step would find nothing (they sit on an area labelled by an earlier
-//       region) are no-ops and are filtered out per batch of 1024, in parallel.
+//       region) are no-ops and are filtered out in parallel;
+//   ms_filter_kernel     the same two "dead mode" tests (suppressed by an accepted region, empty
+//       first step) for ALL remaining modes on the whole GPU.  Both are monotone (accepted
+//       regions only accumulate; labels only move kUnlabeled -> label across region boundaries),
+//       so a mode found dead now is dead at its turn.  The host alternates filter and growth
+//       launches: the growth CTA stops after kMsRegionsPerRound accepted regions, the filter
+//       clears the flags of the modes those regions killed, and the growth CTA then skips
+//       dead batches with one flag read instead of a serial CTA-wide round per 1024 modes.
 #pragma once
 #include "meanshift.cuh"
 
@@ -69,27 +76,80 @@ struct MsGrowArgs {
   int* inliers;          // N ints
   MsRegionMeta* meta;    // rcap records
   int rcap;
-  int* out;              // [0] = number of regions, [1] = error flags, [2] = total inliers
+  int* out;              // [0] = number of regions, [1] = error flags, [2] = total inliers, [3] = resume position
+  unsigned char* alive;  // n_seeds flags: 0 = known dead (ms_filter_kernel)
 };
 
-constexpr int kMsGrowBlock = 1024;
+constexpr int kMsRegionsPerRound = 8;
 
-__global__ void __launch_bounds__(kMsGrowBlock) ms_grow_kernel(MsGrowArgs a) {
+// Dead-mode tests for the modes [pos0, n_seeds) against the regions [r0, r1) accepted since the
+// last pass and the current labels.
+__global__ void ms_filter_kernel(MsGrowArgs a, int pos0, int r0, int r1) {
+  __shared__ float s_seed[3 * 64];
+  const int rows = a.rows, cols = a.cols;
+  const int W = 2 * a.half_window + 1;
+  const int WW = W * W;
+  for (long long j0 = (long long)pos0 + (long long)blockIdx.x * blockDim.x; j0 < a.n_seeds; j0 += (long long)gridDim.x * blockDim.x) {
+    const long long jl = j0 + threadIdx.x;
+    const int j = (int)(jl < a.n_seeds ? jl : a.n_seeds - 1);
+    bool alive = jl < a.n_seeds && a.alive[j] != 0;
+    const MsSeedRec me = alive ? a.seeds[j] : MsSeedRec{0.0f, 0.0f, 0.0f, 0};
+    for (int rb = r0; rb < r1; rb += 64) {
+      const int cnt = min(64, r1 - rb);
+      __syncthreads();
+      if (threadIdx.x < 3 * cnt) s_seed[threadIdx.x] = a.meta[rb + threadIdx.x / 3].seed[threadIdx.x % 3];
+      __syncthreads();
+      if (alive) {
+        for (int r = 0; r < cnt && alive; ++r) {
+          const V3 d{me.mx - s_seed[3 * r], me.my - s_seed[3 * r + 1], me.mz - s_seed[3 * r + 2]};
+          if ((double)vsqn(d) < 1.0) alive = false;   // kSquaredCentroidDistanceThreshold, :316-318
+        }
+      }
+    }
+    if (alive) {
+      const V3 mm{me.mx, me.my, me.mz};
+      const int crow = me.centre % rows, ccol = me.centre / rows;
+      bool any = false;
+      for (int s = 0; s < WW && !any; ++s) {
+        const int rc = crow + s % W - a.half_window, cc = ccol + s / W - a.half_window;
+        if (cc >= 0 && cc < cols && rc >= 0 && rc < rows) {
+          const int n = cc * rows + rc;
+          if (a.labels[n] == kUnlabeled) {
+            const V3 p = ld3(a.xyz, n);
+            if (!vhasnan(p) && !((double)vsqn(vsub(p, mm)) > 1.0)) any = true;
+          }
+        }
+      }
+      if (!any) alive = false;
+    }
+    if (jl < a.n_seeds && !alive) a.alive[j] = 0;
+  }
+}
+
+constexpr int kMsGrowBlock = 1024;
+constexpr int kMsPairs = 1;   // (entry, slot) pairs per thread and chunk (4: measured slower, the pair chains serialise)
+
+// pos_begin: first mode of this launch; r_filter: regions [0, r_filter) are already applied to
+// the alive flags (only later ones are tested here); base_begin: inliers written so far.
+__global__ void __launch_bounds__(kMsGrowBlock) ms_grow_kernel(MsGrowArgs a, int pos_begin, int r_filter, int base_begin) {
   __shared__ int s_warp[kMsGrowBlock / 32 + 1];
   __shared__ int s_first;
   const int t = threadIdx.x;
   const int rows = a.rows, cols = a.cols;
   const int W = 2 * a.half_window + 1;
   const int WW = W * W;
-  const int CH = kMsGrowBlock / WW;  // queue entries per chunk: one (entry, slot) pair per thread
-  int n_regions = 0, base = 0;
-  for (int pos = 0; pos < a.n_seeds; pos += kMsGrowBlock) {
+  const int CH = kMsGrowBlock * kMsPairs / WW;  // queue entries per chunk: kMsPairs (entry, slot) pairs per thread
+  int n_regions = r_filter, base = base_begin;
+  int pos = pos_begin;
+  for (; pos < a.n_seeds; pos += kMsGrowBlock) {
+    if (n_regions - r_filter >= kMsRegionsPerRound) break;   // let the filter catch up (resume at pos)
     const int j = pos + t;
     MsSeedRec me{0.0f, 0.0f, 0.0f, 0};
-    bool alive = j < a.n_seeds;
+    bool alive = j < a.n_seeds && a.alive[j] != 0;
+    if (!__syncthreads_or(alive)) continue;                  // a dead batch costs one flag read
     if (alive) {
       me = a.seeds[j];
-      for (int r = 0; r < n_regions && alive; ++r) {  // suppression by regions accepted before this batch
+      for (int r = r_filter; r < n_regions && alive; ++r) {  // suppression by regions accepted since the last filter pass
         const float* s = a.meta[r].seed;
         const V3 d{me.mx - s[0], me.my - s[1], me.mz - s[2]};
         if ((double)vsqn(d) < 1.0) alive = false;     // kSquaredCentroidDistanceThreshold, :316-318
@@ -135,40 +195,58 @@ __global__ void __launch_bounds__(kMsGrowBlock) ms_grow_kernel(MsGrowArgs a) {
       while (head < count + 1) {
         const bool first_entry = head == 0;            // first_unexamined_index
         const int m = first_entry ? 1 : min(count + 1 - head, CH);
-        const int e = t / WW, s = t - e * WW;
-        int cell = -1;
-        bool pass = false;
-        if (e < m && t < CH * WW) {
-          const int centre = (head + e == 0) ? cur.centre : a.inliers[base + head + e - 1];
-          const int dc = s / W - a.half_window, dr = s % W - a.half_window;  // delta_col outer, delta_row inner
-          const int crow = centre % rows, ccol = centre / rows;
-          const int rc = crow + dr, cc = ccol + dc;
-          if (!(dc == 0 && dr == 0 && !first_entry) && cc >= 0 && cc < cols && rc >= 0 && rc < rows) {
-            const int n = cc * rows + rc;
-            if (a.labels[n] == kUnlabeled) {
-              const V3 p = ld3(a.xyz, n);
-              if (!vhasnan(p)) {
-                pass = true;
-                if ((double)vsqn(vsub(p, mode)) > 1.0) {  // :185-187
-                  if (first_entry) pass = false;
-                  else if ((double)vsqn(vsub(p, ld3(a.xyz, centre))) > 0.2 * 0.2) pass = false;  // :188-192
-                }
-                if (pass) {
-                  cell = n;
-                  atomicMin(&a.claim[n], t);
+        // thread t tests the (entry, slot) pairs t * kMsPairs + u: contiguous keys per thread, so the
+        // key order of the winners is thread order x local order
+        int cellv[kMsPairs];
+        bool passv[kMsPairs];
+#pragma unroll
+        for (int u = 0; u < kMsPairs; ++u) {
+          const int key = t * kMsPairs + u;
+          const int e = key / WW, s = key - e * WW;
+          cellv[u] = -1;
+          passv[u] = false;
+          if (e < m) {
+            const int centre = (head + e == 0) ? cur.centre : a.inliers[base + head + e - 1];
+            const int dc = s / W - a.half_window, dr = s % W - a.half_window;  // delta_col outer, delta_row inner
+            const int crow = centre % rows, ccol = centre / rows;
+            const int rc = crow + dr, cc = ccol + dc;
+            if (!(dc == 0 && dr == 0 && !first_entry) && cc >= 0 && cc < cols && rc >= 0 && rc < rows) {
+              const int n = cc * rows + rc;
+              if (a.labels[n] == kUnlabeled) {
+                const V3 p = ld3(a.xyz, n);
+                if (!vhasnan(p)) {
+                  bool pass = true;
+                  if ((double)vsqn(vsub(p, mode)) > 1.0) {  // :185-187
+                    if (first_entry) pass = false;
+                    else if ((double)vsqn(vsub(p, ld3(a.xyz, centre))) > 0.2 * 0.2) pass = false;  // :188-192
+                  }
+                  if (pass) {
+                    passv[u] = true;
+                    cellv[u] = n;
+                    atomicMin(&a.claim[n], key);
+                  }
                 }
               }
             }
           }
         }
         __syncthreads();
-        const bool win = pass && __ldcg(&a.claim[cell]) == t;  // claims are L2 atomics: bypass L1
+        int nw = 0;
+#pragma unroll
+        for (int u = 0; u < kMsPairs; ++u) {
+          passv[u] = passv[u] && __ldcg(&a.claim[cellv[u]]) == t * kMsPairs + u;  // claims are L2 atomics: bypass L1
+          nw += passv[u] ? 1 : 0;
+        }
         int total;
-        const int off = block_scan_excl<kMsGrowBlock>(win ? 1 : 0, &total, s_warp);
-        if (win) {
-          a.labels[cell] = label_id;                 // :195-196
-          a.inliers[base + count + off] = cell;      // :194, :197
-          a.claim[cell] = INT_MAX;
+        int off = block_scan_excl<kMsGrowBlock>(nw, &total, s_warp);
+#pragma unroll
+        for (int u = 0; u < kMsPairs; ++u) {
+          if (passv[u]) {
+            a.labels[cellv[u]] = label_id;                 // :195-196
+            a.inliers[base + count + off] = cellv[u];      // :194, :197
+            a.claim[cellv[u]] = INT_MAX;
+            ++off;
+          }
         }
         count += total;
         head += m;
@@ -206,6 +284,7 @@ __global__ void __launch_bounds__(kMsGrowBlock) ms_grow_kernel(MsGrowArgs a) {
   if (t == 0) {
     a.out[0] = n_regions;
     a.out[2] = base;
+    a.out[3] = pos < a.n_seeds ? pos : a.n_seeds;
   }
 }
 

@@ -1309,12 +1309,32 @@ int mean_shift_finish(pcseg_ctx* c, const float* xyz_dev, int rows, int cols, co
   g.n_seeds = S; g.rows = rows; g.cols = cols; g.half_window = cfg->half_search_window;
   g.min_inliers = cfg->min_region_inliers; g.id_offset = id_offset; g.inliers = d_inl.as<int>();
   g.meta = d_meta.as<MsRegionMeta>(); g.rcap = rcap; g.out = d_out.as<int>();
-  ms_grow_kernel<<<1, kMsGrowBlock, 0, c->stream>>>(g);
-  c->launches += 3;
-  CU_TRY(c, cudaGetLastError());
-  int h_out[4];
-  CU_TRY(c, cudaMemcpyAsync(h_out, d_out.p, sizeof(h_out), cudaMemcpyDeviceToHost, c->stream));
-  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  DevBuf d_alive;
+  CU_TRY(c, d_alive.ensure((size_t)S));
+  CU_TRY(c, cudaMemsetAsync(d_alive.p, 1, (size_t)S, c->stream));
+  g.alive = d_alive.as<unsigned char>();
+  c->launches += 2;
+  // growth in rounds (meanshift_grow.cuh): the serial CTA accepts a few regions, the filter kernel
+  // marks the modes they killed on the whole GPU, the CTA resumes behind the last batch it finished
+  int h_out[4] = {0, 0, 0, 0};
+  int pos = 0, n_reg = 0, n_inl = 0, r_applied = 0;
+  while (pos < S) {
+    if (n_reg > r_applied) {
+      const unsigned fgrid = (unsigned)std::min<size_t>(((size_t)(S - pos) + 255) / 256, (size_t)148 * 8);
+      ms_filter_kernel<<<fgrid, 256, 0, c->stream>>>(g, pos, r_applied, n_reg);
+      r_applied = n_reg;
+      ++c->launches;
+    }
+    ms_grow_kernel<<<1, kMsGrowBlock, 0, c->stream>>>(g, pos, r_applied, n_inl);
+    ++c->launches;
+    CU_TRY(c, cudaGetLastError());
+    CU_TRY(c, cudaMemcpyAsync(h_out, d_out.p, sizeof(h_out), cudaMemcpyDeviceToHost, c->stream));
+    CU_TRY(c, cudaStreamSynchronize(c->stream));
+    if (h_out[1]) break;
+    if (h_out[3] <= pos && h_out[0] == n_reg) { c->last_error = "mean-shift growth made no progress"; d_alive.release(); return PCSEG_ERR_CUDA; }
+    pos = h_out[3]; n_reg = h_out[0]; n_inl = h_out[2];
+  }
+  d_alive.release();
   const int R = h_out[0], total = h_out[2];
   std::vector<MsRegionMeta> meta(R);
   res->inlier_indices.resize(total);

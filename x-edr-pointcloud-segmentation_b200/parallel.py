@@ -47,6 +47,10 @@ def sharded_mean_shift_modes(modes_fn, n_cells, rank, world, group=None, device=
     b, e = ranges[rank]
     full = torch.zeros((world * per, MODE_FLOATS), dtype=torch.float32, device=device)
     mine = full[rank * per: rank * per + per]
+    if device is not None and torch.device(device).type == "cuda":
+        # the zero fill runs on torch's stream, the kernel on the library's own stream (which the
+        # call synchronises before it returns): order them explicitly
+        torch.cuda.current_stream().synchronize()
     if e > b:
         modes_fn(b, e, mine[: e - b])
     if world > 1:
@@ -56,7 +60,7 @@ def sharded_mean_shift_modes(modes_fn, n_cells, rank, world, group=None, device=
 
 
 def sharded_mean_shift(ctx, xyz_dev, rows, cols, labels_dev, rank, world, cfg=None, iterations=5,
-                       id_offset=0, sort_mode=0, group=None, grow_on_all_ranks=False):
+                       id_offset=0, sort_mode=0, group=None, grow_on_all_ranks=False, labels_out=None):
     """SlidingMeanShift of one large cloud with the seed cells sharded over the
     ranks.  xyz_dev / labels_dev: torch CUDA tensors (replicated on every rank).
     Returns (labels numpy, regions) on rank 0 (on every rank if
@@ -78,6 +82,7 @@ def sharded_mean_shift(ctx, xyz_dev, rows, cols, labels_dev, rank, world, cfg=No
         return None, None
     modes = modes.contiguous()
     labels = labels_dev.clone()
+    torch.cuda.current_stream().synchronize()   # clone / gather done before the library's stream reads them
     c = cfg if isinstance(cfg, pcseg.ClusterConfig) else pcseg.cluster_config(**(cfg or {}))
     h = C.c_void_p()
     ctx._check(L.pcseg_mean_shift_from_modes(ctx.h, C.c_void_p(xyz_dev.data_ptr()), rows, cols,
@@ -86,4 +91,7 @@ def sharded_mean_shift(ctx, xyz_dev, rows, cols, labels_dev, rank, world, cfg=No
     regs = pcseg._collect(L, h, "meanshift")
     L.pcseg_regions_free(h)
     torch.cuda.synchronize()
+    if labels_out is not None:   # caller's (pinned) host tensor
+        labels_out.copy_(labels)
+        return labels_out.numpy(), regs
     return labels.cpu().numpy(), regs

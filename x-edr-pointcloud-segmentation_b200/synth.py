@@ -175,8 +175,11 @@ def c4(rows=128, cols=16384, seed=3234, n_objects=200):
     return np.ascontiguousarray(p), labels
 
 
-def c5(rows=2500, cols=4000, seed=4234, n_blobs=2000, pitch=0.02, nan_frac=0.10):
-    """Stereo-like grid: Gaussian blobs (sigma 0.15 m) on a ground sheet."""
+def c5(rows=2500, cols=4000, seed=4234, n_blobs=2000, pitch=0.02, nan_frac=0.10, tiles=None):
+    """Stereo-like grid: Gaussian blobs (sigma 0.15 m) on a ground sheet.
+    tiles = (tile_rows, tile_cols, gap): the sheet is cut into tiles separated by `gap` NaN rows /
+    columns (wider than the growth window), so that it is not ONE closure under the 0.2 m neighbour
+    rule of ps/mean_shift_segmentation.h:152-199 and the sort + suppression loop sees many regions."""
     rng = np.random.default_rng(seed + 10)
     z = np.zeros((cols, rows), np.float64)  # [col, row] == column-major
     sig = 0.15
@@ -196,7 +199,18 @@ def c5(rows=2500, cols=4000, seed=4234, n_blobs=2000, pitch=0.02, nan_frac=0.10)
     p = np.stack([x, y, z.reshape(-1)], axis=1).astype(np.float32)
     p[:, 2] += (0.003 * np.random.default_rng(seed).standard_normal(rows * cols)).astype(np.float32)
     p[np.random.default_rng(seed + 1).random(rows * cols) < nan_frac] = NAN
+    if tiles:
+        tr, tc, gap = tiles
+        rr = np.tile(np.arange(rows), cols)
+        cc = np.repeat(np.arange(cols), rows)
+        p[((rr % tr) >= tr - gap) | ((cc % tc) >= tc - gap)] = NAN
     return np.ascontiguousarray(p)
+
+
+def c5_full(rows=2500, cols=4000):
+    """Config C5 at full size: 10 M points, 2 000 blobs, cut into 20 x 20 tiles of
+    125 x 200 cells (2.5 m x 4 m) by 8-cell NaN gaps => several hundred mean-shift regions."""
+    return c5(rows, cols, tiles=(max(rows // 20, 16), max(cols // 20, 16), 8))
 
 
 def clustering_test_cloud():
