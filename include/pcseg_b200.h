@@ -220,6 +220,23 @@ int pcseg_plane_estimators_transform(pcseg_ctx*, float* states, int n, const dou
 int pcseg_plane_estimators_merge(pcseg_ctx*, float* dst_states, const float* src_states, int n,
                                  const double* poses, int pose_per_state);
 
+/* ---- Unorganized clouds (extension; SURVEY.md 8(f) rank 4, BASELINE.json config 4): fixed-radius
+ * Euclidean clustering through a voxel-hash grid (voxel = radius).  The reference has no
+ * unorganized path (its ClusterRegion needs a grid, ps/cluster_region.h:122-150), so the semantics
+ * are defined by this library (csrc/voxel_cluster.cuh) and restated by the CPU oracle:
+ * participating points = labels == kUnlabeled and finite; neighbours = squared distance < radius^2
+ * (fp32, the reduction order of ps/cluster_region.h:94); clusters = connected components with
+ * >= min_region_inliers points; ids = initial_id_offset + rank by smallest member index; inlier
+ * lists ascending.  Result accessors: count, inlier_offsets / inlier_indices, label_ids, centroids
+ * (sum of the member points / count) and bboxes (min xyz, max xyz) -- north_star item (4). ---- */
+typedef struct {
+  float radius;
+  int min_region_inliers;
+} pcseg_voxel_cluster_config;
+int pcseg_cluster_unorganized(pcseg_ctx*, const float* xyz, int n_points,
+                              const pcseg_voxel_cluster_config* cfg, int initial_id_offset,
+                              int* labels, pcseg_regions** out);
+
 /* ---- Batched pipeline (extension: the reference has no batch entry point;
  * a caller looping ComputeNormalsOrganized -> SegmentRegions<PlanarRegion> ->
  * SegmentRegions<ClusterRegion> over independent frames binds this instead).
@@ -376,6 +393,7 @@ const int* pcseg_regions_discontinuous_indices(const pcseg_regions*); /* a set, 
 const int* pcseg_regions_hull_offsets(const pcseg_regions*);          /* n+1 (points) */
 const float* pcseg_regions_hull_points(const pcseg_regions*);         /* xyz */
 const float* pcseg_regions_seed_points(const pcseg_regions*);         /* 3n (mean shift) */
+const float* pcseg_regions_bboxes(const pcseg_regions*);              /* 6n (pcseg_cluster_unorganized) */
 void pcseg_regions_free(pcseg_regions*);
 
 #ifdef __cplusplus

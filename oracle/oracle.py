@@ -181,6 +181,9 @@ def collect_regions(L, prefix, handle, kind):
         r.hull_points = arr("hull_points", 3 * int(r.hull_offsets[-1]), np.float32).reshape(-1, 3)
     if kind == "meanshift":
         r.seed_points = arr("seed_points", 3 * n, np.float32).reshape(n, 3)
+    if kind == "unorganized":
+        r.centroids = arr("centroids", 3 * n, np.float32).reshape(n, 3)
+        r.bboxes = arr("bboxes", 6 * n, np.float32).reshape(n, 6)
     r.inliers = [r.inlier_indices[r.inlier_offsets[i]:r.inlier_offsets[i + 1]] for i in range(n)]
     return r
 
@@ -381,6 +384,23 @@ def mean_shift(xyz, rows, cols, labels, cfg=None, iterations=5, id_offset=0,
     r = collect_regions(L, "oracle_", h, "meanshift")
     L.oracle_regions_free(h)
     return labels, r, modes.reshape(-1, 8)[:nm.value].copy()
+
+
+def cluster_unorganized(xyz, labels, radius=0.5, min_region_inliers=10, id_offset=0):
+    """Voxel-grid Euclidean clustering of an unorganized cloud (extension; csrc/voxel_cluster.cuh)."""
+    L = lib()
+    xyz = _f32(xyz).reshape(-1, 3)
+    lab = _i32(labels).reshape(-1).copy()
+    h = C.c_void_p()
+    L.oracle_cluster_unorganized.restype = C.c_int
+    L.oracle_regions_bboxes.restype = F32P
+    L.oracle_regions_bboxes.argtypes = [C.c_void_p]
+    st = L.oracle_cluster_unorganized(_ptr(xyz, F32P), C.c_int(xyz.shape[0]), C.c_float(radius),
+                                      C.c_int(min_region_inliers), C.c_int(id_offset), _ptr(lab, I32P), C.byref(h))
+    assert st == 0, st
+    r = collect_regions(L, "oracle_", h, "unorganized")
+    L.oracle_regions_free(h)
+    return lab, r
 
 
 def seeds_plane_support(xyz, normals, rows, cols, neighborhood_size=9,

@@ -33,6 +33,7 @@
 #include <queue>
 #include <set>
 #include <utility>
+#include <unordered_map>
 #include <vector>
 
 namespace {
@@ -617,6 +618,7 @@ struct oracle_regions {
   std::vector<int> hull_offsets{0};
   std::vector<float> hull_points;
   std::vector<float> seed_points;
+  std::vector<float> bboxes;
   int count() const { return static_cast<int>(label_ids.size()); }
 };
 
@@ -1204,6 +1206,99 @@ int oracle_segment_cluster(const float* xyz, int rows, int cols,
   return 0;
 }
 
+// Fixed-radius Euclidean clustering of an UNORGANIZED cloud (extension; semantics defined in
+// x-edr-pointcloud-segmentation_b200/csrc/voxel_cluster.cuh).  Plain
+// restatement: voxel buckets in a std::unordered_map, sequential union-find, regions numbered by
+// smallest member index, inlier lists ascending, centroid summed in the documented lane order.
+int oracle_cluster_unorganized(const float* xyz, int n, float radius,
+                               int min_region_inliers, int id_offset,
+                               int* labels, oracle_regions** out) {
+  if (n <= 0 || !(radius > 0.0f) || min_region_inliers < 1) return 2;
+  const float r2 = radius * radius;
+  auto coord = [&](float v) {
+    float q = std::floor(v / radius);
+    q = std::fmin(std::fmax(q, -1048576.0f), 1048575.0f);
+    return static_cast<long long>(q);
+  };
+  auto key = [](long long x, long long y, long long z) {
+    return ((x + 1048576) << 42) | ((y + 1048576) << 21) | (z + 1048576);
+  };
+  std::vector<char> part(n, 0);
+  std::unordered_map<long long, std::vector<int>> grid;
+  for (int i = 0; i < n; ++i) {
+    const float* p = xyz + 3 * static_cast<size_t>(i);
+    if (labels[i] != kUnlabeled || !std::isfinite(p[0]) || !std::isfinite(p[1]) || !std::isfinite(p[2])) continue;
+    part[i] = 1;
+    grid[key(coord(p[0]), coord(p[1]), coord(p[2]))].push_back(i);
+  }
+  std::vector<int> parent(n);
+  for (int i = 0; i < n; ++i) parent[i] = i;
+  auto find = [&](int x) {
+    while (parent[x] != x) { parent[x] = parent[parent[x]]; x = parent[x]; }
+    return x;
+  };
+  for (int i = 0; i < n; ++i) {
+    if (!part[i]) continue;
+    const float* p = xyz + 3 * static_cast<size_t>(i);
+    const long long vx = coord(p[0]), vy = coord(p[1]), vz = coord(p[2]);
+    for (long long dz = -1; dz <= 1; ++dz)
+      for (long long dy = -1; dy <= 1; ++dy)
+        for (long long dx = -1; dx <= 1; ++dx) {
+          const long long nx = vx + dx, ny = vy + dy, nz = vz + dz;
+          if (nx < -1048576 || nx > 1048575 || ny < -1048576 || ny > 1048575 || nz < -1048576 || nz > 1048575) continue;
+          auto it = grid.find(key(nx, ny, nz));
+          if (it == grid.end()) continue;
+          for (int j : it->second) {
+            if (j >= i) continue;
+            const float* q = xyz + 3 * static_cast<size_t>(j);
+            const float d0 = q[0] - p[0], d1 = q[1] - p[1], d2 = q[2] - p[2];
+            if (d0 * d0 + (d1 * d1 + d2 * d2) < r2) {   // ps/cluster_region.h:94 order
+              int a = find(i), b = find(j);
+              if (a != b) { if (a < b) std::swap(a, b); parent[a] = b; }   // root = smallest member
+            }
+          }
+        }
+  }
+  std::vector<int> count(n, 0), root(n, -1);
+  for (int i = 0; i < n; ++i)
+    if (part[i]) { root[i] = find(i); ++count[root[i]]; }
+  auto* res = new oracle_regions();
+  std::vector<int> ordinal(n, -1);
+  int R = 0;
+  for (int i = 0; i < n; ++i)
+    if (part[i] && root[i] == i && count[i] >= min_region_inliers) ordinal[i] = R++;
+  std::vector<std::vector<int>> lists(R);
+  for (int i = 0; i < n; ++i)
+    if (part[i] && ordinal[root[i]] >= 0) {
+      labels[i] = id_offset + ordinal[root[i]];
+      lists[ordinal[root[i]]].push_back(i);
+    }
+  for (int r = 0; r < R; ++r) {
+    const std::vector<int>& l = lists[r];
+    res->inlier_indices.insert(res->inlier_indices.end(), l.begin(), l.end());
+    res->inlier_offsets.push_back(static_cast<int>(res->inlier_indices.size()));
+    res->label_ids.push_back(id_offset + r);
+    double lane[32][3] = {};
+    float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (size_t k = 0; k < l.size(); ++k) {   // lane k % 32 adds its elements in ascending order
+      const float* p = xyz + 3 * static_cast<size_t>(l[k]);
+      for (int c = 0; c < 3; ++c) {
+        lane[k % 32][c] += static_cast<double>(p[c]);
+        mn[c] = std::fmin(mn[c], p[c]);
+        mx[c] = std::fmax(mx[c], p[c]);
+      }
+    }
+    double tot[3] = {0.0, 0.0, 0.0};
+    for (int k = 0; k < 32; ++k)
+      for (int c = 0; c < 3; ++c) tot[c] += lane[k][c];
+    for (int c = 0; c < 3; ++c) res->centroids.push_back(static_cast<float>(tot[c] / static_cast<double>(l.size())));
+    for (int c = 0; c < 3; ++c) res->bboxes.push_back(mn[c]);
+    for (int c = 0; c < 3; ++c) res->bboxes.push_back(mx[c]);
+  }
+  *out = res;
+  return 0;
+}
+
 int oracle_mean_shift(const float* xyz, int rows, int cols,
                       const oracle_cluster_config* cfg, int iterations,
                       int id_offset, int sort_mode, int* labels,
@@ -1543,6 +1638,7 @@ const int* oracle_regions_discontinuous_offsets(const oracle_regions* r) { retur
 const int* oracle_regions_discontinuous_indices(const oracle_regions* r) { return r->disc_indices.data(); }
 const int* oracle_regions_hull_offsets(const oracle_regions* r) { return r->hull_offsets.data(); }
 const float* oracle_regions_hull_points(const oracle_regions* r) { return r->hull_points.data(); }
+const float* oracle_regions_bboxes(const oracle_regions* r) { return r->bboxes.data(); }
 const float* oracle_regions_seed_points(const oracle_regions* r) { return r->seed_points.data(); }
 void oracle_regions_free(oracle_regions* r) { delete r; }
 

@@ -111,6 +111,13 @@ int oracle_segment_cluster(const float* xyz, int rows, int cols,
                            const oracle_cluster_config* cfg, int id_offset,
                            int* labels, oracle_regions** out);
 
+/* Fixed-radius Euclidean clustering of an unorganized cloud through a voxel grid (extension with
+ * library-defined semantics, csrc/voxel_cluster.cuh): connected components of "squared distance <
+ * radius^2" over the unlabeled finite points; regions numbered by smallest member index. */
+int oracle_cluster_unorganized(const float* xyz, int n, float radius,
+                               int min_region_inliers, int id_offset,
+                               int* labels, oracle_regions** out);
+
 /* ps/mean_shift_segmentation.h:207-330.  modes_out (nullable): per seed
  * 8 floats {mode xyz, index row, index col, intensity, valid, cloud index},
  * n_modes = number of seed points (unlabeled & non-NaN), in seed order.
@@ -167,6 +174,7 @@ const int* oracle_regions_discontinuous_indices(const oracle_regions*); /* sorte
 const int* oracle_regions_hull_offsets(const oracle_regions*);     /* n+1, in points */
 const float* oracle_regions_hull_points(const oracle_regions*);    /* xyz */
 const float* oracle_regions_seed_points(const oracle_regions*);    /* 3n (mean shift) */
+const float* oracle_regions_bboxes(const oracle_regions*);         /* 6n (unorganized clustering) */
 void oracle_regions_free(oracle_regions*);
 
 #ifdef __cplusplus

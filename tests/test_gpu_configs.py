@@ -49,16 +49,15 @@ def test_c3_1280x720_indoor_full(ctx):
 
 def test_c4_lidar_2m_points_full(ctx):
     """C4 (reference-parity variant): 128 x 16384 organized lidar sweep = 2 097 152 points,
-    ground pre-masked, Euclidean clustering with h = 2 (fewer objects than SURVEY.md's 200 so
-    that the CPU scene generator stays within seconds; the cloud size is the full one)."""
+    ground pre-masked, 200 boxes, Euclidean clustering with h = 2."""
     rows, cols = 128, 16384
-    xyz, labels = synth.c4(rows=rows, cols=cols, n_objects=24)
+    xyz, labels = synth.c4(rows=rows, cols=cols, n_objects=200)
     assert xyz.shape[0] == 2097152
     seeds = np.arange(rows * cols - 1, -1, -1, dtype=np.int32)
     cfg = dict(squared_distance_threshold=0.25, half_search_window=2, min_region_inliers=10)
     o_lab, o_r = oracle.segment_cluster(xyz, rows, cols, seeds, labels, cfg=oracle.default_cluster_config(**cfg))
     g_lab, g_r = ctx.segment_cluster(xyz, rows, cols, seeds, labels, cfg=cfg)
-    assert o_r.n > 5
+    assert o_r.n > 50
     assert np.array_equal(g_lab, o_lab)
     assert_regions_equal(g_r, o_r, "cluster")
 

@@ -22,6 +22,7 @@
 #include "results_pack.cuh"
 #include "plane_estimator.cuh"
 #include "msort.cuh"
+#include "voxel_cluster.cuh"
 
 using namespace pcseg;
 
@@ -95,6 +96,7 @@ struct pcseg_regions {
   std::vector<int> hull_offsets{0};
   std::vector<float> hull_points;
   std::vector<float> seed_points;
+  std::vector<float> bboxes;   // 6 per region (min xyz, max xyz): pcseg_cluster_unorganized
 };
 
 struct pcseg_batch {
@@ -1437,6 +1439,124 @@ int pcseg_mean_shift(pcseg_ctx* c, const float* xyz, int rows, int cols, const p
   return st;
 }
 
+// ---- unorganized clouds: voxel-hash Euclidean clustering (voxel_cluster.cuh) ----------------------
+int pcseg_cluster_unorganized(pcseg_ctx* c, const float* xyz, int n, const pcseg_voxel_cluster_config* cfg,
+                              int initial_id_offset, int* labels, pcseg_regions** out) {
+  if (!c || !xyz || !cfg || !labels || !out) return PCSEG_ERR_NULL;
+  if (n <= 0) return PCSEG_ERR_DIMS;
+  if (!(cfg->radius > 0.0f) || !(cfg->radius <= FLT_MAX) || cfg->min_region_inliers < 1) return PCSEG_ERR_CONFIG;
+  cudaSetDevice(c->device);
+  cudaStream_t st = c->stream;
+  DevBuf sx, sl;
+  const void* xyz_dev;
+  int rc = to_device(c, xyz, (size_t)n * 3 * sizeof(float), &sx, &xyz_dev);
+  if (rc) return rc;
+  int* lab_dev = labels;
+  if (!is_device_ptr(labels)) {
+    const void* tmp;
+    if ((rc = to_device(c, labels, (size_t)n * sizeof(int), &sl, &tmp))) { sx.release(); return rc; }
+    lab_dev = (int*)sl.p;
+  }
+  size_t cap = 1024;
+  while (cap < 2 * (size_t)n) cap <<= 1;
+  DevBuf d_keys, d_head, d_next, d_slot, d_parent, d_count, d_v, d_incl, d_tiles, d_ord, d_rb, d_rc, d_rr,
+      d_idx[2], d_key, d_hist, d_hincl, d_cen, d_box;
+  DevBuf* all[] = {&sx, &sl, &d_keys, &d_head, &d_next, &d_slot, &d_parent, &d_count, &d_v, &d_incl, &d_tiles, &d_ord,
+                   &d_rb, &d_rc, &d_rr, &d_idx[0], &d_idx[1], &d_key, &d_hist, &d_hincl, &d_cen, &d_box};
+  struct Cleanup { DevBuf** b; int k; ~Cleanup() { for (int i = 0; i < k; ++i) b[i]->release(); } } cleanup{all, (int)(sizeof(all) / sizeof(all[0]))};
+  CU_TRY(c, d_keys.ensure(cap * 8));
+  CU_TRY(c, d_head.ensure(cap * 4));
+  CU_TRY(c, d_next.ensure((size_t)n * 4));
+  CU_TRY(c, d_slot.ensure((size_t)n * 4));
+  CU_TRY(c, d_parent.ensure((size_t)n * 4));
+  CU_TRY(c, d_count.ensure((size_t)n * 4));
+  CU_TRY(c, d_v.ensure((size_t)n * 8));
+  CU_TRY(c, d_incl.ensure((size_t)n * 8));
+  CU_TRY(c, cudaMemsetAsync(d_keys.p, 0xff, cap * 8, st));
+  CU_TRY(c, cudaMemsetAsync(d_head.p, 0xff, cap * 4, st));
+  VoxArgs a;
+  a.xyz = (const float*)xyz_dev; a.labels = lab_dev; a.n = n;
+  a.radius = cfg->radius; a.r2 = cfg->radius * cfg->radius; a.inv_unused = 0.0f;
+  a.min_inliers = cfg->min_region_inliers; a.id_offset = initial_id_offset;
+  a.keys = d_keys.as<unsigned long long>(); a.head = d_head.as<int>(); a.cap_mask = (int)(cap - 1);
+  a.next = d_next.as<int>(); a.slot_of = d_slot.as<int>(); a.parent = d_parent.as<int>(); a.count = d_count.as<int>();
+  const unsigned grid = (unsigned)((n + 255) / 256);
+  vox_insert_kernel<<<grid, 256, 0, st>>>(a);
+  vox_union_kernel<<<grid, 256, 0, st>>>(a);
+  vox_flatten_kernel<<<grid, 256, 0, st>>>(a);
+  vox_rootflag_kernel<<<grid, 256, 0, st>>>(a, d_v.as<unsigned long long>());
+  c->launches += 4;
+  if ((rc = scan64(c, d_v.as<unsigned long long>(), n, d_incl.as<unsigned long long>(), &d_tiles))) return rc;
+  unsigned long long last = 0;
+  CU_TRY(c, cudaMemcpyAsync(&last, d_incl.as<unsigned long long>() + (n - 1), 8, cudaMemcpyDeviceToHost, st));
+  CU_TRY(c, cudaStreamSynchronize(st));
+  const int R = (int)(last & 0xffffffffull), total = (int)(last >> 32);
+  pcseg_regions* res = new pcseg_regions();
+  if (R > 0) {
+    CU_TRY(c, d_ord.ensure((size_t)n * 4));
+    CU_TRY(c, d_rb.ensure((size_t)R * 4));
+    CU_TRY(c, d_rc.ensure((size_t)R * 4));
+    CU_TRY(c, d_rr.ensure((size_t)R * 4));
+    vox_label_kernel<<<grid, 256, 0, st>>>(a, d_incl.as<unsigned long long>(), R, d_ord.as<int>(), d_rb.as<int>(),
+                                           d_rc.as<int>(), d_rr.as<int>());
+    ++c->launches;
+    // inlier lists: stable LSD radix sort of the point indices by region ordinal (points outside every
+    // region carry the ordinal R and end up behind the lists); ascending index inside a region
+    CU_TRY(c, d_idx[0].ensure((size_t)n * 4));
+    CU_TRY(c, d_idx[1].ensure((size_t)n * 4));
+    CU_TRY(c, d_key.ensure((size_t)n));
+    const int n_chunks = (n + kCountChunk - 1) / kCountChunk;
+    const int hn = 256 * n_chunks;
+    CU_TRY(c, d_hist.ensure((size_t)hn * 8));
+    CU_TRY(c, d_hincl.ensure((size_t)hn * 8));
+    const int hb = (n_chunks + kCountWarps - 1) / kCountWarps;
+    vox_iota_kernel<<<grid, 256, 0, st>>>(d_idx[0].as<int>(), n);
+    ++c->launches;
+    int bits = 1;
+    while ((R >> bits) != 0) ++bits;
+    int cur = 0;
+    for (int shift = 0; shift < bits; shift += 8) {
+      vox_digit_kernel<<<grid, 256, 0, st>>>(d_ord.as<int>(), d_idx[cur].as<int>(), n, shift, d_key.as<unsigned char>());
+      msort_hist_kernel<<<hb, 32 * kCountWarps, 0, st>>>(d_key.as<unsigned char>(), n, n_chunks, d_hist.as<unsigned long long>());
+      c->launches += 2;
+      if ((rc = scan64(c, d_hist.as<unsigned long long>(), hn, d_hincl.as<unsigned long long>(), &d_tiles))) { delete res; return rc; }
+      msort_scatter_kernel<<<hb, 32 * kCountWarps, 0, st>>>(d_key.as<unsigned char>(), d_idx[cur].as<int>(), n, n_chunks,
+                                                            d_hist.as<unsigned long long>(), d_hincl.as<unsigned long long>(),
+                                                            d_idx[cur ^ 1].as<int>());
+      ++c->launches;
+      cur ^= 1;
+    }
+    CU_TRY(c, d_cen.ensure((size_t)R * 12));
+    CU_TRY(c, d_box.ensure((size_t)R * 24));
+    vox_stats_kernel<<<(unsigned)(((size_t)R * 32 + 255) / 256), 256, 0, st>>>((const float*)xyz_dev, d_idx[cur].as<int>(),
+                                                                              d_rb.as<int>(), d_rc.as<int>(), R,
+                                                                              d_cen.as<float>(), d_box.as<float>());
+    ++c->launches;
+    if (cudaGetLastError() != cudaSuccess) { delete res; c->last_error = "voxel clustering launch failed"; return PCSEG_ERR_CUDA; }
+    std::vector<int> begin(R), count(R);
+    res->inlier_indices.resize(total);
+    res->centroids.resize(3 * (size_t)R);
+    res->bboxes.resize(6 * (size_t)R);
+    cudaMemcpyAsync(begin.data(), d_rb.p, (size_t)R * 4, cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(count.data(), d_rc.p, (size_t)R * 4, cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(res->inlier_indices.data(), d_idx[cur].p, (size_t)total * 4, cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(res->centroids.data(), d_cen.p, (size_t)R * 12, cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(res->bboxes.data(), d_box.p, (size_t)R * 24, cudaMemcpyDeviceToHost, st);
+    if (cudaStreamSynchronize(st) != cudaSuccess) { delete res; c->last_error = cudaGetErrorString(cudaGetLastError()); return PCSEG_ERR_CUDA; }
+    for (int r = 0; r < R; ++r) {
+      res->inlier_offsets.push_back(begin[r] + count[r]);
+      res->label_ids.push_back(initial_id_offset + r);
+    }
+  }
+  if (lab_dev != labels) {
+    rc = from_device(c, labels, lab_dev, (size_t)n * sizeof(int));
+    if (rc == PCSEG_OK && cudaStreamSynchronize(st) != cudaSuccess) rc = PCSEG_ERR_CUDA;
+    if (rc) { delete res; return rc; }
+  }
+  *out = res;
+  return PCSEG_OK;
+}
+
 // ---- batch pipeline --------------------------------------------------------
 int pcseg_batch_create(pcseg_ctx* c, int n_frames, int rows, int cols, pcseg_batch** out) {
   if (!c || !out) return PCSEG_ERR_NULL;
@@ -1872,6 +1992,7 @@ const int* pcseg_regions_discontinuous_indices(const pcseg_regions* r) { return 
 const int* pcseg_regions_hull_offsets(const pcseg_regions* r) { return r->hull_offsets.data(); }
 const float* pcseg_regions_hull_points(const pcseg_regions* r) { return r->hull_points.data(); }
 const float* pcseg_regions_seed_points(const pcseg_regions* r) { return r->seed_points.data(); }
+const float* pcseg_regions_bboxes(const pcseg_regions* r) { return r->bboxes.data(); }
 void pcseg_regions_free(pcseg_regions* r) { delete r; }
 
 }  // extern "C"

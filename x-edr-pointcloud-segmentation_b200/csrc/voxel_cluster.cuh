@@ -1,0 +1,219 @@
+// voxel_cluster.cuh -- fixed-radius Euclidean clustering of an UNORGANIZED cloud via a voxel-hash
+// grid (BASELINE.json config 4: "unorganized 2M-point synthetic lidar sweep
+// via voxel-hash neighbourhoods + Euclidean clustering into ClusterRegions").
+//
+// The reference has no unorganized path, so the semantics are DEFINED here and
+// restated on the CPU in oracle/pcseg_oracle.cc (oracle_cluster_unorganized):
+//   * a point takes part iff labels[i] == kUnlabeled and its coordinates are finite;
+//   * two such points are neighbours iff ||p - q||^2 < radius^2 in fp32 with the reduction order
+//     of ClusterRegion::CheckInlierAndUpdate, d0^2 + (d1^2 + d2^2) (ps/cluster_region.h:94);
+//   * clusters are the connected components of that graph (a true closure, unlike the FIFO rule
+//     of quirk Q5); components with >= min_region_inliers points become regions, the others stay
+//     kUnlabeled;
+//   * regions are numbered initial_id_offset, +1, ... by ascending SMALLEST MEMBER INDEX, and a
+//     region's inlier list is ascending by index (the deterministic order north_star asks for);
+//   * per region: centroid (double sums in a fixed order, see vox_stats_kernel) and axis-aligned
+//     extent -- north_star item (4).
+// Method: voxel = radius, so every neighbour of a point lies in the 27 voxels around its own.
+// Voxel keys go into an open-addressing hash table (one slot per occupied voxel, CAS on the key);
+// the points of a voxel form a linked list.  Union-find with lock-free hooking towards the
+// SMALLER index (the root of a set is its smallest member, which is exactly the ordering key)
+// and path halving; one pointer-jumping pass flattens it.  Labels, offsets and the sorted inlier
+// lists then come from scans and the stable counting sort of msort.cuh -- no atomics-ordered
+// output anywhere, so the result does not depend on thread scheduling.
+#pragma once
+#include "grow_common.cuh"
+
+namespace pcseg {
+
+constexpr unsigned long long kVoxEmpty = 0xffffffffffffffffull;
+constexpr int kVoxBias = 1 << 20;   // voxel coordinates are clamped to [-2^20, 2^20)
+
+struct VoxArgs {
+  const float* xyz;      // [n][3]
+  int* labels;           // [n] in/out
+  int n;
+  float radius, r2, inv_unused;
+  int min_inliers, id_offset;
+  unsigned long long* keys;  // [cap] voxel key per slot
+  int* head;                 // [cap] first point of the slot's list, -1 = empty
+  int cap_mask;              // cap - 1 (power of two)
+  int* next;                 // [n] next point in the voxel's list
+  int* slot_of;              // [n] slot of the point's voxel, -1 = the point does not take part
+  int* parent;               // [n] union-find
+  int* count;                // [n] members per root
+};
+
+__device__ __forceinline__ unsigned long long vox_key(int vx, int vy, int vz) {
+  return ((unsigned long long)(unsigned)(vx + kVoxBias) << 42) | ((unsigned long long)(unsigned)(vy + kVoxBias) << 21) |
+         (unsigned long long)(unsigned)(vz + kVoxBias);
+}
+__device__ __forceinline__ unsigned vox_hash(unsigned long long k) {
+  k ^= k >> 33; k *= 0xff51afd7ed558ccdull; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ull; k ^= k >> 33;
+  return (unsigned)k;
+}
+// voxel coordinate of one component: floor(v / radius), fp32 division, clamped
+__device__ __forceinline__ int vox_coord(float v, float radius) {
+  const float q = floorf(v / radius);
+  return (int)fminf(fmaxf(q, (float)(-kVoxBias)), (float)(kVoxBias - 1));
+}
+
+// 1: every participating point finds (or claims) the slot of its voxel and links itself into the list
+__global__ void __launch_bounds__(256) vox_insert_kernel(VoxArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.n) return;
+  a.parent[i] = i;
+  a.count[i] = 0;
+  const V3 p = ld3(a.xyz, i);
+  if (a.labels[i] != kUnlabeled || !vfinite(p)) { a.slot_of[i] = -1; return; }
+  const unsigned long long key = vox_key(vox_coord(p.x, a.radius), vox_coord(p.y, a.radius), vox_coord(p.z, a.radius));
+  unsigned s = vox_hash(key) & (unsigned)a.cap_mask;
+  while (true) {
+    const unsigned long long old = atomicCAS(&a.keys[s], kVoxEmpty, key);
+    if (old == kVoxEmpty || old == key) break;
+    s = (s + 1) & (unsigned)a.cap_mask;
+  }
+  a.slot_of[i] = (int)s;
+  a.next[i] = atomicExch(&a.head[s], i);
+}
+
+__device__ __forceinline__ int vox_find(int* parent, int x) {
+  // path halving; parents only ever decrease, so a stale read is still an ancestor
+  while (true) {
+    const int p = *(volatile int*)(parent + x);
+    if (p == x) return x;
+    const int g = *(volatile int*)(parent + p);
+    if (g != p) atomicMin(&parent[x], g);
+    x = p;
+  }
+}
+__device__ __forceinline__ void vox_unite(int* parent, int x, int y) {
+  while (true) {
+    x = vox_find(parent, x);
+    y = vox_find(parent, y);
+    if (x == y) return;
+    if (x < y) { const int t = x; x = y; y = t; }   // hook the larger root under the smaller one
+    const int old = atomicMin(&parent[x], y);
+    if (old == x) return;                            // x was still a root: linked
+    x = old;                                         // somebody hooked x first: go on from there
+  }
+}
+
+// 2: every participating point looks at the 27 voxels around its own and unites with the
+// neighbours of smaller index (each pair is seen once, from its larger end)
+__global__ void __launch_bounds__(256) vox_union_kernel(VoxArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.n || a.slot_of[i] < 0) return;
+  const V3 p = ld3(a.xyz, i);
+  const int vx = vox_coord(p.x, a.radius), vy = vox_coord(p.y, a.radius), vz = vox_coord(p.z, a.radius);
+  for (int dz = -1; dz <= 1; ++dz)
+    for (int dy = -1; dy <= 1; ++dy)
+      for (int dx = -1; dx <= 1; ++dx) {
+        const int nx = vx + dx, ny = vy + dy, nz = vz + dz;
+        if (nx < -kVoxBias || nx >= kVoxBias || ny < -kVoxBias || ny >= kVoxBias || nz < -kVoxBias || nz >= kVoxBias) continue;
+        const unsigned long long key = vox_key(nx, ny, nz);
+        unsigned s = vox_hash(key) & (unsigned)a.cap_mask;
+        int j = -1;
+        while (true) {
+          const unsigned long long k = a.keys[s];
+          if (k == key) { j = a.head[s]; break; }
+          if (k == kVoxEmpty) break;
+          s = (s + 1) & (unsigned)a.cap_mask;
+        }
+        for (; j >= 0; j = a.next[j]) {
+          if (j >= i) continue;
+          const V3 d = vsub(ld3(a.xyz, j), p);
+          if (vsqn(d) < a.r2) vox_unite(a.parent, i, j);
+        }
+      }
+}
+
+// 3: flatten + member counts
+__global__ void __launch_bounds__(256) vox_flatten_kernel(VoxArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.n || a.slot_of[i] < 0) return;
+  const int r = vox_find(a.parent, i);
+  a.parent[i] = r;
+  atomicAdd(&a.count[r], 1);
+}
+
+// 4: packed (is an accepted root, its member count) per point for the scan: low word -> region
+// ordinal, high word -> inlier offset
+__global__ void __launch_bounds__(256) vox_rootflag_kernel(VoxArgs a, unsigned long long* v) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.n) return;
+  const bool root = a.slot_of[i] >= 0 && a.parent[i] == i && a.count[i] >= a.min_inliers;
+  v[i] = root ? (1ull | ((unsigned long long)(unsigned)a.count[i] << 32)) : 0ull;
+}
+
+// 5: labels, per-point region ordinal (n_regions = "none"), per-region records
+__global__ void __launch_bounds__(256) vox_label_kernel(VoxArgs a, const unsigned long long* __restrict__ incl, int n_regions,
+                                                        int* ord, int* reg_begin, int* reg_count, int* reg_root) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.n) return;
+  int o = n_regions;
+  if (a.slot_of[i] >= 0) {
+    const int r = a.parent[i];
+    if (a.count[r] >= a.min_inliers) {
+      o = (int)(incl[r] & 0xffffffffull) - 1;
+      a.labels[i] = a.id_offset + o;
+      if (r == i) {
+        reg_count[o] = a.count[r];
+        reg_begin[o] = (int)(incl[r] >> 32) - a.count[r];
+        reg_root[o] = r;
+      }
+    }
+  }
+  ord[i] = o;
+}
+
+// one byte of the region ordinal of the points in their current order (LSD radix passes of the
+// stable counting sort of msort.cuh)
+__global__ void __launch_bounds__(256) vox_digit_kernel(const int* __restrict__ ord, const int* __restrict__ idx, int n, int shift,
+                                                        unsigned char* key) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n) key[k] = (unsigned char)((ord[idx ? idx[k] : k] >> shift) & 255);
+}
+__global__ void __launch_bounds__(256) vox_iota_kernel(int* idx, int n) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n) idx[k] = k;
+}
+
+// 6: centroid + extent of every region: one warp per region.  Fixed summation order (restated by the
+// oracle): lane l adds the elements l, l + 32, ... of the sorted inlier list in double; the total is
+// lanes 0 .. 31 added in that order; centroid = (float)(total / count).
+__global__ void __launch_bounds__(256) vox_stats_kernel(const float* __restrict__ xyz, const int* __restrict__ inliers,
+                                                        const int* __restrict__ reg_begin, const int* __restrict__ reg_count,
+                                                        int n_regions, float* centroid, float* bbox) {
+  const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (r >= n_regions) return;
+  const int b = reg_begin[r], n = reg_count[r];
+  double sx = 0.0, sy = 0.0, sz = 0.0;
+  float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+  for (int i = lane; i < n; i += 32) {
+    const V3 p = ld3(xyz, inliers[b + i]);
+    sx += (double)p.x; sy += (double)p.y; sz += (double)p.z;
+    mn[0] = fminf(mn[0], p.x); mn[1] = fminf(mn[1], p.y); mn[2] = fminf(mn[2], p.z);
+    mx[0] = fmaxf(mx[0], p.x); mx[1] = fmaxf(mx[1], p.y); mx[2] = fmaxf(mx[2], p.z);
+  }
+  double tx = 0.0, ty = 0.0, tz = 0.0;
+  for (int l = 0; l < 32; ++l) {
+    tx += __shfl_sync(0xffffffffu, sx, l);
+    ty += __shfl_sync(0xffffffffu, sy, l);
+    tz += __shfl_sync(0xffffffffu, sz, l);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      mn[k] = fminf(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
+      mx[k] = fmaxf(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
+    }
+  if (lane == 0) {
+    centroid[3 * r] = (float)(tx / (double)n); centroid[3 * r + 1] = (float)(ty / (double)n); centroid[3 * r + 2] = (float)(tz / (double)n);
+    for (int k = 0; k < 3; ++k) { bbox[6 * r + k] = mn[k]; bbox[6 * r + 3 + k] = mx[k]; }
+  }
+}
+
+}  // namespace pcseg

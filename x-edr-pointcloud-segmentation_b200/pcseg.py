@@ -106,7 +106,7 @@ pcseg_normals_organized pcseg_segment_planar pcseg_segment_cluster
 pcseg_mean_shift_modes pcseg_mean_shift_modes_range pcseg_mean_shift_from_modes
 pcseg_mean_shift pcseg_mean_shift_sort_order pcseg_seeds_plane_support pcseg_seeds_average_normals pcseg_seeds_last_planar_regions
 pcseg_fit_planes pcseg_plane_estimator_replay pcseg_plane_estimators_transform pcseg_plane_estimators_merge
-pcseg_batch_submit_regions pcseg_transform_in_place pcseg_gather_points
+pcseg_batch_submit_regions pcseg_transform_in_place pcseg_gather_points pcseg_cluster_unorganized pcseg_regions_bboxes
 pcseg_batch_create pcseg_batch_destroy pcseg_batch_run pcseg_batch_submit pcseg_batch_wait pcseg_batch_stream pcseg_batch_frame_stats
 pcseg_batch_regions pcseg_batch_stage_times pcseg_batch_profile pcseg_batch_device_labels pcseg_batch_device_normals
 pcseg_regions_count pcseg_regions_inlier_offsets pcseg_regions_inlier_indices
@@ -155,7 +155,7 @@ def lib():
                          ("boundary_indices", I32P),
                          ("discontinuous_offsets", I32P),
                          ("discontinuous_indices", I32P), ("hull_offsets", I32P),
-                         ("hull_points", F32P), ("seed_points", F32P)]:
+                         ("hull_points", F32P), ("seed_points", F32P), ("bboxes", F32P)]:
             f = getattr(L, "pcseg_regions_" + name)
             f.restype = rt
             f.argtypes = [C.c_void_p]
@@ -192,6 +192,9 @@ def _collect(L, handle, kind):
         r.hull_points = arr("hull_points", 3 * int(r.hull_offsets[-1]), np.float32).reshape(-1, 3)
     if kind == "meanshift":
         r.seed_points = arr("seed_points", 3 * n, np.float32).reshape(n, 3)
+    if kind == "unorganized":
+        r.centroids = arr("centroids", 3 * n, np.float32).reshape(n, 3)
+        r.bboxes = arr("bboxes", 6 * n, np.float32).reshape(n, 6)
     r.inliers = [r.inlier_indices[r.inlier_offsets[i]:r.inlier_offsets[i + 1]] for i in range(n)]
     return r
 
@@ -356,6 +359,23 @@ class Context:
         self._check(self.L.pcseg_mean_shift(self.h, _addr(xyz), rows, cols, C.byref(c), iterations,
                                             id_offset, sort_mode, _addr(labels), C.byref(h)))
         r = _collect(self.L, h, "meanshift")
+        self.L.pcseg_regions_free(h)
+        return labels, r
+
+    def cluster_unorganized(self, xyz, labels, radius=0.5, min_region_inliers=10, id_offset=0):
+        """Fixed-radius Euclidean clustering of an unorganized cloud through a voxel-hash grid
+        (pcseg_cluster_unorganized; extension): labels out, regions with
+        inlier lists, centroids and extents."""
+        xyz = _f32(xyz).reshape(-1)
+        labels = _i32(labels).reshape(-1).copy()
+
+        class Cfg(C.Structure):
+            _fields_ = [("radius", C.c_float), ("min_region_inliers", C.c_int)]
+        cfg = Cfg(radius, min_region_inliers)
+        h = C.c_void_p()
+        self._check(self.L.pcseg_cluster_unorganized(self.h, _addr(xyz), labels.size, C.byref(cfg), int(id_offset),
+                                                     _addr(labels), C.byref(h)))
+        r = _collect(self.L, h, "unorganized")
         self.L.pcseg_regions_free(h)
         return labels, r
 

@@ -158,10 +158,19 @@ def c4(rows=128, cols=16384, seed=3234, n_objects=200):
         s = rng.uniform(0.3, 1.5, size=3)
         x, y = r * math.cos(th), r * math.sin(th)
         boxes.append(((x - s[0], y - s[1], 0.0), (x + s[0], y + s[1], 2 * s[2])))
-    chunk = 1 << 18
-    for s0 in range(0, w.shape[0], chunk):
-        sl = slice(s0, s0 + chunk)
-        t[sl] = np.minimum(t[sl], _ray_boxes(o, w[sl], boxes))
+    # a box can only be hit by the azimuth columns its footprint spans (+ a margin): same arithmetic per
+    # (ray, box) pair and same box order as testing every ray against every box, 50x less work
+    daz = 2.0 * math.pi / cols
+    for lo, hi in boxes:
+        ang = [math.atan2(y, x) for x in (lo[0], hi[0]) for y in (lo[1], hi[1])]
+        a0, a1 = min(ang), max(ang)
+        if a1 - a0 > math.pi or (lo[0] <= 0.0 <= hi[0] and lo[1] <= 0.0 <= hi[1]):   # wraps around +-pi (or contains the sensor)
+            c0, c1 = 0, cols
+        else:
+            c0 = max(int((a0 + math.pi) / daz) - 2, 0)
+            c1 = min(int((a1 + math.pi) / daz) + 3, cols)
+        sl = slice(c0 * rows, c1 * rows)
+        t[sl] = np.minimum(t[sl], _ray_boxes(o, w[sl], [(lo, hi)]))
     g = np.random.default_rng(seed).standard_normal(t.shape[0])
     t = t + 0.01 * g
     p = w * t[:, None]
