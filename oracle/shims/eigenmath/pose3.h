@@ -19,8 +19,13 @@ class Pose3 {
   Pose3<U> cast() const { return Pose3<U>(q_.template cast<U>(), t_.template cast<U>()); }
   Vector3<T> operator*(const Vector3<T>& p) const { return q_ * p + t_; }
   Pose3 operator*(const Pose3& o) const { return Pose3(q_ * o.q_, q_ * o.t_ + t_); }
+  // The rotation of a pose is a UNIT quaternion (eigenmath keeps it in an SO3), so its inverse is the
+  // conjugate -- no division by the squared norm.  x_edr_eigenmath is not vendored; the CPU
+  // restatement (pcseg_oracle.cc: PlanarConvexHull) and the CUDA path (make_plane_frame) state the
+  // same choice, and tests/test_gpu_configs.py::test_c3 (33 regions, hull vertex counts) keeps the
+  // three in agreement.
   Pose3 inverse() const {
-    const Quaternion<T> qi = q_.inverse();
+    const Quaternion<T> qi = q_.conjugate();
     return Pose3(qi, -(qi * t_));
   }
  private:

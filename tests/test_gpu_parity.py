@@ -163,8 +163,18 @@ def test_planar_seed_orders(ctx):
     _planar_case(ctx, xyz, rows, cols, np.zeros(0, np.int32))
 
 
-def test_c1_full_pipeline_parity(ctx):
-    """Config C1: 640x480, normals -> planes -> clusters, all stages vs the oracle."""
+@pytest.mark.parametrize("checker", ["port", "reference"])
+def test_c1_full_pipeline_parity(ctx, checker):
+    """Config C1: 640x480, normals -> planes -> clusters, all stages vs the oracle: the CPU
+    restatement and the reference's own sources compiled in place (oracle/_ref)."""
+    import contextlib
+    if checker == "reference" and not oracle.ref_available():
+        pytest.skip("oracle/_ref/libref.so not built on this machine")
+    with (oracle.reference() if checker == "reference" else contextlib.nullcontext()):
+        _c1_full_pipeline(ctx)
+
+
+def _c1_full_pipeline(ctx):
     rows, cols = 480, 640
     xyz = synth.c1()
     g_n = ctx.normals_organized(xyz, rows, cols)

@@ -132,9 +132,12 @@ def test_batch_regions_c2_256_frames(ctx):
     assert res.s.error_flags == 0
     for f in range(F):
         _check_frame(res, f, xyz[f], labels[f], want[f], False)
-    if oracle.ref_available():   # the reference's own sources, first frames
-        for f in (0, 255):
-            _check_frame(res, f, xyz[f], labels[f], _oracle_frame((xyz[f], rows, cols, True)), False)
+    if oracle.ref_available():   # every frame again, against the reference's own sources (oracle/_ref)
+        oracle.lib()
+        with mp.get_context("fork").Pool(min(32, os.cpu_count() or 1)) as pool:
+            want_ref = pool.map(_oracle_frame, [(xyz[i], rows, cols, True) for i in range(F)], chunksize=2)
+        for f in range(F):
+            _check_frame(res, f, xyz[f], labels[f], want_ref[f], False)
     b.close()
 
 

@@ -34,10 +34,18 @@
 
 namespace pcseg {
 
+#ifdef PCSEG_W2_SMALL
+// footprint for three frames per SM (BLOCK 224 at <= 96 registers, ~72 KB of shared memory for C1)
+constexpr int kW2Hash = 2048;    // claim table slots
+constexpr int kW2Rej = 256;      // rejected-cell table slots (<= W rejected entries per window)
+constexpr int kW2MaxJ = 15;      // re-fits per window
+constexpr int kW2Ver = 64;       // plane / request ring (versions in flight <= 4 * kW2MaxJ + 1)
+#else
 constexpr int kW2Hash = 2048;    // claim table slots
 constexpr int kW2Rej = 512;      // rejected-cell table slots
 constexpr int kW2MaxJ = 16;      // re-fits per window
 constexpr int kW2Ver = 128;      // plane / request ring (versions in flight <= 4 * kW2MaxJ + 1)
+#endif
 constexpr int kW2Rec = 4;        // window records (<= 3 in flight)
 constexpr int kW2KeyBits = 10;   // claim key = entry * 4 + slot < 1024  (W <= 256)
 constexpr int kW2MaxCells = 1 << (32 - kW2KeyBits);

@@ -335,14 +335,18 @@ int run_planar(pcseg_batch* b, const float* xyz_dev, const float* normals_dev, c
   if (!force_global && !want_pipe && !want_wave1 && b->N < (size_t)kW2MaxCells) {
     CU_TRY(c, cudaFuncGetAttributes(&fattr, planar_grow_kernel<kWave2Block, 3, false>));
     const size_t st = fattr.sharedSizeBytes;
+#ifdef PCSEG_W2_SMALL
+    const int nstage = 256;
+#else
     const int nstage = 512;
+#endif
     const size_t fixed = (size_t)nstage * 40 + kW2Hash * 4 + kW2Rej * 4 + 16;
     const size_t smem_max = 227 * 1024 - st;
     // as many frames per SM as the mask allows (228 KB per SM, 1 KB reserved per CTA): 3, 2 or 1
     int ring = 0;
     for (int per_sm = 3; per_sm >= 1 && !ring; --per_sm) {
       const size_t lim = per_sm == 1 ? smem_max : (228 * 1024) / per_sm - 1024 - st;
-      for (int r = (per_sm == 3 ? 512 : 2048); r >= 256 && !ring; r /= 2)
+      for (int r = (per_sm == 3 ? 256 : 2048); r >= 256 && !ring; r /= 2)
         if ((size_t)a.mask_words * 4 + (size_t)r * 20 + fixed <= lim) ring = r;
     }
     if (ring) {

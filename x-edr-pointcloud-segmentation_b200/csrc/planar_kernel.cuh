@@ -26,7 +26,10 @@ namespace pcseg {
 #ifdef PLANAR_MAXNREG
 #define PLANAR_REG_ATTR __maxnreg__(PLANAR_MAXNREG)
 #else
-#define PLANAR_REG_ATTR __launch_bounds__(MODE == 1 ? 384 : BLOCK, MODE ? 2 : 1)  // pipeline: register budget of the 12-warp CTA (<= 85) for every warp count
+#ifndef PCSEG_W2_MINB
+#define PCSEG_W2_MINB 2   // frames per SM the register budget of the MODE 3 kernel allows
+#endif
+#define PLANAR_REG_ATTR __launch_bounds__(MODE == 1 ? 384 : BLOCK, MODE == 3 ? PCSEG_W2_MINB : (MODE ? 2 : 1))  // pipeline: register budget of the 12-warp CTA (<= 85) for every warp count
 #endif
 template <int BLOCK, int MODE, bool FUSE>
 __global__ void PLANAR_REG_ATTR planar_grow_kernel(PlanarArgs a, ClusterArgs ca) {
