@@ -1464,9 +1464,10 @@ int pcseg_cluster_unorganized(pcseg_ctx* c, const float* xyz, int n, const pcseg
   size_t cap = 1024;
   while (cap < 2 * (size_t)n) cap <<= 1;
   DevBuf d_keys, d_head, d_next, d_slot, d_parent, d_count, d_v, d_incl, d_tiles, d_ord, d_rb, d_rc, d_rr,
-      d_idx[2], d_key, d_hist, d_hincl, d_cen, d_box;
+      d_idx[2], d_key, d_hist, d_hincl, d_cen, d_box, d_sv, d_sincl, d_cs, d_cb, d_cc;
   DevBuf* all[] = {&sx, &sl, &d_keys, &d_head, &d_next, &d_slot, &d_parent, &d_count, &d_v, &d_incl, &d_tiles, &d_ord,
-                   &d_rb, &d_rc, &d_rr, &d_idx[0], &d_idx[1], &d_key, &d_hist, &d_hincl, &d_cen, &d_box};
+                   &d_rb, &d_rc, &d_rr, &d_idx[0], &d_idx[1], &d_key, &d_hist, &d_hincl, &d_cen, &d_box,
+                   &d_sv, &d_sincl, &d_cs, &d_cb, &d_cc};
   struct Cleanup { DevBuf** b; int k; ~Cleanup() { for (int i = 0; i < k; ++i) b[i]->release(); } } cleanup{all, (int)(sizeof(all) / sizeof(all[0]))};
   CU_TRY(c, d_keys.ensure(cap * 8));
   CU_TRY(c, d_head.ensure(cap * 4));
@@ -1477,19 +1478,40 @@ int pcseg_cluster_unorganized(pcseg_ctx* c, const float* xyz, int n, const pcseg
   CU_TRY(c, d_v.ensure((size_t)n * 8));
   CU_TRY(c, d_incl.ensure((size_t)n * 8));
   CU_TRY(c, cudaMemsetAsync(d_keys.p, 0xff, cap * 8, st));
-  CU_TRY(c, cudaMemsetAsync(d_head.p, 0xff, cap * 4, st));
+  CU_TRY(c, cudaMemsetAsync(d_head.p, 0, cap * 4, st));
   VoxArgs a;
   a.xyz = (const float*)xyz_dev; a.labels = lab_dev; a.n = n;
-  a.radius = cfg->radius; a.r2 = cfg->radius * cfg->radius; a.inv_unused = 0.0f;
+  a.radius = cfg->radius; a.r2 = cfg->radius * cfg->radius; a.cell = 0.57f * cfg->radius;
   a.min_inliers = cfg->min_region_inliers; a.id_offset = initial_id_offset;
   a.keys = d_keys.as<unsigned long long>(); a.head = d_head.as<int>(); a.cap_mask = (int)(cap - 1);
   a.next = d_next.as<int>(); a.slot_of = d_slot.as<int>(); a.parent = d_parent.as<int>(); a.count = d_count.as<int>();
   const unsigned grid = (unsigned)((n + 255) / 256);
   vox_insert_kernel<<<grid, 256, 0, st>>>(a);
-  vox_union_kernel<<<grid, 256, 0, st>>>(a);
+  // cells -> CSR of their points
+  CU_TRY(c, d_sv.ensure(cap * 8));
+  CU_TRY(c, d_sincl.ensure(cap * 8));
+  const unsigned sgrid = (unsigned)((cap + 255) / 256);
+  vox_slotflag_kernel<<<sgrid, 256, 0, st>>>(a, (int)cap, d_sv.as<unsigned long long>());
+  c->launches += 2;
+  if ((rc = scan64(c, d_sv.as<unsigned long long>(), (int)cap, d_sincl.as<unsigned long long>(), &d_tiles))) return rc;
+  unsigned long long slast = 0;
+  CU_TRY(c, cudaMemcpyAsync(&slast, d_sincl.as<unsigned long long>() + (cap - 1), 8, cudaMemcpyDeviceToHost, st));
+  CU_TRY(c, cudaStreamSynchronize(st));
+  const int n_cells = (int)(slast & 0xffffffffull);
+  if (n_cells > 0) {
+    CU_TRY(c, d_cs.ensure((size_t)n_cells * 4));
+    CU_TRY(c, d_cb.ensure((size_t)n_cells * 4));
+    CU_TRY(c, d_cc.ensure((size_t)n_cells * 4));
+    vox_cells_kernel<<<sgrid, 256, 0, st>>>(a, (int)cap, d_sincl.as<unsigned long long>(), d_cs.as<int>(), d_cb.as<int>(), d_cc.as<int>());
+    vox_scatter_kernel<<<grid, 256, 0, st>>>(a, d_sincl.as<unsigned long long>(), d_cb.as<int>());
+    vox_union_cell_kernel<<<grid, 256, 0, st>>>(a, d_sincl.as<unsigned long long>(), d_cb.as<int>());
+    vox_union_pairs_kernel<<<(unsigned)(((size_t)n_cells * 32 + 255) / 256), 256, 0, st>>>(
+        a, d_sincl.as<unsigned long long>(), d_cs.as<int>(), d_cb.as<int>(), d_cc.as<int>(), n_cells);
+    c->launches += 4;
+  }
   vox_flatten_kernel<<<grid, 256, 0, st>>>(a);
   vox_rootflag_kernel<<<grid, 256, 0, st>>>(a, d_v.as<unsigned long long>());
-  c->launches += 4;
+  c->launches += 2;
   if ((rc = scan64(c, d_v.as<unsigned long long>(), n, d_incl.as<unsigned long long>(), &d_tiles))) return rc;
   unsigned long long last = 0;
   CU_TRY(c, cudaMemcpyAsync(&last, d_incl.as<unsigned long long>() + (n - 1), 8, cudaMemcpyDeviceToHost, st));

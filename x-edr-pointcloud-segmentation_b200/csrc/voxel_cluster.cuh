@@ -14,11 +14,18 @@
 //     region's inlier list is ascending by index (the deterministic order north_star asks for);
 //   * per region: centroid (double sums in a fixed order, see vox_stats_kernel) and axis-aligned
 //     extent -- north_star item (4).
-// Method: voxel = radius, so every neighbour of a point lies in the 27 voxels around its own.
-// Voxel keys go into an open-addressing hash table (one slot per occupied voxel, CAS on the key);
-// the points of a voxel form a linked list.  Union-find with lock-free hooking towards the
-// SMALLER index (the root of a set is its smallest member, which is exactly the ordering key)
-// and path halving; one pointer-jumping pass flattens it.  Labels, offsets and the sorted inlier
+// Method: the grid cell is 0.57 * radius, so that a cell's diagonal (0.987 radius) is below the
+// radius: ALL points of a cell are mutual neighbours and are united with the cell's first point
+// without a single distance test, and every neighbour of a point lies within +-2 cells.  (With
+// voxel = radius a 0.5 m voxel of a dense lidar sweep holds thousands of points and the pair
+// tests explode: 3 s for the 2 M-point sweep; this formulation: milliseconds.)  Cell keys go into
+// an open-addressing hash table (one slot per occupied cell, CAS on the key); a scan over the
+// slots turns the per-cell counts into a CSR of the cells' points.  One warp per occupied cell
+// then visits the 62 cells of the upper half-space around it: same component already -> skip;
+// else the pairs are tested 32 at a time until the FIRST pair below the radius unites the two
+// components (exact: components do not depend on which edges are found).  Union-find with
+// lock-free hooking towards the SMALLER index (the root of a set is its smallest member, which
+// is exactly the ordering key) and path halving; one pointer-jumping pass flattens it.  Labels, offsets and the sorted inlier
 // lists then come from scans and the stable counting sort of msort.cuh -- no atomics-ordered
 // output anywhere, so the result does not depend on thread scheduling.
 #pragma once
@@ -33,13 +40,13 @@ struct VoxArgs {
   const float* xyz;      // [n][3]
   int* labels;           // [n] in/out
   int n;
-  float radius, r2, inv_unused;
+  float radius, r2, cell;    // cell = grid cell size (0.57 * radius)
   int min_inliers, id_offset;
   unsigned long long* keys;  // [cap] voxel key per slot
-  int* head;                 // [cap] first point of the slot's list, -1 = empty
+  int* head;                 // [cap] number of points of the slot's cell (0 = empty); then its fill cursor
   int cap_mask;              // cap - 1 (power of two)
-  int* next;                 // [n] next point in the voxel's list
-  int* slot_of;              // [n] slot of the point's voxel, -1 = the point does not take part
+  int* next;                 // [n] cell-major point list (CSR payload)
+  int* slot_of;              // [n] slot of the point's cell, -1 = the point does not take part
   int* parent;               // [n] union-find
   int* count;                // [n] members per root
 };
@@ -66,7 +73,7 @@ __global__ void __launch_bounds__(256) vox_insert_kernel(VoxArgs a) {
   a.count[i] = 0;
   const V3 p = ld3(a.xyz, i);
   if (a.labels[i] != kUnlabeled || !vfinite(p)) { a.slot_of[i] = -1; return; }
-  const unsigned long long key = vox_key(vox_coord(p.x, a.radius), vox_coord(p.y, a.radius), vox_coord(p.z, a.radius));
+  const unsigned long long key = vox_key(vox_coord(p.x, a.cell), vox_coord(p.y, a.cell), vox_coord(p.z, a.cell));
   unsigned s = vox_hash(key) & (unsigned)a.cap_mask;
   while (true) {
     const unsigned long long old = atomicCAS(&a.keys[s], kVoxEmpty, key);
@@ -74,7 +81,39 @@ __global__ void __launch_bounds__(256) vox_insert_kernel(VoxArgs a) {
     s = (s + 1) & (unsigned)a.cap_mask;
   }
   a.slot_of[i] = (int)s;
-  a.next[i] = atomicExch(&a.head[s], i);
+  atomicAdd(&a.head[s], 1);
+}
+
+// per slot: (occupied, point count) packed for the scan: low word -> cell ordinal, high word -> CSR offset
+__global__ void __launch_bounds__(256) vox_slotflag_kernel(VoxArgs a, int cap, unsigned long long* v) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= cap) return;
+  const int c = a.head[s];
+  v[s] = c > 0 ? (1ull | ((unsigned long long)(unsigned)c << 32)) : 0ull;
+}
+// cell records + cursors reset
+__global__ void __launch_bounds__(256) vox_cells_kernel(VoxArgs a, int cap, const unsigned long long* __restrict__ incl,
+                                                        int* cell_slot, int* cell_begin, int* cell_count) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= cap) return;
+  const int c = a.head[s];
+  if (c > 0) {
+    const int o = (int)(incl[s] & 0xffffffffull) - 1;
+    cell_slot[o] = s;
+    cell_count[o] = c;
+    cell_begin[o] = (int)(incl[s] >> 32) - c;
+    a.head[s] = 0;   // becomes the fill cursor of vox_scatter_kernel
+  }
+}
+// CSR payload: the points of every cell (order inside a cell is irrelevant)
+__global__ void __launch_bounds__(256) vox_scatter_kernel(VoxArgs a, const unsigned long long* __restrict__ incl,
+                                                          const int* __restrict__ cell_begin) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.n) return;
+  const int s = a.slot_of[i];
+  if (s < 0) return;
+  const int o = (int)(incl[s] & 0xffffffffull) - 1;
+  a.next[cell_begin[o] + atomicAdd(&a.head[s], 1)] = i;
 }
 
 __device__ __forceinline__ int vox_find(int* parent, int x) {
@@ -99,33 +138,75 @@ __device__ __forceinline__ void vox_unite(int* parent, int x, int y) {
   }
 }
 
-// 2: every participating point looks at the 27 voxels around its own and unites with the
-// neighbours of smaller index (each pair is seen once, from its larger end)
-__global__ void __launch_bounds__(256) vox_union_kernel(VoxArgs a) {
+// 2a: all points of a cell are mutual neighbours (cell diagonal < radius): unite with the cell's first point
+__global__ void __launch_bounds__(256) vox_union_cell_kernel(VoxArgs a, const unsigned long long* __restrict__ incl,
+                                                             const int* __restrict__ cell_begin) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= a.n || a.slot_of[i] < 0) return;
-  const V3 p = ld3(a.xyz, i);
-  const int vx = vox_coord(p.x, a.radius), vy = vox_coord(p.y, a.radius), vz = vox_coord(p.z, a.radius);
-  for (int dz = -1; dz <= 1; ++dz)
-    for (int dy = -1; dy <= 1; ++dy)
-      for (int dx = -1; dx <= 1; ++dx) {
-        const int nx = vx + dx, ny = vy + dy, nz = vz + dz;
-        if (nx < -kVoxBias || nx >= kVoxBias || ny < -kVoxBias || ny >= kVoxBias || nz < -kVoxBias || nz >= kVoxBias) continue;
-        const unsigned long long key = vox_key(nx, ny, nz);
-        unsigned s = vox_hash(key) & (unsigned)a.cap_mask;
-        int j = -1;
-        while (true) {
-          const unsigned long long k = a.keys[s];
-          if (k == key) { j = a.head[s]; break; }
-          if (k == kVoxEmpty) break;
-          s = (s + 1) & (unsigned)a.cap_mask;
+  if (i >= a.n) return;
+  const int s = a.slot_of[i];
+  if (s < 0) return;
+  const int rep = a.next[cell_begin[(int)(incl[s] & 0xffffffffull) - 1]];
+  if (rep != i) vox_unite(a.parent, i, rep);
+}
+
+// 2b: one warp per occupied cell: the 62 cells of the upper half-space within +-2 (each unordered cell pair
+// is visited once); two cells already in one component are skipped, else their point pairs are tested 32 at a
+// time until the first pair below the radius unites the components
+__global__ void __launch_bounds__(256) vox_union_pairs_kernel(VoxArgs a, const unsigned long long* __restrict__ incl,
+                                                              const int* __restrict__ cell_slot, const int* __restrict__ cell_begin,
+                                                              const int* __restrict__ cell_count, int n_cells) {
+  const unsigned FULL = 0xffffffffu;
+  const int ca = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (ca >= n_cells) return;
+  const unsigned long long keyA = a.keys[cell_slot[ca]];
+  const int vx = (int)((keyA >> 42) & 0x1fffff) - kVoxBias, vy = (int)((keyA >> 21) & 0x1fffff) - kVoxBias,
+            vz = (int)(keyA & 0x1fffff) - kVoxBias;
+  const int bA = cell_begin[ca], nA = cell_count[ca];
+  const int repA = a.next[bA];
+  for (int o = 63; o < 125; ++o) {   // offsets (dz, dy, dx) lexicographically after (0, 0, 0)
+    const int dz = o / 25 - 2, dy = (o / 5) % 5 - 2, dx = o % 5 - 2;
+    const int nx = vx + dx, ny = vy + dy, nz = vz + dz;
+    if (nx < -kVoxBias || nx >= kVoxBias || ny < -kVoxBias || ny >= kVoxBias || nz < -kVoxBias || nz >= kVoxBias) continue;
+    int sB = -1;
+    if (lane == 0) {
+      const unsigned long long key = vox_key(nx, ny, nz);
+      unsigned s = vox_hash(key) & (unsigned)a.cap_mask;
+      while (true) {
+        const unsigned long long k = a.keys[s];
+        if (k == key) { sB = (int)s; break; }
+        if (k == kVoxEmpty) break;
+        s = (s + 1) & (unsigned)a.cap_mask;
+      }
+    }
+    sB = __shfl_sync(FULL, sB, 0);
+    if (sB < 0) continue;
+    const int cb = (int)(incl[sB] & 0xffffffffull) - 1;
+    const int bB = cell_begin[cb], nB = cell_count[cb];
+    int same = 0;
+    if (lane == 0) same = vox_find(a.parent, repA) == vox_find(a.parent, a.next[bB]);
+    if (__shfl_sync(FULL, same, 0)) continue;
+    bool done = false;
+    for (int ia = 0; ia < nA && !done; ++ia) {
+      const int pi = a.next[bA + ia];
+      const V3 p = ld3(a.xyz, pi);
+      for (int j0 = 0; j0 < nB && !done; j0 += 32) {
+        const int j = j0 + lane;
+        bool hit = false;
+        int pj = -1;
+        if (j < nB) {
+          pj = a.next[bB + j];
+          hit = vsqn(vsub(ld3(a.xyz, pj), p)) < a.r2;
         }
-        for (; j >= 0; j = a.next[j]) {
-          if (j >= i) continue;
-          const V3 d = vsub(ld3(a.xyz, j), p);
-          if (vsqn(d) < a.r2) vox_unite(a.parent, i, j);
+        const unsigned m = __ballot_sync(FULL, hit);
+        if (m) {
+          if (lane == __ffs(m) - 1) vox_unite(a.parent, pi, pj);
+          done = true;
         }
       }
+    }
+    __syncwarp();
+  }
 }
 
 // 3: flatten + member counts
