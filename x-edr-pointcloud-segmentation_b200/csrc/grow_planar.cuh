@@ -284,6 +284,86 @@ __device__ void trace_boundary(const int* labels, int rows, int cols, int start_
   out->min_y = min_y; out->max_y = max_y; out->err = err;
 }
 
+// The same trace by the whole CTA: the serial walk (thread 0) reads "carries the region label" flags of a
+// 64 x 64 cell tile centred on its position from shared memory; all threads reload the tile (coalesced along
+// the rows) whenever the walk leaves the tile's interior.  Same steps, same output; the dependent label reads
+// of the walk cost a shared-memory access instead of an L2 round trip each.
+constexpr int kTraceTile = 64;
+struct TraceState {
+  int curr_idx, cx, cy, dir, nb, err, found_start, first, done;
+  int min_x, max_x, min_y, max_y, ox, oy;
+};
+template <int BLOCK>
+__device__ __forceinline__ void trace_boundary_tiled(const int* labels, int rows, int cols, int start_idx, int region_label,
+                                                     int* boundary, int cap, TraceResult* out, unsigned char* tile /*[64*64]*/,
+                                                     TraceState* st) {
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    st->curr_idx = start_idx;
+    st->cx = start_idx / rows; st->cy = start_idx % rows;
+    st->dir = initial_predecessor_dir(labels, rows, cols, start_idx, region_label);
+    st->nb = 0; st->err = 0; st->found_start = 0; st->first = -1; st->done = 0;
+    st->min_x = cols; st->max_x = 0; st->min_y = rows; st->max_y = 0;  // ps/planar_region.cc:93-96
+    st->ox = st->cx - kTraceTile / 2; st->oy = st->cy - kTraceTile / 2;
+  }
+  __syncthreads();
+  while (true) {
+    const int ox = st->ox, oy = st->oy;
+    for (int t = tid; t < kTraceTile * kTraceTile; t += BLOCK) {
+      const int x = ox + t / kTraceTile, y = oy + t % kTraceTile;
+      tile[t] = (x >= 0 && x < cols && y >= 0 && y < rows && labels[x * rows + y] == region_label) ? 1 : 0;
+    }
+    __syncthreads();
+    if (tid == 0) {
+      int curr_idx = st->curr_idx, cx = st->cx, cy = st->cy, dir = st->dir, nb = st->nb, err = 0;
+      bool found_start = st->found_start != 0;
+      int first = st->first;
+      int min_x = st->min_x, max_x = st->max_x, min_y = st->min_y, max_y = st->max_y;
+      bool done = false;
+      // all 8 neighbours of (cx, cy) are inside the tile while 1 <= cx - ox <= 62 (same for y)
+      while (cx - ox >= 1 && cx - ox <= kTraceTile - 2 && cy - oy >= 1 && cy - oy <= kTraceTile - 2) {
+        // detail::FindNextBoundaryPointDirection, ps/planar_region.cc:47-65 (out-of-bounds cells hold 0)
+        const unsigned char* c = tile + (cx - ox) * kTraceTile + (cy - oy);
+        unsigned same = 0u;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) same |= (unsigned)c[kDx8[i] * kTraceTile + kDy8[i]] << i;
+        int nd = -1;
+        if (same) {
+          const unsigned sh = (unsigned)(dir + 1) & 7u;
+          const unsigned rot = ((same >> sh) | (same << (8u - sh))) & 0xffu;
+          nd = (int)((sh + (unsigned)__ffs(rot) - 1u) & 7u);
+        }
+        if (nd < 0) { err = kErrTraceCheck; done = true; break; }  // CHECK_GE(new_direction_index, 0)
+        dir = (nd + 4) & 7;
+        curr_idx += kDx8[nd] * rows + kDy8[nd];
+        cx += kDx8[nd];
+        cy += kDy8[nd];
+        if (found_start) {
+          if (curr_idx == first) { done = true; break; }
+          found_start = false;
+        }
+        if (nb >= cap) { err = kErrBoundaryCap; done = true; break; }
+        boundary[nb] = curr_idx;
+        if (nb == 0) first = curr_idx;
+        ++nb;
+        min_x = min(min_x, cx); max_x = max(max_x, cx);
+        min_y = min(min_y, cy); max_y = max(max_y, cy);
+        if (curr_idx == start_idx) found_start = true;
+      }
+      st->curr_idx = curr_idx; st->cx = cx; st->cy = cy; st->dir = dir; st->nb = nb; st->err = err;
+      st->found_start = found_start ? 1 : 0; st->first = first; st->done = done ? 1 : 0;
+      st->min_x = min_x; st->max_x = max_x; st->min_y = min_y; st->max_y = max_y;
+      st->ox = cx - kTraceTile / 2; st->oy = cy - kTraceTile / 2;
+    }
+    __syncthreads();
+    if (st->done) break;
+  }
+  if (tid == 0) {
+    out->nb = st->nb; out->min_x = st->min_x; out->max_x = st->max_x;
+    out->min_y = st->min_y; out->max_y = st->max_y; out->err = st->err;
+  }
+}
+
 // Plane-frame (x, y) of a point as in PlanarConvexHull, ps/algorithms.h:527-538
 // with eigenmath::PoseFromPlane restated (not in the reference tree):
 // rotation = Quaternion::FromTwoVectors(UnitZ, normal), origin = -offset*normal.

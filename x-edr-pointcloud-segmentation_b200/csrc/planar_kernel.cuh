@@ -60,6 +60,8 @@ __global__ void PLANAR_REG_ATTR planar_grow_kernel(PlanarArgs a, ClusterArgs ca)
   __shared__ float s_area;
   __shared__ float s_cross[3 * BLOCK];
   __shared__ double s_ext[4][BLOCK / 32];
+  __shared__ unsigned char s_ttile[MODE >= 2 ? kTraceTile * kTraceTile : 4];
+  __shared__ TraceState s_tstate;
   constexpr bool SMEM = MODE != 0;
 
   PlanarSmem sm;
@@ -231,9 +233,13 @@ __global__ void PLANAR_REG_ATTR planar_grow_kernel(PlanarArgs a, ClusterArgs ca)
       if (start_i < 0) {
         ok = false;  // boundary_indices_ empty -> CheckMinRowsAndCols fails, :205-212
       } else {
-        if (tid == 0)
+        if constexpr (MODE >= 2) {
+          trace_boundary_tiled<BLOCK>(const_cast<const int*>(labels), rows, cols, inliers[base + start_i], label_id,
+                                      boundary + b_total, a.bcap - b_total, &s_trace, s_ttile, &s_tstate);
+        } else if (tid == 0) {
           trace_boundary(const_cast<const int*>(labels), rows, cols, inliers[base + start_i], label_id, boundary + b_total,
                          a.bcap - b_total, &s_trace);
+        }
         __syncthreads();
         nb = s_trace.nb;
         if (s_trace.err) {
