@@ -234,6 +234,38 @@ def test_cluster_parity_noisy_thresholds(ctx):
         assert_regions_equal(g_r, o_r, "cluster")
 
 
+def test_cluster_shared_memory_path(ctx, monkeypatch):
+    """The opt-in shared-memory cluster path (grow_cluster_wave.cuh, PCSEG_CLUSTER_MODE=wave; h == 1) on the
+    reference's golden cloud, on the noisy Q5 case and on a depth frame after the planar stage."""
+    monkeypatch.setenv("PCSEG_CLUSTER_MODE", "wave")
+    test_clustering_golden(ctx)
+    rows, cols = 64, 96
+    rng = np.random.default_rng(11)
+    xyz = np.zeros((rows * cols, 3), np.float32)
+    xyz[:, 0] = np.repeat(0.05 * np.arange(cols), rows)
+    xyz[:, 1] = np.tile(0.05 * np.arange(rows), cols)
+    xyz[:, 2] = 0.08 * rng.standard_normal(rows * cols)
+    xyz[rng.random(rows * cols) < 0.05] = np.nan
+    seeds = rng.permutation(rows * cols).astype(np.int32)
+    labels = np.full(rows * cols, -1, np.int32)
+    labels[rng.random(rows * cols) < 0.03] = -2
+    for thr, mi in ((0.012, 7), (0.02, 1), (0.006, 2)):
+        cfg = dict(squared_distance_threshold=thr, half_search_window=1, min_region_inliers=mi)
+        o_lab, o_r = oracle.segment_cluster(xyz, rows, cols, seeds, labels, cfg=oracle.default_cluster_config(**cfg))
+        g_lab, g_r = ctx.segment_cluster(xyz, rows, cols, seeds, labels, cfg=cfg)
+        assert np.array_equal(g_lab, o_lab), (thr, mi)
+        assert_regions_equal(g_r, o_r, "cluster")
+    rows, cols = 240, 320
+    xyz = _frame(rows, cols, seed=77)
+    nrm = oracle.normals_organized(xyz, rows, cols, params=oracle.default_normals_params(min_neighbor_distance=0.04))
+    alld = np.arange(rows * cols - 1, -1, -1, dtype=np.int32)
+    o_lab, o_r = oracle.segment_planar(xyz, nrm, rows, cols, alld, np.full(rows * cols, -1, np.int32))
+    o_lab2, o_c = oracle.segment_cluster(xyz, rows, cols, alld, o_lab, id_offset=o_r.n)
+    g_lab2, g_c = ctx.segment_cluster(xyz, rows, cols, alld, o_lab, id_offset=o_r.n)
+    assert np.array_equal(g_lab2, o_lab2)
+    assert_regions_equal(g_c, o_c, "cluster")
+
+
 def test_mean_shift_modes_parity(ctx):
     rows, cols = 200, 300
     xyz = synth.c5(rows=rows, cols=cols, n_blobs=40)

@@ -23,6 +23,7 @@
 #include "plane_estimator.cuh"
 #include "msort.cuh"
 #include "voxel_cluster.cuh"
+#include "grow_cluster_wave.cuh"
 
 using namespace pcseg;
 
@@ -420,6 +421,33 @@ int run_cluster(pcseg_batch* b, const float* xyz_dev, const int* seeds_dev, int 
   ClusterArgs a;
   int st = make_cluster_args(b, xyz_dev, seeds_dev, n_seeds, cfg, id_offset, offset_from_planar, &a);
   if (st) return st;
+  // h == 1 with the frame's label mask in shared memory (grow_cluster_wave.cuh): opt-in
+  // (PCSEG_CLUSTER_MODE=wave).  Parity-green, but measured slower than the L2 path on the C2 batch
+  // (6.5 vs 6.0 ms; a 256 k-point floor cluster alone 5.1 vs 3.8 ms): its 256-entry windows are half the
+  // 512-entry steps of cluster_grow_kernel and the 8-neighbour frontier is wide.
+  const char* cmode = getenv("PCSEG_CLUSTER_MODE");
+  if (a.half_window == 1 && b->N < (size_t)kCwMaxCells && cmode && !strcmp(cmode, "wave")) {
+    cudaFuncAttributes fattr;
+    CU_TRY(c, cudaFuncGetAttributes(&fattr, cluster_wave_kernel));
+    const int mask_words = (int)((b->N + 31) / 32);
+    const size_t fixed = (size_t)kCwHash * 4 + kCwRej * 4;
+    const size_t smem_two = (228 * 1024) / 2 - 1024 - fattr.sharedSizeBytes;
+    const size_t smem_max = 227 * 1024 - fattr.sharedSizeBytes;
+    int ring = 2048;
+    while (ring > 256 && (size_t)mask_words * 4 + (size_t)ring * 32 + fixed > smem_two) ring /= 2;
+    if ((size_t)mask_words * 4 + (size_t)ring * 32 + fixed > smem_two) {
+      ring = 2048;
+      while (ring > 256 && (size_t)mask_words * 4 + (size_t)ring * 32 + fixed > smem_max) ring /= 2;
+    }
+    const size_t smem = (size_t)mask_words * 4 + (size_t)ring * 32 + fixed;
+    if (smem <= smem_max) {
+      CU_TRY(c, cudaFuncSetAttribute(cluster_wave_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      cluster_wave_kernel<<<b->n_frames, kCwBlock, smem, stream>>>(a, mask_words, ring);
+      ++c->launches;
+      CU_TRY(c, cudaGetLastError());
+      return PCSEG_OK;
+    }
+  }
   if (a.half_window == 1) cluster_grow_kernel<kClusterBlock, true><<<b->n_frames, kClusterBlock, 0, stream>>>(a);
   else cluster_grow_kernel<kClusterBlock, false><<<b->n_frames, kClusterBlock, 0, stream>>>(a);
   ++c->launches;
