@@ -32,6 +32,10 @@
 #include "grow_planar.cuh"
 #include "grow_planar_smem.cuh"
 
+#ifndef PCSEG_W2_HELPER_NS
+#define PCSEG_W2_HELPER_NS 20   // back-off of the idle warps S and R between polls
+#endif
+
 namespace pcseg {
 
 #ifdef PCSEG_W2_SMALL
@@ -149,7 +153,7 @@ __device__ __noinline__ void w2_warp_S(W2Ctl& ctl, const float* stage, int nstag
     }
     if (ctl.e_pub <= k) {
       if (ctl.done) break;
-      __nanosleep(20);
+      __nanosleep(PCSEG_W2_HELPER_NS);
       continue;
     }
     __threadfence_block();
@@ -212,7 +216,7 @@ __device__ __noinline__ void w2_warp_R(W2Ctl& ctl) {
       // warp S first: it withdraws the requests behind the roll-back point (s_posted) before its ack
       if (ctl.s_ack != e) {
         if (ctl.done) break;
-        __nanosleep(20);
+        __nanosleep(PCSEG_W2_HELPER_NS);
         continue;
       }
       __threadfence_block();
@@ -234,7 +238,7 @@ __device__ __noinline__ void w2_warp_R(W2Ctl& ctl) {
     const int posted = ctl.s_posted;
     if (posted <= g) {
       if (ctl.done) break;
-      __nanosleep(20);
+      __nanosleep(PCSEG_W2_HELPER_NS);
       continue;
     }
     __threadfence_block();
