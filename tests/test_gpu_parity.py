@@ -140,6 +140,39 @@ def test_planar_parity_small(ctx, rows, cols):
     assert regs.n >= 1
 
 
+@pytest.mark.parametrize("mode", ["global", "pipe", "wave1"])
+def test_planar_alternative_paths(ctx, monkeypatch, mode):
+    """The older planar growth paths stay selectable (PCSEG_PLANAR_MODE, read per call): everything through
+    L2 (also the fallback for clouds whose mask does not fit shared memory), the warp-specialised
+    32-entry pipeline of round 1, and the first window-parallel version."""
+    monkeypatch.setenv("PCSEG_PLANAR_MODE", mode)
+    rows, cols = 120, 160
+    xyz = _frame(rows, cols, seed=5, yaw_deg=-8.0)
+    seeds = np.arange(rows * cols - 1, -1, -1, dtype=np.int32)
+    for cfg in (None, dict(plane_model_reestimation_period=7, max_plane_distance=0.02)):
+        _, regs, _ = _planar_case(ctx, xyz, rows, cols, seeds, cfg=cfg, nparams=dict(min_neighbor_distance=0.05))
+        assert regs.n >= 1
+
+
+def test_planar_above_shared_memory_mask(ctx):
+    """A cloud of 2.4 M cells: its 1-bit mask (300 KB) does not fit shared memory, so the planes are grown
+    by the L2 path without any environment override.  Two tilted sheets with a step between them."""
+    rows, cols = 1200, 2000
+    c, r = np.meshgrid(np.arange(cols, dtype=np.float32), np.arange(rows, dtype=np.float32), indexing="ij")
+    z = np.where(c < cols // 2, 2.0, 2.8).astype(np.float32) + 0.0005 * r
+    xyz = np.stack([0.004 * c, 0.004 * r, z], axis=-1).reshape(-1, 3).astype(np.float32)
+    nrm = np.zeros_like(xyz)
+    nrm[:, 2] = -1.0
+    seeds = np.array([10 * rows + 10, (cols - 10) * rows + 10], np.int32)
+    labels = np.full(rows * cols, -1, np.int32)
+    cfg = dict(plane_model_reestimation_period=200)
+    o_lab, o_r = oracle.segment_planar(xyz, nrm, rows, cols, seeds, labels, cfg=oracle.default_planar_config(**cfg))
+    g_lab, g_r = ctx.segment_planar(xyz, nrm, rows, cols, seeds, labels, cfg=cfg)
+    assert o_r.n == 2
+    assert np.array_equal(g_lab, o_lab)
+    assert_regions_equal(g_r, o_r, "planar")
+
+
 def test_planar_parity_configs(ctx):
     rows, cols = 120, 160
     xyz = _frame(rows, cols, seed=77, yaw_deg=12.0)
@@ -226,7 +259,7 @@ def test_cluster_parity_noisy_thresholds(ctx):
     seeds = rng.permutation(rows * cols).astype(np.int32)
     labels = np.full(rows * cols, -1, np.int32)
     labels[rng.random(rows * cols) < 0.03] = -2
-    for h, thr, mi in ((1, 0.012, 7), (2, 0.02, 3), (3, 0.008, 1)):
+    for h, thr, mi in ((1, 0.012, 7), (2, 0.02, 3), (3, 0.008, 1), (4, 0.03, 2), (5, 0.012, 4), (7, 0.02, 1)):
         cfg = dict(squared_distance_threshold=thr, half_search_window=h, min_region_inliers=mi)
         o_lab, o_r = oracle.segment_cluster(xyz, rows, cols, seeds, labels, cfg=oracle.default_cluster_config(**cfg))
         g_lab, g_r = ctx.segment_cluster(xyz, rows, cols, seeds, labels, cfg=cfg)

@@ -21,7 +21,7 @@ struct ClusterArgs {
   int n_seeds;
   int min_inliers;
   float sq_thr;
-  int half_window;    // <= 3
+  int half_window;    // <= 7 (224 window slots in four 64-bit masks)
   int id_offset;      // used when id_offset_from_planar == 0
   int id_offset_from_planar;  // 1: offset = stats[f].n_planar
   int* queue;         // [F][qcap][2]
@@ -38,7 +38,8 @@ struct ClusterArgs {
 // stage, by planar_grow_kernel (a frame's stages are sequential, different
 // frames are independent: fusing removes the batch-wide barrier between them).
 // H1 = true: instantiation for half_search_window == 1 (the default; 8 neighbours, lean register
-// allocation so that two CTAs share an SM); H1 = false: any window up to h = 3.
+// allocation so that two CTAs share an SM); H1 = false: any window up to h = 7 (the slot masks are
+// kClW 64-bit words; claim key = thread * 256 + slot).
 template <int BLOCK, bool H1>
 __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, int id_offset, int* s_warp) {
   const int tid = threadIdx.x;
@@ -119,7 +120,11 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
       // AddNeighbors, ps/cluster_region.h:122-150: delta_col outer, delta_row inner.
       // All label probes of an entry are issued before the first one is used (one memory
       // round trip instead of one per neighbour); same for the claim read-back below.
-      unsigned long long el = 0ull;
+      constexpr int kClW = H1 ? 1 : 4;             // 64-bit words of the slot masks
+      constexpr int kKeyStride = H1 ? 64 : 256;   // claim key = tid * kKeyStride + slot
+      unsigned long long el[kClW];
+#pragma unroll
+      for (int w = 0; w < kClW; ++w) el[w] = 0ull;
       const int row = cand % rows, col = cand / rows;
       if (acc) {
         if (H1) {
@@ -135,30 +140,38 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
 #pragma unroll
           for (int s = 0; s < 8; ++s) {
             if (nn[s] >= 0 && (L[s] == kUnlabeled || (L[s] <= kRejBase && (kRejBase - L[s]) < tid))) {
-              el |= 1ull << s;
-              atomicMin(claim + nn[s], tid * 64 + s);
+              el[0] |= 1ull << s;
+              atomicMin(claim + nn[s], tid * kKeyStride + s);
             }
           }
         } else {
           // window slots in groups of kG: the label probes of a group are in flight together
-          constexpr int kG = 12;
+          constexpr int kG = 16;
           const int nslots = side * side - 1;
-          for (int s0 = 0; s0 < nslots; s0 += kG) {
-            int L[kG], nn[kG];
 #pragma unroll
-            for (int k = 0; k < kG; ++k) {
-              const int sl = s0 + k;
-              const int cell = sl + (sl >= (side * side) / 2 ? 1 : 0);  // skip the centre
-              const int cc = col + cell / side - h, rc = row + cell % side - h;
-              const bool in = sl < nslots && cc >= 0 && cc < cols && rc >= 0 && rc < rows;
-              nn[k] = in ? cc * rows + rc : -1;
-              L[k] = in ? labels[nn[k]] : 0;
-            }
+          for (int w = 0; w < kClW; ++w) {
+            if (w * 64 < nslots) {
+#pragma unroll 1
+              for (int g0 = 0; g0 < 64; g0 += kG) {
+                const int s0 = w * 64 + g0;
+                if (s0 >= nslots) break;
+                int L[kG], nn[kG];
 #pragma unroll
-            for (int k = 0; k < kG; ++k) {
-              if (nn[k] >= 0 && (L[k] == kUnlabeled || (L[k] <= kRejBase && (kRejBase - L[k]) < tid))) {
-                el |= 1ull << (s0 + k);
-                atomicMin(claim + nn[k], tid * 64 + s0 + k);
+                for (int k = 0; k < kG; ++k) {
+                  const int sl = s0 + k;
+                  const int cell = sl + (sl >= (side * side) / 2 ? 1 : 0);  // skip the centre
+                  const int cc = col + cell / side - h, rc = row + cell % side - h;
+                  const bool in = sl < nslots && cc >= 0 && cc < cols && rc >= 0 && rc < rows;
+                  nn[k] = in ? cc * rows + rc : -1;
+                  L[k] = in ? labels[nn[k]] : 0;
+                }
+#pragma unroll
+                for (int k = 0; k < kG; ++k) {
+                  if (nn[k] >= 0 && (L[k] == kUnlabeled || (L[k] <= kRejBase && (kRejBase - L[k]) < tid))) {
+                    el[w] |= 1ull << (g0 + k);
+                    atomicMin(claim + nn[k], tid * kKeyStride + s0 + k);
+                  }
+                }
               }
             }
           }
@@ -166,7 +179,9 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
       }
       __syncthreads();
       if (mine && !acc) labels[cand] = kUnlabeled;  // ps/cluster_region.h:105
-      unsigned long long win = 0ull;
+      unsigned long long win[kClW];
+#pragma unroll
+      for (int w = 0; w < kClW; ++w) win[w] = 0ull;
       if (acc) {
         if (H1) {
           int cv[8];
@@ -174,51 +189,61 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
           for (int s = 0; s < 8; ++s) {
             const int cell = s + (s >= 4 ? 1 : 0);
             const int n = (col + cell / 3 - 1) * rows + (row + cell % 3 - 1);
-            cv[s] = ((el >> s) & 1ull) ? vclaim[n] : -1;
+            cv[s] = ((el[0] >> s) & 1ull) ? vclaim[n] : -1;
           }
 #pragma unroll
           for (int s = 0; s < 8; ++s)
-            if (cv[s] == tid * 64 + s) win |= 1ull << s;
+            if (cv[s] == tid * kKeyStride + s) win[0] |= 1ull << s;
         } else {
-          unsigned long long e = el;
-          while (e) {  // claim read-back, 8 claimed slots per round trip
-            int ss[8], cv[8];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-              ss[k] = -1;
-              if (e) {
-                ss[k] = __ffsll((long long)e) - 1;
-                e &= e - 1;
+          for (int w = 0; w < kClW; ++w) {
+            unsigned long long e = el[w];
+            while (e) {  // claim read-back, 8 claimed slots per round trip
+              int ss[8], cv[8];
+#pragma unroll
+              for (int k = 0; k < 8; ++k) {
+                ss[k] = -1;
+                if (e) {
+                  ss[k] = w * 64 + __ffsll((long long)e) - 1;
+                  e &= e - 1;
+                }
               }
-            }
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-              cv[k] = -1;
-              if (ss[k] >= 0) {
-                const int cell = ss[k] + (ss[k] >= (side * side) / 2 ? 1 : 0);  // skip the centre
-                cv[k] = vclaim[(col + cell / side - h) * rows + (row + cell % side - h)];
+              for (int k = 0; k < 8; ++k) {
+                cv[k] = -1;
+                if (ss[k] >= 0) {
+                  const int cell = ss[k] + (ss[k] >= (side * side) / 2 ? 1 : 0);  // skip the centre
+                  cv[k] = vclaim[(col + cell / side - h) * rows + (row + cell % side - h)];
+                }
               }
-            }
 #pragma unroll
-            for (int k = 0; k < 8; ++k)
-              if (ss[k] >= 0 && cv[k] == tid * 64 + ss[k]) win |= 1ull << ss[k];
+              for (int k = 0; k < 8; ++k)
+                if (ss[k] >= 0 && cv[k] == tid * kKeyStride + ss[k]) win[w] |= 1ull << (ss[k] - w * 64);
+            }
           }
         }
       }
       int nwin;
-      int off = block_scan_excl<BLOCK>(__popcll(win), &nwin, s_warp);  // syncs inside
-      while (win) {
-        const int s = __ffsll((long long)win) - 1;
-        win &= win - 1;
-        const int cell = s + (s >= (side * side) / 2 ? 1 : 0);
-        const int dc = cell / side - h, dr = cell % side - h;
-        const int n = (col + dc) * rows + (row + dr);
-        const int qi = (tail + off) & (a.qcap - 1);
-        queue[2 * qi] = cand;
-        queue[2 * qi + 1] = n;
-        labels[n] = kAlreadyInQueue;
-        claim[n] = INT_MAX;
-        ++off;
+      int nmine = 0;
+#pragma unroll
+      for (int w = 0; w < kClW; ++w) nmine += __popcll(win[w]);
+      int off = block_scan_excl<BLOCK>(nmine, &nwin, s_warp);  // syncs inside
+#pragma unroll
+      for (int w = 0; w < kClW; ++w) {
+        unsigned long long ww = win[w];
+        while (ww) {
+          const int s = w * 64 + __ffsll((long long)ww) - 1;
+          ww &= ww - 1;
+          const int cell = s + (s >= (side * side) / 2 ? 1 : 0);
+          const int dc = cell / side - h, dr = cell % side - h;
+          const int n = (col + dc) * rows + (row + dr);
+          const int qi = (tail + off) & (a.qcap - 1);
+          queue[2 * qi] = cand;
+          queue[2 * qi + 1] = n;
+          labels[n] = kAlreadyInQueue;
+          claim[n] = INT_MAX;
+          ++off;
+        }
       }
       __syncthreads();
       head += m;

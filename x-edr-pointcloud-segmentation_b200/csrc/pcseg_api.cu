@@ -206,7 +206,7 @@ int planar_region_bound(const pcseg_batch* b, const pcseg_planar_config* cfg) {
 }
 int check_cluster_cfg(const pcseg_cluster_config* cfg) {
   if (cfg->min_region_inliers < 1 || cfg->half_search_window < 0) return PCSEG_ERR_CONFIG;
-  if (cfg->half_search_window > 3) return PCSEG_ERR_UNSUPPORTED;
+  if (cfg->half_search_window > 7) return PCSEG_ERR_UNSUPPORTED;   // 224 window slots; the reference's default is 1
   return PCSEG_OK;
 }
 
