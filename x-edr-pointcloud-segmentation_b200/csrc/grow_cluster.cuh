@@ -33,6 +33,24 @@ struct ClusterArgs {
   FrameStats* stats;  // [F]
 };
 
+// One CTA's share of a SINGLE large frame (cluster_band_kernel): a band of consecutive columns that no
+// window of the growth can leave, because at least `half_window` columns without any unlabeled finite
+// cell separate it from the next band (cells there are labelled / masked, or not finite -- a non-finite
+// cell can be enqueued and is always rejected, so it carries nothing across).  With the seeds consumed in
+// the all-descending list (consumed back to front = ascending indices) the reference finishes every region
+// of a lower band before it touches a higher one, so the bands are grown concurrently and only the region ids are assigned afterwards, by band order
+// (cluster_band_merge_kernel).  on == 0: the whole frame (the batched path).
+struct ClusterBand {
+  int on;
+  int c_begin, c_end;   // columns [c_begin, c_end)
+  int* queue;           // [qcap][2], qcap a power of two >= the band's cell count
+  int qcap;
+  int inl_base;         // the band's slice of the frame's inlier buffer starts here (= c_begin * rows)
+  ClusterMeta* meta;    // the band's slice of the temporary region table
+  int rcap;
+  int* out;             // {regions, inliers, error flags, steps}
+};
+
 // All cluster regions of frame f, grown by the calling CTA (every thread of the
 // CTA must call).  Used by cluster_grow_kernel and, fused behind a frame's planar
 // stage, by planar_grow_kernel (a frame's stages are sequential, different
@@ -41,22 +59,28 @@ struct ClusterArgs {
 // allocation so that two CTAs share an SM); H1 = false: any window up to h = 7 (the slot masks are
 // kClW 64-bit words; claim key = thread * 256 + slot).
 template <int BLOCK, bool H1>
-__device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, int id_offset, int* s_warp) {
+__device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, int id_offset, int* s_warp,
+                                                   const ClusterBand band = ClusterBand{0, 0, 0, nullptr, 0, 0, nullptr, 0, nullptr}) {
   const int tid = threadIdx.x;
   const int rows = a.rows, cols = a.cols;
   const int N = rows * cols;
   const float* __restrict__ xyz = a.xyz + (size_t)f * N * 3;
   volatile int* labels = a.labels + (size_t)f * N;
-  volatile int* queue = a.queue + (size_t)f * a.qcap * 2;
+  volatile int* queue = band.on ? band.queue : a.queue + (size_t)f * a.qcap * 2;
+  const int qmask = (band.on ? band.qcap : a.qcap) - 1;
   int* claim = a.claim + (size_t)f * N;
   volatile int* vclaim = claim;
   int* inliers = a.inliers + (size_t)f * N;
-  ClusterMeta* meta = a.meta + (size_t)f * a.rcap;
+  ClusterMeta* meta = band.on ? band.meta : a.meta + (size_t)f * a.rcap;
+  const int rcap = band.on ? band.rcap : a.rcap;
   const int h = H1 ? 1 : a.half_window;
   const int side = 2 * h + 1;
 
-  int seed_pos = a.n_seeds;  // seeds are consumed back to front
-  int nreg = 0, inl_total = 0, err = 0, steps = 0;
+  // seeds are consumed back to front; a band (all-descending seeds only: seeds[k] = N-1-k) owns the
+  // positions of its own cells
+  int seed_pos = band.on ? N - band.c_begin * rows : a.n_seeds;
+  const int seed_lo = band.on ? N - band.c_end * rows : 0;
+  int nreg = 0, inl_total = band.on ? band.inl_base : 0, err = 0, steps = 0;
   bool any_failed = false;
 
   while (true) {
@@ -64,12 +88,12 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
     // not finite (or a non-positive threshold) fails its own self-test, adds no
     // inlier and leaves labels untouched, so skipping it here is exact.
     int found = -1;
-    while (seed_pos > 0 && found < 0) {
+    while (seed_pos > seed_lo && found < 0) {
       int cand = -1;
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         int pos = seed_pos - 1 - (tid + k * BLOCK);
-        if (pos >= 0 && cand < 0) {
+        if (pos >= seed_lo && cand < 0) {
           int s = seed_at(a.seeds, N, pos);
           if (labels[s] == kUnlabeled) {
             V3 p = ld3(xyz, s);
@@ -79,7 +103,7 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
       }
       // threads with smaller tid hold larger positions within each k; take max
       found = block_max<BLOCK>(cand, s_warp);
-      if (found < 0) seed_pos = max(seed_pos - 4 * BLOCK, 0);
+      if (found < 0) seed_pos = max(seed_pos - 4 * BLOCK, seed_lo);
     }
     if (found < 0) break;
     seed_pos = found;
@@ -100,7 +124,7 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
       int src = -1, cand = -1;
       bool acc = false;
       if (mine) {
-        const int qi = (head + tid) & (a.qcap - 1);
+        const int qi = (head + tid) & qmask;
         src = queue[2 * qi];
         cand = queue[2 * qi + 1];
         // (candidate - source).squaredNorm() < threshold, ps/cluster_region.h:94
@@ -237,7 +261,7 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
           const int cell = s + (s >= (side * side) / 2 ? 1 : 0);
           const int dc = cell / side - h, dr = cell % side - h;
           const int n = (col + dc) * rows + (row + dr);
-          const int qi = (tail + off) & (a.qcap - 1);
+          const int qi = (tail + off) & qmask;
           queue[2 * qi] = cand;
           queue[2 * qi + 1] = n;
           labels[n] = kAlreadyInQueue;
@@ -253,7 +277,7 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
 
     // CheckAndFinalize, ps/cluster_region.h:111-116
     if (ninl >= a.min_inliers) {
-      if (nreg < a.rcap) {
+      if (nreg < rcap) {
         if (tid == 0) meta[nreg] = ClusterMeta{base, ninl, label_id};
         ++nreg;
         inl_total += ninl;
@@ -271,8 +295,13 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
   // ps/segmentation.h:287-291
   __syncthreads();
   if (any_failed) {
-    for (int i = tid; i < N; i += BLOCK)
+    const int i0 = band.on ? band.c_begin * rows : 0, i1 = band.on ? band.c_end * rows : N;
+    for (int i = i0 + tid; i < i1; i += BLOCK)
       if (labels[i] == kAlreadyExamedPoint) labels[i] = kUnlabeled;
+  }
+  if (band.on) {
+    if (tid == 0) { band.out[0] = nreg; band.out[1] = inl_total - band.inl_base; band.out[2] = err; band.out[3] = steps; }
+    return;
   }
   if (tid == 0) {
     a.stats[f].n_cluster = nreg;
@@ -287,6 +316,102 @@ __global__ void __launch_bounds__(BLOCK, H1 ? 2 : 1) cluster_grow_kernel(Cluster
   __shared__ int s_warp[BLOCK / 32 + 1];
   const int f = blockIdx.x;
   cluster_grow_frame<BLOCK, H1>(a, f, a.id_offset_from_planar ? a.stats[f].n_planar : a.id_offset, s_warp);
+}
+
+// ---- one large frame: bands of columns grown concurrently (see ClusterBand) ----
+struct ClusterBandTable {
+  const int* c_begin;      // [n_bands], bands in the order the reference reaches them (ascending columns for the
+                           // back-to-front consumption of the all-descending seed list)
+  const int* c_end;
+  const long long* q_off;  // queue offset of the band, in (source, candidate) pairs
+  const int* q_cap;
+  const int* m_off;        // offset into the temporary region table
+  int* queue;              // band queues
+  ClusterMeta* meta;       // temporary region table
+  int* out;                // [n_bands][4]
+  int rcap_total;
+};
+
+// a column is active iff it holds a cell that can become an inlier: unlabeled and finite
+__global__ void __launch_bounds__(256) cluster_colflag_kernel(const float* __restrict__ xyz, const int* __restrict__ labels,
+                                                              int rows, int cols, int* flag) {
+  const int col = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (col >= cols) return;
+  bool any = false;
+  for (int r = lane; r < rows && !any; r += 32) {
+    const int i = col * rows + r;
+    any = labels[i] == kUnlabeled && vfinite(ld3(xyz, i));
+  }
+  any = __any_sync(0xffffffffu, any);
+  if (lane == 0) flag[col] = any ? 1 : 0;
+}
+
+template <int BLOCK, bool H1>
+__global__ void __launch_bounds__(BLOCK, H1 ? 2 : 1) cluster_band_kernel(ClusterArgs a, ClusterBandTable t) {
+  __shared__ int s_warp[BLOCK / 32 + 1];
+  const int bnd = blockIdx.x;
+  ClusterBand band;
+  band.on = 1;
+  band.c_begin = t.c_begin[bnd]; band.c_end = t.c_end[bnd];
+  band.queue = t.queue + 2 * t.q_off[bnd]; band.qcap = t.q_cap[bnd];
+  band.inl_base = band.c_begin * a.rows;
+  band.meta = t.meta + t.m_off[bnd];
+  band.rcap = (bnd + 1 < (int)gridDim.x ? t.m_off[bnd + 1] : t.rcap_total) - t.m_off[bnd];
+  band.out = t.out + 4 * bnd;
+  cluster_grow_frame<BLOCK, H1>(a, 0, a.id_offset, s_warp, band);   // provisional ids: renumbered by the merge
+}
+
+// region ids in the reference's order (band order, then the order inside the band), final region table
+// with the inlier lists packed in that order (cluster_band_compact_kernel moves them), frame statistics.
+// region_base: [2][n_bands] = regions / inliers of the bands in front
+__global__ void __launch_bounds__(256) cluster_band_merge_kernel(ClusterArgs a, ClusterBandTable t, int n_bands, int* region_base) {
+  __shared__ int s_total[3];
+  if (threadIdx.x == 0) {
+    int nreg = 0, ninl = 0, err = 0, steps = 0;
+    for (int b = 0; b < n_bands; ++b) {
+      region_base[b] = nreg;
+      region_base[n_bands + b] = ninl;
+      nreg += t.out[4 * b]; ninl += t.out[4 * b + 1]; err |= t.out[4 * b + 2]; steps += t.out[4 * b + 3];
+    }
+    if (nreg > a.rcap) { err |= kErrRegionCap; nreg = a.rcap; }
+    a.stats[0].n_cluster = nreg;
+    a.stats[0].cluster_inliers = ninl;
+    a.stats[0].error_flags |= err;
+    a.stats[0].grow_steps += steps;
+    s_total[0] = nreg;
+  }
+  __syncthreads();
+  const int total = s_total[0];
+  for (int b = 0; b < n_bands; ++b) {
+    const int n = t.out[4 * b], g0 = region_base[b];
+    for (int r = threadIdx.x; r < n; r += blockDim.x) {
+      if (g0 + r >= total) continue;
+      ClusterMeta m = t.meta[t.m_off[b] + r];
+      m.label_id = a.id_offset + g0 + r;
+      m.inlier_begin = region_base[n_bands + b] + (m.inlier_begin - t.c_begin[b] * a.rows);
+      a.meta[g0 + r] = m;
+    }
+  }
+}
+// the bands' inlier slices, packed in band order into tmp; then back into the frame's inlier buffer
+__global__ void __launch_bounds__(256) cluster_band_compact_kernel(ClusterArgs a, ClusterBandTable t, int n_bands,
+                                                                   const int* region_base, int* tmp) {
+  const int b = blockIdx.x;
+  const int n = t.out[4 * b + 1], src = t.c_begin[b] * a.rows, dst = region_base[n_bands + b];
+  for (int i = threadIdx.x; i < n; i += blockDim.x) tmp[dst + i] = a.inliers[src + i];
+}
+__global__ void __launch_bounds__(256) cluster_band_copyback_kernel(ClusterArgs a, const int* tmp) {
+  const int n = a.stats[0].cluster_inliers;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) a.inliers[i] = tmp[i];
+}
+// labels of every inlier <- the region's final id
+__global__ void __launch_bounds__(256) cluster_band_relabel_kernel(ClusterArgs a) {
+  const int n = a.stats[0].n_cluster;
+  for (int r = blockIdx.x; r < n; r += gridDim.x) {
+    const ClusterMeta m = a.meta[r];
+    for (int i = threadIdx.x; i < m.inlier_count; i += blockDim.x) a.labels[a.inliers[m.inlier_begin + i]] = m.label_id;
+  }
 }
 
 }  // namespace pcseg

@@ -455,6 +455,89 @@ int run_cluster(pcseg_batch* b, const float* xyz_dev, const int* seeds_dev, int 
   return PCSEG_OK;
 }
 
+// One large frame with all-descending seeds: bands of columns separated by >= h columns without an
+// unlabeled finite cell are independent (grow_cluster.cuh: ClusterBand) and are grown by one CTA each.
+// *used = false when the frame has fewer than two bands (the caller then takes the one-CTA path).
+int run_cluster_banded(pcseg_batch* b, const float* xyz_dev, const pcseg_cluster_config* cfg, int id_offset, bool* used) {
+  pcseg_ctx* c = b->ctx;
+  cudaStream_t stream = S(b);
+  *used = false;
+  const int rows = b->rows, cols = b->cols, h = cfg->half_search_window;
+  ClusterArgs a;
+  int st = make_cluster_args(b, xyz_dev, nullptr, 0, cfg, id_offset, 0, &a);
+  if (st) return st;
+  DevBuf d_flag;
+  CU_TRY(c, d_flag.ensure((size_t)cols * sizeof(int)));
+  cluster_colflag_kernel<<<(unsigned)(((size_t)cols * 32 + 255) / 256), 256, 0, stream>>>(xyz_dev, a.labels, rows, cols, d_flag.as<int>());
+  ++c->launches;
+  std::vector<int> flag(cols);
+  CU_TRY(c, cudaMemcpyAsync(flag.data(), d_flag.p, (size_t)cols * sizeof(int), cudaMemcpyDeviceToHost, stream));
+  CU_TRY(c, cudaStreamSynchronize(stream));
+  // bands in ascending columns: a run of >= max(h, 1) inactive columns separates two bands
+  std::vector<int> cb, ce;
+  const int gap = std::max(h, 1);
+  int col = 0;
+  while (col < cols) {
+    while (col < cols && !flag[col]) ++col;
+    if (col >= cols) break;
+    int begin = col, last_active = col, idle = 0;
+    while (col < cols && idle < gap) {
+      if (flag[col]) { last_active = col; idle = 0; } else ++idle;
+      ++col;
+    }
+    cb.push_back(begin);
+    ce.push_back(last_active + 1);
+  }
+  const int nb = (int)cb.size();
+  if (nb < 2) return PCSEG_OK;
+  // tables, bands in ASCENDING column order: the list "all indices descending" is consumed back to front,
+  // i.e. in ascending index order (ps/segmentation.h:254-256), so lower columns are reached first
+  std::vector<int> h_cb(nb), h_ce(nb), h_qcap(nb), h_moff(nb);
+  std::vector<long long> h_qoff(nb);
+  long long qtot = 0;
+  int mtot = 0;
+  for (int k = 0; k < nb; ++k) {
+    const int i = k;
+    h_cb[k] = cb[i]; h_ce[k] = ce[i];
+    const long long cells = (long long)(ce[i] - cb[i]) * rows;
+    int qc = 1024;
+    while (qc < cells) qc <<= 1;
+    h_qcap[k] = qc; h_qoff[k] = qtot; qtot += qc;
+    h_moff[k] = mtot; mtot += (int)(cells / std::max(cfg->min_region_inliers, 1)) + 1;
+  }
+  DevBuf d_tab, d_queue, d_meta, d_out;
+  const size_t tab_bytes = (size_t)nb * (4 * sizeof(int) + sizeof(long long));
+  CU_TRY(c, d_tab.ensure(tab_bytes));
+  CU_TRY(c, d_queue.ensure((size_t)qtot * 2 * sizeof(int)));
+  CU_TRY(c, d_meta.ensure((size_t)mtot * sizeof(ClusterMeta)));
+  CU_TRY(c, d_out.ensure((size_t)nb * 6 * sizeof(int)));
+  char* tp = d_tab.as<char>();
+  long long* p_qoff = reinterpret_cast<long long*>(tp);
+  int* p_cb = reinterpret_cast<int*>(tp + (size_t)nb * sizeof(long long));
+  int* p_ce = p_cb + nb; int* p_qcap = p_ce + nb; int* p_moff = p_qcap + nb;
+  CU_TRY(c, cudaMemcpyAsync(p_qoff, h_qoff.data(), (size_t)nb * sizeof(long long), cudaMemcpyHostToDevice, stream));
+  CU_TRY(c, cudaMemcpyAsync(p_cb, h_cb.data(), (size_t)nb * sizeof(int), cudaMemcpyHostToDevice, stream));
+  CU_TRY(c, cudaMemcpyAsync(p_ce, h_ce.data(), (size_t)nb * sizeof(int), cudaMemcpyHostToDevice, stream));
+  CU_TRY(c, cudaMemcpyAsync(p_qcap, h_qcap.data(), (size_t)nb * sizeof(int), cudaMemcpyHostToDevice, stream));
+  CU_TRY(c, cudaMemcpyAsync(p_moff, h_moff.data(), (size_t)nb * sizeof(int), cudaMemcpyHostToDevice, stream));
+  ClusterBandTable t;
+  t.c_begin = p_cb; t.c_end = p_ce; t.q_off = p_qoff; t.q_cap = p_qcap; t.m_off = p_moff;
+  t.queue = d_queue.as<int>(); t.meta = d_meta.as<ClusterMeta>(); t.out = d_out.as<int>(); t.rcap_total = mtot;
+  if (a.half_window == 1) cluster_band_kernel<kClusterBlock, true><<<nb, kClusterBlock, 0, stream>>>(a, t);
+  else cluster_band_kernel<kClusterBlock, false><<<nb, kClusterBlock, 0, stream>>>(a, t);
+  int* region_base = d_out.as<int>() + 4 * nb;
+  cluster_band_merge_kernel<<<1, 256, 0, stream>>>(a, t, nb, region_base);
+  // the band queues are idle now: scratch for packing the inlier lists in region order
+  cluster_band_compact_kernel<<<nb, 256, 0, stream>>>(a, t, nb, region_base, d_queue.as<int>());
+  cluster_band_copyback_kernel<<<296, 256, 0, stream>>>(a, d_queue.as<int>());
+  cluster_band_relabel_kernel<<<296, 256, 0, stream>>>(a);
+  c->launches += 5;
+  CU_TRY(c, cudaGetLastError());
+  CU_TRY(c, cudaStreamSynchronize(stream));   // the tables above die with this scope
+  *used = true;
+  return PCSEG_OK;
+}
+
 int map_error_flags(pcseg_ctx* c, int flags) {
   if (flags == 0) return PCSEG_OK;
   c->last_error = "per-frame capacity/trace error flags = " + std::to_string(flags);
@@ -863,8 +946,19 @@ int pcseg_segment_cluster(pcseg_ctx* c, const float* xyz, int rows, int cols, co
   CU_TRY(c, cudaMemsetAsync(b->stats.p, 0, sizeof(FrameStats), c->stream));
   if (n_seeds > 0) {
     const int* seeds_dev;
-    if ((st = check_seeds_host(seeds, n_seeds, N, c, &b->seeds, &seeds_dev))) return st;
-    if ((st = run_cluster(b, b->xyz_dev, seeds_dev, n_seeds, cfg, id_offset, 0))) return st;
+    // one large frame with the seed list "all indices descending" (ps/clustering_test.cc:57-59): independent
+    // column bands are grown concurrently (PCSEG_CLUSTER_BANDS=0 turns it off)
+    bool banded = false;
+    const char* be = getenv("PCSEG_CLUSTER_BANDS");
+    if (!(be && be[0] == '0') && N >= ((size_t)1 << 18) && (size_t)n_seeds == N && !is_device_ptr(seeds)) {
+      bool alldesc = true;
+      for (size_t k = 0; k < N && alldesc; ++k) alldesc = seeds[k] == (int)(N - 1 - k);
+      if (alldesc && (st = run_cluster_banded(b, b->xyz_dev, cfg, id_offset, &banded))) return st;
+    }
+    if (!banded) {
+      if ((st = check_seeds_host(seeds, n_seeds, N, c, &b->seeds, &seeds_dev))) return st;
+      if ((st = run_cluster(b, b->xyz_dev, seeds_dev, n_seeds, cfg, id_offset, 0))) return st;
+    }
   }
   if ((st = from_device(c, labels, b->labels.p, N * sizeof(int)))) return st;
   pcseg_regions* r = new pcseg_regions();
