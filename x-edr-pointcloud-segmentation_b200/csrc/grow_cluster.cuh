@@ -36,10 +36,11 @@ struct ClusterArgs {
 // One CTA's share of a SINGLE large frame (cluster_band_kernel): a band of consecutive columns that no
 // window of the growth can leave, because at least `half_window` columns without any unlabeled finite
 // cell separate it from the next band (cells there are labelled / masked, or not finite -- a non-finite
-// cell can be enqueued and is always rejected, so it carries nothing across).  With the seeds consumed in
-// the all-descending list (consumed back to front = ascending indices) the reference finishes every region
-// of a lower band before it touches a higher one, so the bands are grown concurrently and only the region ids are assigned afterwards, by band order
-// (cluster_band_merge_kernel).  on == 0: the whole frame (the batched path).
+// cell can be enqueued and is always rejected, so it carries nothing across).  The seed list "all
+// indices descending" is consumed back to front, i.e. in ascending index order, so the reference
+// finishes every region of a lower band before it touches a higher one: the bands are grown
+// concurrently and only the region ids and the order of the inlier lists are assigned afterwards, by
+// band order (cluster_band_merge_kernel).  on == 0: the whole frame (the batched path).
 struct ClusterBand {
   int on;
   int c_begin, c_end;   // columns [c_begin, c_end)
