@@ -10,6 +10,10 @@ from types import SimpleNamespace
 
 import numpy as np
 
+# Several workspaces (each with its own streams) overlap only if their streams map to distinct
+# hardware queues; the default is 8.  Read by the driver when the CUDA context is created.
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PCSEG_LIB", os.path.join(_HERE, "libpcseg_b200.so"))
 _LIB = None
