@@ -171,6 +171,27 @@ int pcseg_seeds_average_normals(pcseg_ctx*, const float* xyz, const float* norma
                                 int min_num_valid_normals, float min_avg_normal_length,
                                 int* seeds_out, int cap, int* n_out);
 
+/* No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The same computation and the same seeds as pcseg_seeds_average_normals, but the entry point
+ * allocates NOTHING (no cudaMalloc / cudaFree / allocating library routine): its scratch (one
+ * flag byte per window position) lives in a file-scope `static __device__` array of
+ * PCSEG_NOALLOC_MAX_CELLS bytes that every GPU loading the library holds until exit.
+ *   - normals_dev, seeds_out_dev, n_out_dev are DEVICE pointers on the context's device (host
+ *     pointers would need a staging allocation: PCSEG_ERR_UNSUPPORTED).  seeds_out_dev holds cap
+ *     ints and cap must cover every window position, cap >= (rows - 2*(neighborhood_size/2)) * cols
+ *     (PCSEG_ERR_CAPACITY otherwise); *n_out_dev receives the number of seeds.
+ *   - rows * cols > PCSEG_NOALLOC_MAX_CELLS -> PCSEG_ERR_CAPACITY with a message in pcseg_last_error.
+ *   - The call returns after the context's stream has drained (cudaStreamSynchronize).
+ *   - ALL calls (any context, any thread) on one device share the array, which keeps the last
+ *     call's contents; every flag the second kernel reads is written by the first kernel of the same
+ *     call, so nothing has to start at zero.  Calls that overlap on one GPU race: serialise them. */
+#define PCSEG_NOALLOC_MAX_CELLS (1 << 20)
+int pcseg_seeds_average_normals_noalloc(pcseg_ctx*, const float* normals_dev, int rows, int cols,
+                                        int neighborhood_size, int min_num_valid_normals,
+                                        float min_avg_normal_length, int* seeds_out_dev, int cap,
+                                        int* n_out_dev);
+
 /* Replaces ps/planar_region.h:478-519 FindSeedPointsFromLastPlanarRegions.  The previous
  * regions are given by what the function reads of them: inlier_indices().size(), centroid(),
  * plane().normal().  current_pose_prev = (q_xyzw, translation), an eigenmath::Pose3f.

@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1069,6 +1070,87 @@ int pcseg_seeds_average_normals(pcseg_ctx* c, const float* xyz, const float* nor
   *n_out = n;
   const int ncopy = std::min(n, cap);
   if (ncopy > 0 && (st = from_device(c, seeds_out, b->seeds.p, (size_t)ncopy * sizeof(int)))) return st;
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  return PCSEG_OK;
+}
+
+// ---------------------------------------------------------------------------
+// pcseg_seeds_average_normals_noalloc: the seed finder above for callers that cannot call
+// cudaMalloc (no counterpart in the reference).
+// Scratch = the flag byte per window position, in a file-scope device array instead of the
+// workspace's queue buffer.  g_noalloc_flags names the array: in HOST code that name is a
+// host-side stand-in, not a device address, so the address is asked for once per device with
+// cudaGetSymbolAddress (that device current) and only that pointer is handed to the kernels.
+// ---------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_noalloc_flags[PCSEG_NOALLOC_MAX_CELLS];
+
+namespace {
+constexpr int kNoallocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+unsigned char* g_noalloc_flags_dev[kNoallocMaxDevices] = {};
+
+// Device address of g_noalloc_flags on `device` (which must be current); looked up once per device.
+cudaError_t noalloc_flags_address(int device, unsigned char** out) {
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (!g_noalloc_flags_dev[device]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_flags);
+    if (e != cudaSuccess) return e;
+    g_noalloc_flags_dev[device] = static_cast<unsigned char*>(p);
+  }
+  *out = g_noalloc_flags_dev[device];
+  return cudaSuccess;
+}
+}  // namespace
+
+int pcseg_seeds_average_normals_noalloc(pcseg_ctx* c, const float* normals_dev, int rows, int cols,
+                                        int neighborhood_size, int min_num_valid_normals,
+                                        float min_avg_normal_length, int* seeds_out_dev, int cap, int* n_out_dev) {
+  if (!c || !normals_dev || !seeds_out_dev || !n_out_dev) return PCSEG_ERR_NULL;
+  if (rows <= 1 || cols <= 0) return PCSEG_ERR_DIMS;   // CHECK_GT(points.Rows(), 1), ps/segmentation.h:143
+  if (rows > cols) return PCSEG_ERR_UNSUPPORTED;        // as pcseg_seeds_average_normals
+  if (neighborhood_size < 1 || neighborhood_size > kAvgMaxNbhd) return PCSEG_ERR_UNSUPPORTED;
+  if (c->device < 0 || c->device >= kNoallocMaxDevices) return PCSEG_ERR_UNSUPPORTED;
+  const long long N = (long long)rows * cols;
+  if (N > (long long)PCSEG_NOALLOC_MAX_CELLS) {
+    c->last_error = "pcseg_seeds_average_normals_noalloc: rows * cols = " + std::to_string(N) +
+                    " exceeds the static scratch of PCSEG_NOALLOC_MAX_CELLS = " +
+                    std::to_string((long long)PCSEG_NOALLOC_MAX_CELLS) + " cells; use pcseg_seeds_average_normals";
+    return PCSEG_ERR_CAPACITY;
+  }
+  CU_TRY(c, cudaSetDevice(c->device));
+  if (!is_device_ptr(normals_dev) || !is_device_ptr(seeds_out_dev) || !is_device_ptr(n_out_dev)) {
+    c->last_error = "pcseg_seeds_average_normals_noalloc: normals, seeds_out and n_out must be device pointers "
+                    "(a host pointer would need a staging allocation)";
+    return PCSEG_ERR_UNSUPPORTED;
+  }
+  const int half = neighborhood_size / 2;
+  if (rows < neighborhood_size || cols < neighborhood_size) {  // ps/segmentation.h:150-152: no seeds
+    CU_TRY(c, cudaMemsetAsync(n_out_dev, 0, sizeof(int), c->stream));
+    CU_TRY(c, cudaStreamSynchronize(c->stream));
+    return PCSEG_OK;
+  }
+  const int nrows = rows - 2 * half;
+  const long long positions = (long long)nrows * cols;
+  if ((long long)cap < positions) {
+    c->last_error = "pcseg_seeds_average_normals_noalloc: cap = " + std::to_string(cap) +
+                    " is below the number of window positions " + std::to_string(positions);
+    return PCSEG_ERR_CAPACITY;
+  }
+  unsigned char* flags = nullptr;
+  CU_TRY(c, noalloc_flags_address(c->device, &flags));
+  AvgSeedArgs a;
+  a.normals = normals_dev; a.rows = rows; a.cols = cols;
+  a.nbhd = neighborhood_size; a.half = half; a.min_valid = min_num_valid_normals;
+  a.sq_min_len = min_avg_normal_length * min_avg_normal_length;  // ps/segmentation.h:146-147
+  a.flags = flags; a.flag_stride = (size_t)PCSEG_NOALLOC_MAX_CELLS;
+  a.seeds = seeds_out_dev; a.stride = cap; a.n_seeds = n_out_dev;
+  // every flag in [0, positions) is written by the first kernel before the second reads it:
+  // the previous call's contents of the shared array need no clearing
+  seed_avg_normals_flag_kernel<<<dim3((nrows + 63) / 64, 1), 64, 0, c->stream>>>(a);
+  seed_avg_normals_order_kernel<<<1, 1024, 0, c->stream>>>(a);
+  c->launches += 2;
+  CU_TRY(c, cudaGetLastError());
   CU_TRY(c, cudaStreamSynchronize(c->stream));
   return PCSEG_OK;
 }

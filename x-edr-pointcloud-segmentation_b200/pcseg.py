@@ -108,7 +108,7 @@ pcseg_default_cluster_config pcseg_create pcseg_destroy pcseg_status_string
 pcseg_last_error pcseg_launch_count pcseg_stream pcseg_prepare_unlabeled_labels
 pcseg_normals_organized pcseg_segment_planar pcseg_segment_cluster
 pcseg_mean_shift_modes pcseg_mean_shift_modes_range pcseg_mean_shift_from_modes
-pcseg_mean_shift pcseg_mean_shift_sort_order pcseg_seeds_plane_support pcseg_seeds_average_normals pcseg_seeds_last_planar_regions
+pcseg_mean_shift pcseg_mean_shift_sort_order pcseg_seeds_plane_support pcseg_seeds_average_normals pcseg_seeds_average_normals_noalloc pcseg_seeds_last_planar_regions
 pcseg_fit_planes pcseg_plane_estimator_replay pcseg_plane_estimators_transform pcseg_plane_estimators_merge
 pcseg_batch_submit_regions pcseg_transform_in_place pcseg_gather_points pcseg_cluster_unorganized pcseg_regions_bboxes
 pcseg_batch_create pcseg_batch_destroy pcseg_batch_run pcseg_batch_submit pcseg_batch_wait pcseg_batch_stream pcseg_batch_frame_stats
@@ -413,6 +413,16 @@ class Context:
             self.h, _addr(xyz), _addr(normals), rows, cols, neighborhood_size, min_num_valid_normals,
             C.c_float(min_avg_normal_length), _addr(out), out.size, C.byref(n)))
         return out[:n.value].copy()
+
+    def seeds_average_normals_noalloc(self, normals_dev, rows, cols, seeds_out_dev, cap, n_out_dev,
+                                      neighborhood_size=5, min_num_valid_normals=8,
+                                      min_avg_normal_length=0.9999):
+        """pcseg_seeds_average_normals_noalloc: the same seeds with the scratch in a static device
+        array (no allocation inside the call).  normals_dev / seeds_out_dev / n_out_dev are DEVICE
+        addresses (ints) owned by the caller; returns after the context's stream has drained."""
+        self._check(self.L.pcseg_seeds_average_normals_noalloc(
+            self.h, C.c_void_p(normals_dev), rows, cols, neighborhood_size, min_num_valid_normals,
+            C.c_float(min_avg_normal_length), C.c_void_p(seeds_out_dev), cap, C.c_void_p(n_out_dev)))
 
     def seeds_last_planar_regions(self, xyz, normals, prev_inlier_counts, prev_centroids, prev_normals,
                                   q_xyzw=(0, 0, 0, 1), translation=(0, 0, 0), max_distance=0.5,
