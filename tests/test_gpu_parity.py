@@ -337,6 +337,41 @@ def test_mean_shift_full_parity(ctx, rows, cols, pitch, blobs, h, sort_mode, min
     _assert_ms_equal(g_lab, g_r, o_lab, o_r)
 
 
+def _terraces(rows, cols, tr, tc, pitch, step, seed, nan_frac=0.03):
+    """Tiles of tr x tc cells at heights step * ((ti + 2 tj) % 4), no gaps: the regions TOUCH (their
+    windows overlap) without merging, and cells within 1 m of a neighbour's mode cross the steps --
+    the case in which regions grown at the same time interact (meanshift_wave.cuh)."""
+    rng = np.random.default_rng(seed)
+    cc, rr = np.meshgrid(np.arange(cols), np.arange(rows), indexing="ij")
+    z = step * (((rr // tr) + 2 * (cc // tc)) % 4) + 0.002 * rng.standard_normal((cols, rows))
+    p = np.stack([cc * pitch, rr * pitch, z], axis=-1).reshape(-1, 3).astype(np.float32)
+    p[rng.random(rows * cols) < nan_frac] = np.nan
+    return np.ascontiguousarray(p)
+
+
+@pytest.mark.parametrize("rows,cols,tr,tc,pitch,step,h,min_inl", [
+    (96, 120, 24, 30, 0.05, 0.6, 1, 7), (96, 120, 24, 30, 0.05, 0.6, 2, 7), (150, 150, 25, 25, 0.08, 0.3, 1, 20),
+    (120, 160, 12, 16, 0.1, 0.7, 3, 5), (200, 200, 20, 20, 0.03, 0.5, 2, 300)])
+def test_mean_shift_touching_regions(ctx, rows, cols, tr, tc, pitch, step, h, min_inl):
+    """Many regions that touch one another: the wave path (several regions in flight, resolved in
+    order) and the serial path (PCSEG_MS_GROWTH=serial) both equal the oracle."""
+    import os
+    xyz = _terraces(rows, cols, tr, tc, pitch, step, seed=rows + h)
+    labels = np.full(rows * cols, -1, np.int32)
+    cfg = dict(half_search_window=h, min_region_inliers=min_inl)
+    o_lab, o_r, _ = oracle.mean_shift(xyz, rows, cols, labels, cfg=oracle.default_cluster_config(**cfg),
+                                      iterations=3, id_offset=2, sort_mode=1)
+    assert o_r.n >= 4
+    g_lab, g_r = ctx.mean_shift(xyz, rows, cols, labels, cfg=cfg, iterations=3, id_offset=2, sort_mode=1)
+    _assert_ms_equal(g_lab, g_r, o_lab, o_r)
+    os.environ["PCSEG_MS_GROWTH"] = "serial"
+    try:
+        s_lab, s_r = ctx.mean_shift(xyz, rows, cols, labels, cfg=cfg, iterations=3, id_offset=2, sort_mode=1)
+    finally:
+        del os.environ["PCSEG_MS_GROWTH"]
+    _assert_ms_equal(s_lab, s_r, o_lab, o_r)
+
+
 def test_mean_shift_sharded_ranges_equal_full(ctx):
     """Seed-cell shards (the multi-GPU path of C5) concatenate to the unsharded records, and
     the growth phase on gathered records equals the one-call path."""

@@ -18,6 +18,7 @@
 #include "grow_cluster.cuh"
 #include "planar_kernel.cuh"
 #include "meanshift_grow.cuh"
+#include "meanshift_wave.cuh"
 #include "normals.cuh"
 #include "seeds.cuh"
 #include "results_pack.cuh"
@@ -1528,25 +1529,66 @@ int mean_shift_finish(pcseg_ctx* c, const float* xyz_dev, int rows, int cols, co
   CU_TRY(c, cudaMemsetAsync(d_alive.p, 1, (size_t)S, c->stream));
   g.alive = d_alive.as<unsigned char>();
   c->launches += 2;
-  // growth in rounds (meanshift_grow.cuh): the serial CTA accepts a few regions, the filter kernel
-  // marks the modes they killed on the whole GPU, the CTA resumes behind the last batch it finished
   int h_out[4] = {0, 0, 0, 0};
-  int pos = 0, n_reg = 0, n_inl = 0, r_applied = 0;
-  while (pos < S) {
-    if (n_reg > r_applied) {
-      const unsigned fgrid = (unsigned)std::min<size_t>(((size_t)(S - pos) + 255) / 256, (size_t)148 * 8);
-      ms_filter_kernel<<<fgrid, 256, 0, c->stream>>>(g, pos, r_applied, n_reg);
-      r_applied = n_reg;
+  const char* ms_mode = getenv("PCSEG_MS_GROWTH");
+  if (ms_mode && strcmp(ms_mode, "serial") == 0) {
+    // growth in rounds (meanshift_grow.cuh): the serial CTA accepts a few regions, the filter kernel
+    // marks the modes they killed on the whole GPU, the CTA resumes behind the last batch it finished
+    int pos = 0, n_reg = 0, n_inl = 0, r_applied = 0;
+    while (pos < S) {
+      if (n_reg > r_applied) {
+        const unsigned fgrid = (unsigned)std::min<size_t>(((size_t)(S - pos) + 255) / 256, (size_t)148 * 8);
+        ms_filter_kernel<<<fgrid, 256, 0, c->stream>>>(g, pos, r_applied, n_reg);
+        r_applied = n_reg;
+        ++c->launches;
+      }
+      ms_grow_kernel<<<1, kMsGrowBlock, 0, c->stream>>>(g, pos, r_applied, n_inl);
       ++c->launches;
+      CU_TRY(c, cudaGetLastError());
+      CU_TRY(c, cudaMemcpyAsync(h_out, d_out.p, sizeof(h_out), cudaMemcpyDeviceToHost, c->stream));
+      CU_TRY(c, cudaStreamSynchronize(c->stream));
+      if (h_out[1]) break;
+      if (h_out[3] <= pos && h_out[0] == n_reg) { c->last_error = "mean-shift growth made no progress"; d_alive.release(); return PCSEG_ERR_CUDA; }
+      pos = h_out[3]; n_reg = h_out[0]; n_inl = h_out[2];
     }
-    ms_grow_kernel<<<1, kMsGrowBlock, 0, c->stream>>>(g, pos, r_applied, n_inl);
-    ++c->launches;
-    CU_TRY(c, cudaGetLastError());
-    CU_TRY(c, cudaMemcpyAsync(h_out, d_out.p, sizeof(h_out), cudaMemcpyDeviceToHost, c->stream));
-    CU_TRY(c, cudaStreamSynchronize(c->stream));
-    if (h_out[1]) break;
-    if (h_out[3] <= pos && h_out[0] == n_reg) { c->last_error = "mean-shift growth made no progress"; d_alive.release(); return PCSEG_ERR_CUDA; }
-    pos = h_out[3]; n_reg = h_out[0]; n_inl = h_out[2];
+  } else {
+    // waves of regions grown at the same time and resolved in order (meanshift_wave.cuh)
+    const int kmax = (int)std::max<size_t>(1, std::min<size_t>(std::min<size_t>(kMsWaveMax, (size_t)S),
+                                                               ((size_t)3 << 30) / (N * sizeof(int))));
+    DevBuf d_slots, d_wave;
+    CU_TRY(c, d_slots.ensure((size_t)kmax * N * sizeof(int)));
+    CU_TRY(c, d_wave.ensure(kWvInts * sizeof(int)));
+    CU_TRY(c, cudaMemsetAsync(d_wave.p, 0, kWvInts * sizeof(int), c->stream));
+    MsWaveArgs w;
+    w.g = g; w.slot_inliers = d_slots.as<int>(); w.slot_stride = N; w.wave = d_wave.as<int>();
+    int h_wave[4] = {0, 0, 0, 0};
+    int pos = 0, n_reg = 0, n_inl = 0, r_applied = 0, K = std::min(16, kmax);
+    bool first = true;
+    while (pos < S) {
+      if (first || n_reg > r_applied) {   // dead-mode flags up to date before the candidates are picked
+        const unsigned fgrid = (unsigned)std::min<size_t>(((size_t)(S - pos) + 255) / 256, (size_t)148 * 8);
+        ms_filter_kernel<<<fgrid, 256, 0, c->stream>>>(g, pos, r_applied, n_reg);
+        r_applied = n_reg;
+        first = false;
+        ++c->launches;
+      }
+      ms_wave_select_kernel<<<1, 1024, 0, c->stream>>>(w, pos, K);
+      ms_wave_grow_kernel<<<K, kMsGrowBlock, 0, c->stream>>>(w);
+      ms_wave_check_kernel<<<dim3(64, K), 256, 0, c->stream>>>(w);
+      ms_wave_resolve_kernel<<<1, 1024, 0, c->stream>>>(w, n_reg, n_inl);
+      ms_wave_finalize_kernel<<<dim3(32, K), 256, 0, c->stream>>>(w);
+      c->launches += 5;
+      CU_TRY(c, cudaGetLastError());
+      CU_TRY(c, cudaMemcpyAsync(h_out, d_out.p, sizeof(h_out), cudaMemcpyDeviceToHost, c->stream));
+      CU_TRY(c, cudaMemcpyAsync(h_wave, d_wave.p, sizeof(h_wave), cudaMemcpyDeviceToHost, c->stream));
+      CU_TRY(c, cudaStreamSynchronize(c->stream));
+      if (h_out[1]) break;
+      const int n_cand = h_wave[kWvNCand], stop = h_wave[kWvStop];
+      if (n_cand == 0) break;   // no live mode left
+      if (h_out[3] <= pos && stop == 0) { c->last_error = "mean-shift growth made no progress"; return PCSEG_ERR_CUDA; }
+      pos = h_out[3]; n_reg = h_out[0]; n_inl = h_out[2];
+      K = stop == n_cand ? std::min(2 * K, kmax) : std::max(K / 2, std::min(4, kmax));
+    }
   }
   d_alive.release();
   const int R = h_out[0], total = h_out[2];
