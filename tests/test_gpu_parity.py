@@ -370,6 +370,13 @@ def test_mean_shift_touching_regions(ctx, rows, cols, tr, tc, pitch, step, h, mi
     finally:
         del os.environ["PCSEG_MS_GROWTH"]
     _assert_ms_equal(s_lab, s_r, o_lab, o_r)
+    # ranks above 0 with room for 100 cells only: they outgrow their slot, stop and are grown again
+    os.environ["PCSEG_MS_SLOT_CAP"] = "100"
+    try:
+        c_lab, c_r = ctx.mean_shift(xyz, rows, cols, labels, cfg=cfg, iterations=3, id_offset=2, sort_mode=1)
+    finally:
+        del os.environ["PCSEG_MS_SLOT_CAP"]
+    _assert_ms_equal(c_lab, c_r, o_lab, o_r)
 
 
 def test_mean_shift_sharded_ranges_equal_full(ctx):

@@ -35,12 +35,13 @@
 namespace pcseg {
 
 constexpr int kMsTmpBase = 0x40000000;  // temporary label of rank k = kMsTmpBase + k
-constexpr int kMsWaveMax = 64;          // ranks per wave (claim key = rank * 1024 + thread)
+constexpr int kMsWaveMax = 256;         // ranks per wave (claim key = rank * 1024 + thread)
 
 struct MsWaveArgs {
   MsGrowArgs g;
-  int* slot_inliers;      // [kMsWaveMax][slot_stride] inlier list of each rank
-  size_t slot_stride;
+  int* slot_inliers;      // inlier list of each rank: rank 0 has room for every cell (slot0 ints), the
+  size_t slot0;           // higher ranks for slot_cap cells each -- a rank that outgrows its slot stops
+  int slot_cap;           // as if it had met a lower rank and is grown again as rank 0 of a later wave
   // wave state (device): see the indices below
   int* wave;
 };
@@ -56,6 +57,9 @@ constexpr int kWvAccBase = kWvAccRank + kMsWaveMax;    //   inlier_begin
 constexpr int kWvAccLabel = kWvAccBase + kMsWaveMax;   //   final label id
 constexpr int kWvInts = kWvAccLabel + kMsWaveMax;
 
+__device__ __forceinline__ int* ms_slot(const MsWaveArgs& w, int k) {
+  return w.slot_inliers + (k == 0 ? (size_t)0 : w.slot0 + (size_t)(k - 1) * (size_t)w.slot_cap);
+}
 __device__ __forceinline__ bool ms_is_lower_tmp(int lab, int mylab) { return lab >= kMsTmpBase && lab < mylab; }
 
 // The first `want` live modes at positions >= pos0 (one CTA).
@@ -99,7 +103,7 @@ __global__ void __launch_bounds__(kMsGrowBlock) ms_wave_grow_kernel(MsWaveArgs w
   const int CH = kMsGrowBlock / WW;   // queue entries per chunk
   const int mylab = kMsTmpBase + k;
   const int ckey = k * kMsGrowBlock + t;   // claims of a lower rank win
-  int* inl = w.slot_inliers + (size_t)k * w.slot_stride;
+  int* inl = ms_slot(w, k);
   const MsSeedRec cur = a.seeds[w.wave[kWvPos + k]];
   const V3 mode{cur.mx, cur.my, cur.mz};
   if (t == 0) s_conflict = 0;
@@ -143,12 +147,18 @@ __global__ void __launch_bounds__(kMsGrowBlock) ms_wave_grow_kernel(MsWaveArgs w
     pass = pass && __ldcg(&a.claim[cell < 0 ? 0 : cell]) == ckey;
     int total;
     const int off = block_scan_excl<kMsGrowBlock>(pass ? 1 : 0, &total, s_warp);
+    const bool fits = k == 0 || count + total <= w.slot_cap;
     if (pass) {
-      const unsigned old = atomicMin(reinterpret_cast<unsigned*>(&a.labels[cell]), (unsigned)mylab);  // :195-196
-      if (ms_is_lower_tmp((int)old, mylab)) s_conflict = 1;
-      inl[count + off] = cell;                                                                     // :194, :197
+      if (fits) {
+        const unsigned old = atomicMin(reinterpret_cast<unsigned*>(&a.labels[cell]), (unsigned)mylab);  // :195-196
+        if (ms_is_lower_tmp((int)old, mylab)) s_conflict = 1;
+        inl[count + off] = cell;                                                                     // :194, :197
+      } else {
+        s_conflict = 1;   // the slot is full: give up here, nothing of this chunk is taken
+      }
       atomicCAS(&a.claim[cell], ckey, INT_MAX);
     }
+    if (!fits) total = 0;
     count += total;
     head += m;
     __threadfence_block();
@@ -171,7 +181,7 @@ __global__ void __launch_bounds__(256) ms_wave_check_kernel(MsWaveArgs w) {
   const int WW = W * W;
   const int mylab = kMsTmpBase + k;
   const int count = w.wave[kWvCount + k];
-  const int* inl = w.slot_inliers + (size_t)k * w.slot_stride;
+  const int* inl = ms_slot(w, k);
   const int centre0 = a.seeds[w.wave[kWvPos + k]].centre;
   const long long pairs = (long long)(count + 1) * WW;
   bool bad = false;
@@ -187,7 +197,7 @@ __global__ void __launch_bounds__(256) ms_wave_check_kernel(MsWaveArgs w) {
 // Undo of rank k by the whole CTA: its cells that still carry ITS label become kUnlabeled (cells a
 // lower rank took keep that rank's label).
 __device__ __forceinline__ void ms_wave_undo(const MsWaveArgs& w, int k, int count) {
-  const int* inl = w.slot_inliers + (size_t)k * w.slot_stride;
+  const int* inl = ms_slot(w, k);
   for (int i = threadIdx.x; i < count; i += blockDim.x) atomicCAS(&w.g.labels[inl[i]], kMsTmpBase + k, kUnlabeled);
 }
 
@@ -293,7 +303,7 @@ __global__ void __launch_bounds__(256) ms_wave_finalize_kernel(MsWaveArgs w) {
   if (q >= w.wave[kWvNAcc]) return;
   const int k = w.wave[kWvAccRank + q], base = w.wave[kWvAccBase + q], label = w.wave[kWvAccLabel + q];
   const int count = w.wave[kWvCount + k];
-  const int* inl = w.slot_inliers + (size_t)k * w.slot_stride;
+  const int* inl = ms_slot(w, k);
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
     const int n = inl[i];
     w.g.labels[n] = label;

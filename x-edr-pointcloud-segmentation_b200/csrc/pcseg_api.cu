@@ -7,10 +7,13 @@
 #include "../../include/pcseg_b200.h"
 
 #include <algorithm>
+#include <chrono>
 #include <climits>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <iterator>
+#include <map>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -47,20 +50,92 @@ constexpr int kWave2Block = PCSEG_WAVE2_BLOCK;  // planar fast path (grow_planar
 constexpr int kWaveBlock = PCSEG_WAVE_BLOCK;  // planar fast path (grow_planar_wave.cuh): W = kWaveBlock - 32 entries per window
 constexpr int kInvCap = 4096;
 
+// Device memory of the calls' temporaries comes from a per-device cache: the single-cloud entry
+// points (mean shift, unorganized clustering, sort) take a dozen buffers per call, and
+// cudaMalloc / cudaFree of hundreds of MB cost milliseconds each (measured on C5: 20 - 60 ms of a
+// 110 ms call, varying from box to box).  A returned block is kept (up to PCSEG_POOL_MB, default
+// 8192, per device) and handed to the next request of about its size.  Returning a block
+// synchronises the device first -- what cudaFree did implicitly -- so a block is never reused
+// while work that reads it is in flight.  The cache is emptied when the last context of the device
+// is destroyed.
+struct DevPool {
+  static constexpr int kMaxDev = 64;
+  std::mutex mu;
+  std::multimap<size_t, void*> blocks[kMaxDev];
+  size_t held[kMaxDev] = {};
+  int live_ctx[kMaxDev] = {};
+  static size_t limit() {
+    static const size_t v = [] {
+      const char* e = getenv("PCSEG_POOL_MB");
+      return (size_t)(e ? std::max(0ll, atoll(e)) : 8192ll) << 20;
+    }();
+    return v;
+  }
+  static int device() {
+    int d = 0;
+    if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= kMaxDev) { cudaGetLastError(); return -1; }
+    return d;
+  }
+  void trim(int d, size_t keep) {   // mu held
+    while (held[d] > keep && !blocks[d].empty()) {
+      auto it = std::prev(blocks[d].end());
+      held[d] -= it->first;
+      cudaFree(it->second);
+      blocks[d].erase(it);
+    }
+  }
+  cudaError_t get(size_t need, void** p, size_t* got) {
+    need = need < ((size_t)1 << 20) ? (need + 511) & ~(size_t)511 : (need + (((size_t)1 << 21) - 1)) & ~(((size_t)1 << 21) - 1);
+    const int d = device();
+    if (d >= 0) {
+      std::lock_guard<std::mutex> lock(mu);
+      auto it = blocks[d].lower_bound(need);
+      if (it != blocks[d].end() && it->first <= need + need / 4 + ((size_t)1 << 20)) {
+        *p = it->second; *got = it->first;
+        held[d] -= it->first;
+        blocks[d].erase(it);
+        return cudaSuccess;
+      }
+    }
+    cudaError_t e = cudaMalloc(p, need);
+    if (e == cudaErrorMemoryAllocation && d >= 0) {   // give the cached blocks back and try again
+      cudaGetLastError();
+      { std::lock_guard<std::mutex> lock(mu); trim(d, 0); }
+      e = cudaMalloc(p, need);
+    }
+    *got = need;
+    return e;
+  }
+  void put(void* p, size_t bytes) {
+    const int d = device();
+    cudaDeviceSynchronize();
+    std::lock_guard<std::mutex> lock(mu);
+    if (d < 0 || live_ctx[d] <= 0 || bytes > limit() / 2) { cudaFree(p); return; }
+    blocks[d].emplace(bytes, p);
+    held[d] += bytes;
+    trim(d, limit());
+  }
+  void context_created(int d) { std::lock_guard<std::mutex> lock(mu); if (d >= 0 && d < kMaxDev) ++live_ctx[d]; }
+  void context_destroyed(int d) {
+    std::lock_guard<std::mutex> lock(mu);
+    if (d < 0 || d >= kMaxDev) return;
+    if (--live_ctx[d] <= 0) { live_ctx[d] = 0; trim(d, 0); }
+  }
+};
+DevPool g_pool;
+
 struct DevBuf {
   void* p = nullptr;
   size_t bytes = 0;
   cudaError_t ensure(size_t need) {
     if (need <= bytes) return cudaSuccess;
-    if (p) cudaFree(p);
-    p = nullptr;
-    bytes = 0;
-    cudaError_t e = cudaMalloc(&p, need);
-    if (e == cudaSuccess) bytes = need;
+    release();
+    cudaError_t e = g_pool.get(need, &p, &bytes);
+    if (e != cudaSuccess) { p = nullptr; bytes = 0; }
     return e;
   }
   void release() {
-    if (p) cudaFree(p);
+    if (p) g_pool.put(p, bytes);
     p = nullptr;
     bytes = 0;
   }
@@ -800,6 +875,7 @@ int pcseg_create(int device, pcseg_ctx** out) {
     delete c;
     return PCSEG_ERR_CUDA;
   }
+  g_pool.context_created(device);
   *out = c;
   return PCSEG_OK;
 }
@@ -813,6 +889,7 @@ void pcseg_destroy(pcseg_ctx* c) {
   if (c->copy_in) cudaStreamDestroy(c->copy_in);
   if (c->copy_out) cudaStreamDestroy(c->copy_out);
   if (c->stream) cudaStreamDestroy(c->stream);
+  g_pool.context_destroyed(c->device);
   delete c;
 }
 
@@ -1384,6 +1461,19 @@ int scan64(pcseg_ctx* c, const unsigned long long* v, int n, unsigned long long*
   return PCSEG_OK;
 }
 
+// PCSEG_MS_DEBUG=1: wall time of the phases of a mean-shift call on stderr (synchronises at every mark)
+struct MsPhaseClock {
+  bool on = getenv("PCSEG_MS_DEBUG") != nullptr;
+  std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+  void mark(pcseg_ctx* c, const char* what) {
+    if (!on) return;
+    cudaStreamSynchronize(c->stream);
+    const auto t1 = std::chrono::steady_clock::now();
+    fprintf(stderr, "ms phase %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+    t0 = t1;
+  }
+};
+
 // The sort of ps/mean_shift_segmentation.h:262-280 on the device (msort.cuh): intensities of the n
 // cells (< 0: not a valid seed) -> cell ids of the valid seeds in the order the reference's
 // std::sort (sort_mode 0, libstdc++ introsort replayed level by level) or std::stable_sort
@@ -1488,6 +1578,8 @@ int mean_shift_finish(pcseg_ctx* c, const float* xyz_dev, int rows, int cols, co
                       const pcseg_cluster_config* cfg, int id_offset, int sort_mode, int* labels_dev,
                       pcseg_regions** out) {
   const size_t N = (size_t)rows * cols;
+  MsPhaseClock clk;
+  clk.mark(c, "before finish (modes)");
   // (1) intensities of the valid seeds, in seed order (ascending cloud index, :219-229,267-274)
   DevBuf d_int, d_cells;
   CU_TRY(c, d_int.ensure(N * sizeof(float)));
@@ -1501,6 +1593,7 @@ int mean_shift_finish(pcseg_ctx* c, const float* xyz_dev, int rows, int cols, co
     if (rc) return rc;
   }
   d_int.release();
+  clk.mark(c, "intensity + sort");
   pcseg_regions* res = new pcseg_regions();
   if (S == 0) { *out = res; return PCSEG_OK; }
   struct ResGuard {  // the result reaches the caller only on success (no live handle beside an error status)
@@ -1530,6 +1623,7 @@ int mean_shift_finish(pcseg_ctx* c, const float* xyz_dev, int rows, int cols, co
   g.alive = d_alive.as<unsigned char>();
   c->launches += 2;
   int h_out[4] = {0, 0, 0, 0};
+  clk.mark(c, "growth buffers + gather");
   const char* ms_mode = getenv("PCSEG_MS_GROWTH");
   if (ms_mode && strcmp(ms_mode, "serial") == 0) {
     // growth in rounds (meanshift_grow.cuh): the serial CTA accepts a few regions, the filter kernel
@@ -1553,16 +1647,18 @@ int mean_shift_finish(pcseg_ctx* c, const float* xyz_dev, int rows, int cols, co
     }
   } else {
     // waves of regions grown at the same time and resolved in order (meanshift_wave.cuh)
-    const int kmax = (int)std::max<size_t>(1, std::min<size_t>(std::min<size_t>(kMsWaveMax, (size_t)S),
-                                                               ((size_t)3 << 30) / (N * sizeof(int))));
+    const int kmax = (int)std::min<size_t>(kMsWaveMax, (size_t)S);
+    size_t cap_cells = (size_t)1 << 21;
+    if (const char* e = getenv("PCSEG_MS_SLOT_CAP")) cap_cells = (size_t)std::max(1, atoi(e));   // tests: force slot overflows
+    const int slot_cap = (int)std::min<size_t>(N, cap_cells);
     DevBuf d_slots, d_wave;
-    CU_TRY(c, d_slots.ensure((size_t)kmax * N * sizeof(int)));
+    CU_TRY(c, d_slots.ensure((N + (size_t)(kmax - 1) * slot_cap) * sizeof(int)));
     CU_TRY(c, d_wave.ensure(kWvInts * sizeof(int)));
     CU_TRY(c, cudaMemsetAsync(d_wave.p, 0, kWvInts * sizeof(int), c->stream));
     MsWaveArgs w;
-    w.g = g; w.slot_inliers = d_slots.as<int>(); w.slot_stride = N; w.wave = d_wave.as<int>();
+    w.g = g; w.slot_inliers = d_slots.as<int>(); w.slot0 = N; w.slot_cap = slot_cap; w.wave = d_wave.as<int>();
     int h_wave[4] = {0, 0, 0, 0};
-    int pos = 0, n_reg = 0, n_inl = 0, r_applied = 0, K = std::min(16, kmax);
+    int pos = 0, n_reg = 0, n_inl = 0, r_applied = 0, K = std::min(64, kmax);
     bool first = true;
     while (pos < S) {
       if (first || n_reg > r_applied) {   // dead-mode flags up to date before the candidates are picked
@@ -1586,10 +1682,14 @@ int mean_shift_finish(pcseg_ctx* c, const float* xyz_dev, int rows, int cols, co
       const int n_cand = h_wave[kWvNCand], stop = h_wave[kWvStop];
       if (n_cand == 0) break;   // no live mode left
       if (h_out[3] <= pos && stop == 0) { c->last_error = "mean-shift growth made no progress"; return PCSEG_ERR_CUDA; }
+      if (getenv("PCSEG_MS_DEBUG"))
+        fprintf(stderr, "ms wave: pos %d K %d cand %d stop %d accepted %d regions %d\n", pos, K, n_cand, stop,
+                h_wave[kWvNAcc], h_out[0]);
       pos = h_out[3]; n_reg = h_out[0]; n_inl = h_out[2];
       K = stop == n_cand ? std::min(2 * K, kmax) : std::max(K / 2, std::min(4, kmax));
     }
   }
+  clk.mark(c, "growth");
   d_alive.release();
   const int R = h_out[0], total = h_out[2];
   std::vector<MsRegionMeta> meta(R);
@@ -1602,7 +1702,9 @@ int mean_shift_finish(pcseg_ctx* c, const float* xyz_dev, int rows, int cols, co
     res->label_ids.push_back(meta[r].label_id);
     res->seed_points.insert(res->seed_points.end(), meta[r].seed, meta[r].seed + 3);
   }
+  clk.mark(c, "results to host");
   d_cells.release(); d_seeds.release(); d_claim.release(); d_inl.release(); d_meta.release(); d_out.release();
+  clk.mark(c, "free");
   if (h_out[1]) { c->last_error = "mean-shift region table overflow"; return PCSEG_ERR_CAPACITY; }
   guard.ok = true;
   return PCSEG_OK;
@@ -1668,6 +1770,7 @@ int pcseg_mean_shift(pcseg_ctx* c, const float* xyz, int rows, int cols, const p
   if (st) return st;
   cudaSetDevice(c->device);
   const size_t N = (size_t)rows * cols;
+  MsPhaseClock clk;
   DevBuf sx, sl, sm;
   const void* xyz_dev;
   if ((st = to_device(c, xyz, N * 3 * sizeof(float), &sx, &xyz_dev))) return st;
@@ -1678,6 +1781,7 @@ int pcseg_mean_shift(pcseg_ctx* c, const float* xyz, int rows, int cols, const p
     lab_dev = (int*)sl.p;
   }
   if (sm.ensure(N * sizeof(ModeRecord)) != cudaSuccess) { sx.release(); sl.release(); return PCSEG_ERR_CUDA; }
+  clk.mark(c, "inputs to device + alloc");
   MeanShiftArgs a;
   a.xyz = (const float*)xyz_dev; a.labels = lab_dev; a.rows = rows; a.cols = cols;
   a.iterations = iterations; a.cell_begin = 0; a.cell_end = (int)N; a.modes = sm.as<ModeRecord>();
@@ -1689,7 +1793,9 @@ int pcseg_mean_shift(pcseg_ctx* c, const float* xyz, int rows, int cols, const p
     st = from_device(c, labels, lab_dev, N * sizeof(int));
     if (st == PCSEG_OK && cudaStreamSynchronize(c->stream) != cudaSuccess) st = PCSEG_ERR_CUDA;
   }
+  clk.mark(c, "labels to host");
   sx.release(); sl.release(); sm.release();
+  clk.mark(c, "free inputs");
   return st;
 }
 
