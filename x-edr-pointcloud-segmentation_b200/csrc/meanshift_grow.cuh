@@ -78,6 +78,7 @@ struct MsGrowArgs {
   int rcap;
   int* out;              // [0] = number of regions, [1] = error flags, [2] = total inliers, [3] = resume position
   unsigned char* alive;  // n_seeds flags: 0 = known dead (ms_filter_kernel)
+  int* first_alive;      // nullable: ms_filter_kernel lowers it to the first position it leaves alive
 };
 
 constexpr int kMsRegionsPerRound = 8;
@@ -123,6 +124,10 @@ __global__ void ms_filter_kernel(MsGrowArgs a, int pos0, int r0, int r1) {
       if (!any) alive = false;
     }
     if (jl < a.n_seeds && !alive) a.alive[j] = 0;
+    if (a.first_alive) {   // first live position (lanes hold consecutive positions: the lowest live lane)
+      const unsigned live = __ballot_sync(0xffffffffu, alive);
+      if (live && (int)(threadIdx.x & 31) == __ffs(live) - 1 && j < *(volatile int*)a.first_alive) atomicMin(a.first_alive, j);
+    }
   }
 }
 

@@ -18,14 +18,24 @@
 //     Then it never read or wrote a cell a lower rank touched, i.e. it grew on exactly the labels
 //     the serial walk would have shown it, provided every lower rank resolved to what is in the
 //     labels -- which the resolver guarantees by stopping at the first rank it cannot resolve.
-//   * Resolver, rank by rank (ms_wave_resolve_kernel, one CTA): suppressed by a region accepted
-//     earlier in this wave (:312-322) -> undone; valid -> accepted if count >= min_region_inliers,
-//     else undone (:323-327); invalid -> undone, then the "dead mode" test of ms_filter_kernel on the
-//     labels as they now are: a dead mode is a no-op in the serial walk, so the walk goes on; a live
-//     one has to be grown again and becomes rank 0 of the next wave, and every higher rank is undone.
-//     Rank 0 has no lower rank, so every wave resolves at least one mode.
-//   * ms_wave_finalize_kernel writes the final label ids (acceptance order = rank order) and packs
-//     the inlier lists of the accepted regions behind one another.
+//   * Resolution in rank order: suppressed by a region accepted earlier in this wave (:312-322) ->
+//     undone; valid -> accepted if count >= min_region_inliers, else undone (:323-327); invalid ->
+//     undone, then the "dead mode" test of ms_filter_kernel on the labels as they now are: a dead
+//     mode is a no-op in the serial walk, so the walk goes on; a live one has to be grown again and
+//     becomes rank 0 of the next wave, and every higher rank is undone.  Rank 0 has no lower rank,
+//     so every wave resolves at least one mode.  Done by four small kernels instead of one serial
+//     CTA (its undo loops and dependent global reads took as long as half the growth):
+//       ms_wave_plan_kernel    the walk itself on shared-memory copies, ASSUMING every invalid rank
+//                              is dead: states, provisional acceptance order, ids, list offsets;
+//       ms_wave_undo_kernel    all ranks that are not accepted, undone in parallel (undos only
+//                              touch the rank's own temporary label, so they commute);
+//       ms_wave_dead_kernel    the dead test of every invalid rank, one warp each, on those labels
+//                              (cells of higher ranks count as unlabeled: they are not there yet in
+//                              the serial walk); the lowest live one is the STOP rank;
+//       ms_wave_commit_kernel  accepted ranks below the stop get their final ids and their inlier
+//                              lists packed behind one another; accepted ranks behind it are undone.
+//     The dead test of rank k is evaluated as if all lower invalid ranks were no-ops; if one of
+//     them is not, the stop lies below k and k's outcome is discarded anyway.
 //
 // Regions that do not touch (the usual case: the growth rule stops at depth gaps, NaN borders and
 // 0.2 m jumps) resolve a whole wave at once.  Caller labels must be below kMsTmpBase.
@@ -48,14 +58,18 @@ struct MsWaveArgs {
 // layout of MsWaveArgs::wave (ints)
 constexpr int kWvNCand = 0;                       // candidates of this wave
 constexpr int kWvStop = 1;                        // first unresolved rank (== n_cand: all resolved)
-constexpr int kWvNAcc = 2;                        // regions accepted in this wave
+constexpr int kWvNAcc = 2;                        // regions accepted in this wave if nothing stops it
+constexpr int kWvFirstAlive = 3;                  // ms_filter_kernel: first live position
+constexpr int kWvTotReg = 4;                      // regions / packed inliers after the whole wave
+constexpr int kWvTotBase = 5;
 constexpr int kWvPos = 8;                         // [kMsWaveMax] position of rank k in the sorted modes
 constexpr int kWvCount = kWvPos + kMsWaveMax;     // [kMsWaveMax] inliers of rank k
 constexpr int kWvConflict = kWvCount + kMsWaveMax;
-constexpr int kWvAccRank = kWvConflict + kMsWaveMax;   // [kMsWaveMax] accepted: rank
-constexpr int kWvAccBase = kWvAccRank + kMsWaveMax;    //   inlier_begin
-constexpr int kWvAccLabel = kWvAccBase + kMsWaveMax;   //   final label id
-constexpr int kWvInts = kWvAccLabel + kMsWaveMax;
+constexpr int kWvState = kWvConflict + kMsWaveMax;     // kMsAccepted ...
+constexpr int kWvRegBefore = kWvState + kMsWaveMax;    // regions accepted before rank k
+constexpr int kWvBaseBefore = kWvRegBefore + kMsWaveMax;  // inliers packed before rank k
+constexpr int kWvInts = kWvBaseBefore + kMsWaveMax;
+enum { kMsAccepted = 0, kMsRejected = 1, kMsSuppressed = 2, kMsInvalid = 3, kMsOverCap = 4 };
 
 __device__ __forceinline__ int* ms_slot(const MsWaveArgs& w, int k) {
   return w.slot_inliers + (k == 0 ? (size_t)0 : w.slot0 + (size_t)(k - 1) * (size_t)w.slot_cap);
@@ -67,7 +81,8 @@ __global__ void __launch_bounds__(1024) ms_wave_select_kernel(MsWaveArgs w, int 
   __shared__ int s_warp[33];
   const int t = threadIdx.x;
   int found = 0;
-  for (int pos = pos0; pos < w.g.n_seeds && found < want; pos += 1024) {
+  const int fa = w.wave[kWvFirstAlive];   // everything below it is dead (ms_filter_kernel)
+  for (int pos = max(pos0, min(fa, w.g.n_seeds)); pos < w.g.n_seeds && found < want; pos += 1024) {
     const int j = pos + t;
     const bool alive = j < w.g.n_seeds && w.g.alive[j] != 0;
     if (!__syncthreads_or(alive)) continue;
@@ -194,120 +209,139 @@ __global__ void __launch_bounds__(256) ms_wave_check_kernel(MsWaveArgs w) {
   if (bad) w.wave[kWvConflict + k] = 1;
 }
 
-// Undo of rank k by the whole CTA: its cells that still carry ITS label become kUnlabeled (cells a
-// lower rank took keep that rank's label).
-__device__ __forceinline__ void ms_wave_undo(const MsWaveArgs& w, int k, int count) {
-  const int* inl = ms_slot(w, k);
-  for (int i = threadIdx.x; i < count; i += blockDim.x) atomicCAS(&w.g.labels[inl[i]], kMsTmpBase + k, kUnlabeled);
-}
 
-// The serial walk over the ranks of the wave (one CTA).  n_regions0 / base0: regions accepted and
-// inliers packed before this wave.  out[] as ms_grow_kernel.
-__global__ void __launch_bounds__(1024) ms_wave_resolve_kernel(MsWaveArgs w, int n_regions0, int base0) {
-  __shared__ float s_acc[3 * kMsWaveMax];   // modes of the regions accepted in this wave
-  __shared__ int s_flag;
+// The walk over the ranks on shared-memory copies (one CTA of kMsWaveMax threads), under the
+// assumption that every invalid rank is dead.  n_regions0 / base0: accepted before this wave.
+__global__ void __launch_bounds__(kMsWaveMax) ms_wave_plan_kernel(MsWaveArgs w, int n_regions0, int base0) {
+  __shared__ float s_mode[3 * kMsWaveMax];   // mode of rank k
+  __shared__ float s_acc[3 * kMsWaveMax];    // modes of the regions accepted so far in this wave
+  __shared__ int s_cnt[kMsWaveMax], s_conf[kMsWaveMax], s_state[kMsWaveMax], s_reg[kMsWaveMax], s_base[kMsWaveMax];
   const MsGrowArgs& a = w.g;
   const int t = threadIdx.x;
-  const int rows = a.rows, cols = a.cols;
-  const int W = 2 * a.half_window + 1;
-  const int WW = W * W;
   const int n_cand = w.wave[kWvNCand];
+  if (t < n_cand) {
+    const MsSeedRec r = a.seeds[w.wave[kWvPos + t]];
+    s_mode[3 * t] = r.mx; s_mode[3 * t + 1] = r.my; s_mode[3 * t + 2] = r.mz;
+    s_cnt[t] = w.wave[kWvCount + t];
+    s_conf[t] = w.wave[kWvConflict + t];
+  }
+  __syncthreads();
   int n_regions = n_regions0, base = base0, n_acc = 0;
-  int k = 0;
-  for (; k < n_cand; ++k) {
-    const int pos = w.wave[kWvPos + k];
-    const int count = w.wave[kWvCount + k];
-    const bool conflict = w.wave[kWvConflict + k] != 0;
-    const MsSeedRec cur = a.seeds[pos];
+  for (int k = 0; k < n_cand; ++k) {
     // suppression by a region accepted earlier in this wave, :312-322 (earlier waves: ms_filter_kernel)
     bool sup = false;
     if (t < n_acc) {
-      const V3 d{cur.mx - s_acc[3 * t], cur.my - s_acc[3 * t + 1], cur.mz - s_acc[3 * t + 2]};
+      const V3 d{s_mode[3 * k] - s_acc[3 * t], s_mode[3 * k + 1] - s_acc[3 * t + 1], s_mode[3 * k + 2] - s_acc[3 * t + 2]};
       sup = (double)vsqn(d) < 1.0;
     }
-    if (__syncthreads_or(sup)) {
-      ms_wave_undo(w, k, count);
-      if (t == 0) a.alive[pos] = 0;
-      __threadfence();
-      __syncthreads();
-      continue;
-    }
-    if (!conflict) {
-      if (count >= a.min_inliers) {               // CheckAndFinalize, ps/cluster_region.h:111-116
-        if (n_regions < a.rcap) {
-          if (t == 0) {
-            MsRegionMeta mt;
-            mt.inlier_begin = base; mt.inlier_count = count; mt.label_id = n_regions + a.id_offset;  // :288-289
-            mt.seed[0] = cur.mx; mt.seed[1] = cur.my; mt.seed[2] = cur.mz;
-            a.meta[n_regions] = mt;
-            w.wave[kWvAccRank + n_acc] = k;
-            w.wave[kWvAccBase + n_acc] = base;
-            w.wave[kWvAccLabel + n_acc] = mt.label_id;
-            s_acc[3 * n_acc] = cur.mx; s_acc[3 * n_acc + 1] = cur.my; s_acc[3 * n_acc + 2] = cur.mz;
-            a.alive[pos] = 0;
-          }
-          ++n_regions; ++n_acc; base += count;
-        } else {
-          if (t == 0) { atomicOr(&a.out[1], kErrRegionCap); a.alive[pos] = 0; }
-          ms_wave_undo(w, k, count);
-        }
-      } else {
-        ms_wave_undo(w, k, count);                // :323-327
-        if (t == 0) a.alive[pos] = 0;
-      }
-      __threadfence();
-      __syncthreads();
-      continue;
-    }
-    // invalid: undo, then decide whether the mode is a no-op on the labels as they are now
-    ms_wave_undo(w, k, count);
-    if (t == 0) s_flag = 0;
-    __threadfence();
-    __syncthreads();
-    {
-      const V3 mm{cur.mx, cur.my, cur.mz};
-      const int crow = cur.centre % rows, ccol = cur.centre / rows;
-      const int mylab = kMsTmpBase + k;
-      for (int s = t; s < WW; s += blockDim.x) {
-        const int rc = crow + s % W - a.half_window, cc = ccol + s / W - a.half_window;
-        if (cc >= 0 && cc < cols && rc >= 0 && rc < rows) {
-          const int n = cc * rows + rc;
-          const int lab = __ldcg(&a.labels[n]);
-          if (lab == kUnlabeled || lab > mylab) {   // higher ranks are not there yet in the serial walk
-            const V3 p = ld3(a.xyz, n);
-            if (!vhasnan(p) && !((double)vsqn(vsub(p, mm)) > 1.0)) s_flag = 1;
-          }
-        }
-      }
+    sup = __syncthreads_or(sup);
+    int state;
+    if (sup) state = kMsSuppressed;
+    else if (s_conf[k]) state = kMsInvalid;
+    else if (s_cnt[k] < a.min_inliers) state = kMsRejected;    // CheckAndFinalize, ps/cluster_region.h:111-116
+    else if (n_regions >= a.rcap) state = kMsOverCap;
+    else state = kMsAccepted;
+    if (t == 0) { s_state[k] = state; s_reg[k] = n_regions; s_base[k] = base; }
+    if (state == kMsAccepted) {
+      if (t == 0) { s_acc[3 * n_acc] = s_mode[3 * k]; s_acc[3 * n_acc + 1] = s_mode[3 * k + 1]; s_acc[3 * n_acc + 2] = s_mode[3 * k + 2]; }
+      ++n_acc; ++n_regions; base += s_cnt[k];
     }
     __syncthreads();
-    const bool live = s_flag != 0;
-    __syncthreads();
-    if (live) break;                 // has to be grown again: rank 0 of the next wave
-    if (t == 0) a.alive[pos] = 0;    // dead: a no-op of the serial walk
   }
-  // ranks behind the stop are undone (rank `k` itself already is)
-  for (int j = k + 1; j < n_cand; ++j) ms_wave_undo(w, j, w.wave[kWvCount + j]);
+  if (t < n_cand) {
+    w.wave[kWvState + t] = s_state[t];
+    w.wave[kWvRegBefore + t] = s_reg[t];
+    w.wave[kWvBaseBefore + t] = s_base[t];
+  }
   if (t == 0) {
-    w.wave[kWvStop] = k;
+    w.wave[kWvStop] = n_cand;
     w.wave[kWvNAcc] = n_acc;
-    a.out[0] = n_regions;
-    a.out[2] = base;
-    a.out[3] = k < n_cand ? w.wave[kWvPos + k] : (n_cand > 0 ? w.wave[kWvPos + n_cand - 1] + 1 : a.n_seeds);
+    w.wave[kWvTotReg] = n_regions;
+    w.wave[kWvTotBase] = base;
   }
 }
 
-// Final label ids and packed inlier lists of the regions accepted in the wave.  grid = (blocks, kMsWaveMax).
-__global__ void __launch_bounds__(256) ms_wave_finalize_kernel(MsWaveArgs w) {
-  const int q = blockIdx.y;
-  if (q >= w.wave[kWvNAcc]) return;
-  const int k = w.wave[kWvAccRank + q], base = w.wave[kWvAccBase + q], label = w.wave[kWvAccLabel + q];
+// Undo of a rank: its cells that still carry ITS label become kUnlabeled (cells a lower rank took
+// keep that rank's label).  grid = (blocks, rank).
+__device__ __forceinline__ void ms_wave_undo(const MsWaveArgs& w, int k) {
+  const int* inl = ms_slot(w, k);
   const int count = w.wave[kWvCount + k];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+    atomicCAS(&w.g.labels[inl[i]], kMsTmpBase + k, kUnlabeled);
+}
+__global__ void __launch_bounds__(256) ms_wave_undo_kernel(MsWaveArgs w) {
+  const int k = blockIdx.y;
+  if (k >= w.wave[kWvNCand] || w.wave[kWvState + k] == kMsAccepted) return;
+  ms_wave_undo(w, k);
+}
+
+// Dead test of the invalid ranks (one warp each): the first queue step of the mode finds nothing.
+__global__ void __launch_bounds__(256) ms_wave_dead_kernel(MsWaveArgs w) {
+  const MsGrowArgs& a = w.g;
+  const int k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (k >= w.wave[kWvNCand] || w.wave[kWvState + k] != kMsInvalid) return;
+  const int rows = a.rows, cols = a.cols;
+  const int W = 2 * a.half_window + 1;
+  const int WW = W * W;
+  const MsSeedRec cur = a.seeds[w.wave[kWvPos + k]];
+  const V3 mm{cur.mx, cur.my, cur.mz};
+  const int crow = cur.centre % rows, ccol = cur.centre / rows;
+  const int mylab = kMsTmpBase + k;
+  bool live = false;
+  for (int s = lane; s < WW && !live; s += 32) {
+    const int rc = crow + s % W - a.half_window, cc = ccol + s / W - a.half_window;
+    if (cc >= 0 && cc < cols && rc >= 0 && rc < rows) {
+      const int n = cc * rows + rc;
+      const int lab = a.labels[n];
+      if (lab == kUnlabeled || lab > mylab) {   // higher ranks are not there yet in the serial walk
+        const V3 p = ld3(a.xyz, n);
+        if (!vhasnan(p) && !((double)vsqn(vsub(p, mm)) > 1.0)) live = true;
+      }
+    }
+  }
+  if (__any_sync(0xffffffffu, live) && lane == 0) atomicMin(&w.wave[kWvStop], k);   // has to be grown again
+}
+
+// Final ids + packed inlier lists of the accepted ranks below the stop; undo of those behind it;
+// dead flags; totals.  grid = (blocks, rank).
+__global__ void __launch_bounds__(256) ms_wave_commit_kernel(MsWaveArgs w) {
+  const MsGrowArgs& a = w.g;
+  const int k = blockIdx.y;
+  const int n_cand = w.wave[kWvNCand];
+  const int stop = w.wave[kWvStop];
+  const bool lead = blockIdx.x == 0 && threadIdx.x == 0;
+  if (k == 0 && lead) {
+    a.out[0] = stop < n_cand ? w.wave[kWvRegBefore + stop] : w.wave[kWvTotReg];
+    a.out[2] = stop < n_cand ? w.wave[kWvBaseBefore + stop] : w.wave[kWvTotBase];
+    a.out[3] = stop < n_cand ? w.wave[kWvPos + stop] : (n_cand > 0 ? w.wave[kWvPos + n_cand - 1] + 1 : a.n_seeds);
+  }
+  if (k >= n_cand) return;
+  const int state = w.wave[kWvState + k];
+  if (k >= stop) {
+    if (state == kMsAccepted) ms_wave_undo(w, k);
+    return;
+  }
+  const int pos = w.wave[kWvPos + k];
+  if (lead) {
+    a.alive[pos] = 0;
+    if (state == kMsOverCap) atomicOr(&a.out[1], kErrRegionCap);
+  }
+  if (state != kMsAccepted) return;
+  const int count = w.wave[kWvCount + k], base = w.wave[kWvBaseBefore + k];
+  const int label = w.wave[kWvRegBefore + k] + a.id_offset;   // :288-289
+  if (lead) {
+    const MsSeedRec cur = a.seeds[pos];
+    MsRegionMeta mt;
+    mt.inlier_begin = base; mt.inlier_count = count; mt.label_id = label;
+    mt.seed[0] = cur.mx; mt.seed[1] = cur.my; mt.seed[2] = cur.mz;
+    a.meta[w.wave[kWvRegBefore + k]] = mt;
+  }
   const int* inl = ms_slot(w, k);
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
     const int n = inl[i];
-    w.g.labels[n] = label;
-    w.g.inliers[base + i] = n;
+    a.labels[n] = label;
+    a.inliers[base + i] = n;
   }
 }
 

@@ -1616,7 +1616,7 @@ int mean_shift_finish(pcseg_ctx* c, const float* xyz_dev, int rows, int cols, co
   g.xyz = xyz_dev; g.labels = labels_dev; g.claim = d_claim.as<int>(); g.seeds = d_seeds.as<MsSeedRec>();
   g.n_seeds = S; g.rows = rows; g.cols = cols; g.half_window = cfg->half_search_window;
   g.min_inliers = cfg->min_region_inliers; g.id_offset = id_offset; g.inliers = d_inl.as<int>();
-  g.meta = d_meta.as<MsRegionMeta>(); g.rcap = rcap; g.out = d_out.as<int>();
+  g.meta = d_meta.as<MsRegionMeta>(); g.rcap = rcap; g.out = d_out.as<int>(); g.first_alive = nullptr;
   DevBuf d_alive;
   CU_TRY(c, d_alive.ensure((size_t)S));
   CU_TRY(c, cudaMemsetAsync(d_alive.p, 1, (size_t)S, c->stream));
@@ -1656,6 +1656,7 @@ int mean_shift_finish(pcseg_ctx* c, const float* xyz_dev, int rows, int cols, co
     CU_TRY(c, d_wave.ensure(kWvInts * sizeof(int)));
     CU_TRY(c, cudaMemsetAsync(d_wave.p, 0, kWvInts * sizeof(int), c->stream));
     MsWaveArgs w;
+    g.first_alive = d_wave.as<int>() + kWvFirstAlive;
     w.g = g; w.slot_inliers = d_slots.as<int>(); w.slot0 = N; w.slot_cap = slot_cap; w.wave = d_wave.as<int>();
     int h_wave[4] = {0, 0, 0, 0};
     int pos = 0, n_reg = 0, n_inl = 0, r_applied = 0, K = std::min(64, kmax);
@@ -1663,7 +1664,8 @@ int mean_shift_finish(pcseg_ctx* c, const float* xyz_dev, int rows, int cols, co
     while (pos < S) {
       if (first || n_reg > r_applied) {   // dead-mode flags up to date before the candidates are picked
         const unsigned fgrid = (unsigned)std::min<size_t>(((size_t)(S - pos) + 255) / 256, (size_t)148 * 8);
-        ms_filter_kernel<<<fgrid, 256, 0, c->stream>>>(g, pos, r_applied, n_reg);
+        CU_TRY(c, cudaMemsetAsync(w.g.first_alive, 0x7f, sizeof(int), c->stream));   // "none" until the filter finds one
+        ms_filter_kernel<<<fgrid, 256, 0, c->stream>>>(w.g, pos, r_applied, n_reg);
         r_applied = n_reg;
         first = false;
         ++c->launches;
@@ -1671,9 +1673,11 @@ int mean_shift_finish(pcseg_ctx* c, const float* xyz_dev, int rows, int cols, co
       ms_wave_select_kernel<<<1, 1024, 0, c->stream>>>(w, pos, K);
       ms_wave_grow_kernel<<<K, kMsGrowBlock, 0, c->stream>>>(w);
       ms_wave_check_kernel<<<dim3(64, K), 256, 0, c->stream>>>(w);
-      ms_wave_resolve_kernel<<<1, 1024, 0, c->stream>>>(w, n_reg, n_inl);
-      ms_wave_finalize_kernel<<<dim3(32, K), 256, 0, c->stream>>>(w);
-      c->launches += 5;
+      ms_wave_plan_kernel<<<1, kMsWaveMax, 0, c->stream>>>(w, n_reg, n_inl);
+      ms_wave_undo_kernel<<<dim3(16, K), 256, 0, c->stream>>>(w);
+      ms_wave_dead_kernel<<<(K + 7) / 8, 256, 0, c->stream>>>(w);
+      ms_wave_commit_kernel<<<dim3(16, K), 256, 0, c->stream>>>(w);
+      c->launches += 7;
       CU_TRY(c, cudaGetLastError());
       CU_TRY(c, cudaMemcpyAsync(h_out, d_out.p, sizeof(h_out), cudaMemcpyDeviceToHost, c->stream));
       CU_TRY(c, cudaMemcpyAsync(h_wave, d_wave.p, sizeof(h_wave), cudaMemcpyDeviceToHost, c->stream));
