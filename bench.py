@@ -274,7 +274,7 @@ def run_c5(args, rank, local_rank, world):
             d_lab.copy_(host_lab, non_blocking=True)
         t0 = time.perf_counter()
         labels, regs = parallel.sharded_mean_shift(ctx, d_xyz, rows, cols, d_lab, rank, world, iterations=iters,
-                                                   labels_out=out_lab if e2e else None)
+                                                   labels_out=out_lab if e2e else None, labels_on_device=not e2e)
         state["t_ms"] = (time.perf_counter() - t0) * 1e3
         if rank == 0:
             state["regions"], state["labels"] = regs, labels

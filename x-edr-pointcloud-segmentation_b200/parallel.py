@@ -60,11 +60,13 @@ def sharded_mean_shift_modes(modes_fn, n_cells, rank, world, group=None, device=
 
 
 def sharded_mean_shift(ctx, xyz_dev, rows, cols, labels_dev, rank, world, cfg=None, iterations=5,
-                       id_offset=0, sort_mode=0, group=None, grow_on_all_ranks=False, labels_out=None):
+                       id_offset=0, sort_mode=0, group=None, grow_on_all_ranks=False, labels_out=None,
+                       labels_on_device=False):
     """SlidingMeanShift of one large cloud with the seed cells sharded over the
     ranks.  xyz_dev / labels_dev: torch CUDA tensors (replicated on every rank).
     Returns (labels numpy, regions) on rank 0 (on every rank if
-    grow_on_all_ranks), else (None, None)."""
+    grow_on_all_ranks), else (None, None).  labels_out: a pinned host tensor to receive the grid;
+    labels_on_device: return the CUDA tensor instead of a host copy."""
     import ctypes as C
     import torch
     import pcseg
@@ -94,4 +96,6 @@ def sharded_mean_shift(ctx, xyz_dev, rows, cols, labels_dev, rank, world, cfg=No
     if labels_out is not None:   # caller's (pinned) host tensor
         labels_out.copy_(labels)
         return labels_out.numpy(), regs
+    if labels_on_device:         # the label grid stays in HBM (a torch tensor)
+        return labels, regs
     return labels.cpu().numpy(), regs
