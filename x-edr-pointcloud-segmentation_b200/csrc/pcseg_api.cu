@@ -1824,7 +1824,7 @@ int pcseg_cluster_unorganized(pcseg_ctx* c, const float* xyz, int n, const pcseg
   size_t cap = 1024;
   while (cap < 2 * (size_t)n) cap <<= 1;
   DevBuf d_keys, d_head, d_next, d_slot, d_parent, d_count, d_v, d_incl, d_tiles, d_ord, d_rb, d_rc, d_rr,
-      d_idx[2], d_key, d_hist, d_hincl, d_cen, d_box, d_sv, d_sincl, d_cs, d_cb, d_cc;
+      d_idx[2], d_key, d_hist, d_hincl, d_cen, d_box, d_sv, d_sincl, d_cs, d_cb, d_cc, d_cbox;
   DevBuf* all[] = {&sx, &sl, &d_keys, &d_head, &d_next, &d_slot, &d_parent, &d_count, &d_v, &d_incl, &d_tiles, &d_ord,
                    &d_rb, &d_rc, &d_rr, &d_idx[0], &d_idx[1], &d_key, &d_hist, &d_hincl, &d_cen, &d_box,
                    &d_sv, &d_sincl, &d_cs, &d_cb, &d_cc};
@@ -1865,9 +1865,14 @@ int pcseg_cluster_unorganized(pcseg_ctx* c, const float* xyz, int n, const pcseg
     vox_cells_kernel<<<sgrid, 256, 0, st>>>(a, (int)cap, d_sincl.as<unsigned long long>(), d_cs.as<int>(), d_cb.as<int>(), d_cc.as<int>());
     vox_scatter_kernel<<<grid, 256, 0, st>>>(a, d_sincl.as<unsigned long long>(), d_cb.as<int>());
     vox_union_cell_kernel<<<grid, 256, 0, st>>>(a, d_sincl.as<unsigned long long>(), d_cb.as<int>());
-    vox_union_pairs_kernel<<<(unsigned)(((size_t)n_cells * 32 + 255) / 256), 256, 0, st>>>(
-        a, d_sincl.as<unsigned long long>(), d_cs.as<int>(), d_cb.as<int>(), d_cc.as<int>(), n_cells);
-    c->launches += 4;
+    CU_TRY(c, d_cbox.ensure((size_t)n_cells * 24));
+    const unsigned wgrid = (unsigned)(((size_t)n_cells * 32 + 255) / 256);
+    vox_cellbox_kernel<<<wgrid, 256, 0, st>>>(a, d_cb.as<int>(), d_cc.as<int>(), n_cells, d_cbox.as<float>());
+    vox_union_pairs_kernel<true><<<wgrid, 256, 0, st>>>(a, d_sincl.as<unsigned long long>(), d_cs.as<int>(), d_cb.as<int>(),
+                                                        d_cc.as<int>(), n_cells, d_cbox.as<float>());
+    vox_union_pairs_kernel<false><<<wgrid, 256, 0, st>>>(a, d_sincl.as<unsigned long long>(), d_cs.as<int>(), d_cb.as<int>(),
+                                                         d_cc.as<int>(), n_cells, d_cbox.as<float>());
+    c->launches += 6;
   }
   vox_flatten_kernel<<<grid, 256, 0, st>>>(a);
   vox_rootflag_kernel<<<grid, 256, 0, st>>>(a, d_v.as<unsigned long long>());

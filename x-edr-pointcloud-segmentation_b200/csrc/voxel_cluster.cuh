@@ -149,12 +149,54 @@ __global__ void __launch_bounds__(256) vox_union_cell_kernel(VoxArgs a, const un
   if (rep != i) vox_unite(a.parent, i, rep);
 }
 
+// 2b-0: axis-aligned box of the points of every occupied cell (one warp per cell), for the pruning below
+__global__ void __launch_bounds__(256) vox_cellbox_kernel(VoxArgs a, const int* __restrict__ cell_begin,
+                                                          const int* __restrict__ cell_count, int n_cells, float* box) {
+  const unsigned FULL = 0xffffffffu;
+  const int ca = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (ca >= n_cells) return;
+  const int b = cell_begin[ca], n = cell_count[ca];
+  float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+  for (int i = lane; i < n; i += 32) {
+    const V3 p = ld3(a.xyz, a.next[b + i]);
+    lo[0] = fminf(lo[0], p.x); lo[1] = fminf(lo[1], p.y); lo[2] = fminf(lo[2], p.z);
+    hi[0] = fmaxf(hi[0], p.x); hi[1] = fmaxf(hi[1], p.y); hi[2] = fmaxf(hi[2], p.z);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      lo[k] = fminf(lo[k], __shfl_xor_sync(FULL, lo[k], o));
+      hi[k] = fmaxf(hi[k], __shfl_xor_sync(FULL, hi[k], o));
+    }
+  }
+  if (lane < 3) box[6 * ca + lane] = lo[lane];
+  else if (lane < 6) box[6 * ca + lane] = hi[lane - 3];
+}
+
+// squared distance from p to the box [lo, hi] (0 inside)
+__device__ __forceinline__ float vox_box_dist2(const V3& p, const float* lo, const float* hi) {
+  const float dx = fmaxf(fmaxf(lo[0] - p.x, p.x - hi[0]), 0.0f);
+  const float dy = fmaxf(fmaxf(lo[1] - p.y, p.y - hi[1]), 0.0f);
+  const float dz = fmaxf(fmaxf(lo[2] - p.z, p.z - hi[2]), 0.0f);
+  return dx * dx + dy * dy + dz * dz;
+}
+
 // 2b: one warp per occupied cell: the 62 cells of the upper half-space within +-2 (each unordered cell pair
 // is visited once); two cells already in one component are skipped, else their point pairs are tested 32 at a
-// time until the first pair below the radius unites the components
+// time until the first pair below the radius unites the components.  PRUNING (results unchanged: a pair is
+// only ever skipped when it cannot be below the radius, with a 1e-4 margin on r^2 against fp32 rounding):
+// cell pairs whose point boxes are farther apart than the radius, and points of the cell farther than the
+// radius from the other cell's box.  Without it every cell pair that is close but NOT connected (the
+// ground under an object, neighbouring scan rings far out) costs all nA x nB tests: 47 of the 50 ms of C4.
+// NEAR = true: the 13 face / edge / corner neighbours (launched first: they unite most of a surface, so
+// that the second launch, the 49 cells at distance 2, mostly ends at the same-component test).
+template <bool NEAR>
 __global__ void __launch_bounds__(256) vox_union_pairs_kernel(VoxArgs a, const unsigned long long* __restrict__ incl,
                                                               const int* __restrict__ cell_slot, const int* __restrict__ cell_begin,
-                                                              const int* __restrict__ cell_count, int n_cells) {
+                                                              const int* __restrict__ cell_count, int n_cells,
+                                                              const float* __restrict__ box) {
   const unsigned FULL = 0xffffffffu;
   const int ca = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
@@ -164,8 +206,14 @@ __global__ void __launch_bounds__(256) vox_union_pairs_kernel(VoxArgs a, const u
             vz = (int)(keyA & 0x1fffff) - kVoxBias;
   const int bA = cell_begin[ca], nA = cell_count[ca];
   const int repA = a.next[bA];
+  const float r2m = a.r2 * 1.0001f;
+  float loA[3], hiA[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) { loA[k] = box[6 * ca + k]; hiA[k] = box[6 * ca + 3 + k]; }
   for (int o = 63; o < 125; ++o) {   // offsets (dz, dy, dx) lexicographically after (0, 0, 0)
     const int dz = o / 25 - 2, dy = (o / 5) % 5 - 2, dx = o % 5 - 2;
+    const bool near = dz >= -1 && dz <= 1 && dy >= -1 && dy <= 1 && dx >= -1 && dx <= 1;
+    if (near != NEAR) continue;
     const int nx = vx + dx, ny = vy + dy, nz = vz + dz;
     if (nx < -kVoxBias || nx >= kVoxBias || ny < -kVoxBias || ny >= kVoxBias || nz < -kVoxBias || nz >= kVoxBias) continue;
     int sB = -1;
@@ -182,26 +230,51 @@ __global__ void __launch_bounds__(256) vox_union_pairs_kernel(VoxArgs a, const u
     sB = __shfl_sync(FULL, sB, 0);
     if (sB < 0) continue;
     const int cb = (int)(incl[sB] & 0xffffffffull) - 1;
+    float loB[3], hiB[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { loB[k] = box[6 * cb + k]; hiB[k] = box[6 * cb + 3 + k]; }
+    {  // box - box distance
+      float d2 = 0.0f;
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        const float d = fmaxf(fmaxf(loA[k] - hiB[k], loB[k] - hiA[k]), 0.0f);
+        d2 += d * d;
+      }
+      if (d2 > r2m) continue;
+    }
     const int bB = cell_begin[cb], nB = cell_count[cb];
     int same = 0;
     if (lane == 0) same = vox_find(a.parent, repA) == vox_find(a.parent, a.next[bB]);
     if (__shfl_sync(FULL, same, 0)) continue;
     bool done = false;
-    for (int ia = 0; ia < nA && !done; ++ia) {
-      const int pi = a.next[bA + ia];
-      const V3 p = ld3(a.xyz, pi);
-      for (int j0 = 0; j0 < nB && !done; j0 += 32) {
-        const int j = j0 + lane;
-        bool hit = false;
-        int pj = -1;
-        if (j < nB) {
-          pj = a.next[bB + j];
-          hit = vsqn(vsub(ld3(a.xyz, pj), p)) < a.r2;
-        }
-        const unsigned m = __ballot_sync(FULL, hit);
-        if (m) {
-          if (lane == __ffs(m) - 1) vox_unite(a.parent, pi, pj);
-          done = true;
+    for (int i0 = 0; i0 < nA && !done; i0 += 32) {
+      // the points of A that can reach B's box at all, 32 candidates at a time
+      int pi_l = -1;
+      V3 p_l{0.0f, 0.0f, 0.0f};
+      if (i0 + lane < nA) {
+        pi_l = a.next[bA + i0 + lane];
+        p_l = ld3(a.xyz, pi_l);
+        if (vox_box_dist2(p_l, loB, hiB) > r2m) pi_l = -1;
+      }
+      unsigned cand = __ballot_sync(FULL, pi_l >= 0);
+      while (cand && !done) {
+        const int src = __ffs(cand) - 1;
+        cand &= cand - 1u;
+        const int pi = __shfl_sync(FULL, pi_l, src);
+        const V3 p{__shfl_sync(FULL, p_l.x, src), __shfl_sync(FULL, p_l.y, src), __shfl_sync(FULL, p_l.z, src)};
+        for (int j0 = 0; j0 < nB && !done; j0 += 32) {
+          const int j = j0 + lane;
+          bool hit = false;
+          int pj = -1;
+          if (j < nB) {
+            pj = a.next[bB + j];
+            hit = vsqn(vsub(ld3(a.xyz, pj), p)) < a.r2;
+          }
+          const unsigned m = __ballot_sync(FULL, hit);
+          if (m) {
+            if (lane == __ffs(m) - 1) vox_unite(a.parent, pi, pj);
+            done = true;
+          }
         }
       }
     }
