@@ -50,7 +50,16 @@ struct ClusterBand {
   ClusterMeta* meta;    // the band's slice of the temporary region table
   int rcap;
   int* out;             // {regions, inliers, error flags, steps}
+  // component mode (cluster_comp_kernel): the CTA owns ONE connected component of the frame instead of a
+  // band of columns.  Its cells carry the code `unl` (= kCompUnlabeledBase + root) where a cell of the
+  // frame would carry kUnlabeled, so "unlabeled AND mine" is one comparison; seeds are the indices
+  // [idx_lo, idx_hi] in ascending order; the seed of every region is returned in ClusterMeta::label_id.
+  int comp_on;
+  int unl;
+  int idx_lo, idx_hi;
+  const int* comp;      // root of every participating cell: tells whose transient "rejected in this step" mark a cell carries
 };
+constexpr int kCompUnlabeledBase = INT_MIN;   // + root index (< 2^30): far below every other label value
 
 // All cluster regions of frame f, grown by the calling CTA (every thread of the
 // CTA must call).  Used by cluster_grow_kernel and, fused behind a frame's planar
@@ -61,7 +70,7 @@ struct ClusterBand {
 // kClW 64-bit words; claim key = thread * 256 + slot).
 template <int BLOCK, bool H1>
 __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, int id_offset, int* s_warp,
-                                                   const ClusterBand band = ClusterBand{0, 0, 0, nullptr, 0, 0, nullptr, 0, nullptr}) {
+                                                   const ClusterBand band = ClusterBand{0, 0, 0, nullptr, 0, 0, nullptr, 0, nullptr, 0, kUnlabeled, 0, 0, nullptr}) {
   const int tid = threadIdx.x;
   const int rows = a.rows, cols = a.cols;
   const int N = rows * cols;
@@ -79,8 +88,9 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
 
   // seeds are consumed back to front; a band (all-descending seeds only: seeds[k] = N-1-k) owns the
   // positions of its own cells
-  int seed_pos = band.on ? N - band.c_begin * rows : a.n_seeds;
-  const int seed_lo = band.on ? N - band.c_end * rows : 0;
+  int seed_pos = band.comp_on ? N - band.idx_lo : band.on ? N - band.c_begin * rows : a.n_seeds;
+  const int seed_lo = band.comp_on ? N - (band.idx_hi + 1) : band.on ? N - band.c_end * rows : 0;
+  const int unl = band.unl;   // what an unlabeled cell (of this CTA's component) looks like
   int nreg = 0, inl_total = band.on ? band.inl_base : 0, err = 0, steps = 0;
   bool any_failed = false;
 
@@ -96,7 +106,7 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
         int pos = seed_pos - 1 - (tid + k * BLOCK);
         if (pos >= seed_lo && cand < 0) {
           int s = seed_at(a.seeds, N, pos);
-          if (labels[s] == kUnlabeled) {
+          if (labels[s] == unl) {
             V3 p = ld3(xyz, s);
             if (vfinite(p) && (0.0f < a.sq_thr)) cand = pos;
           }
@@ -164,7 +174,7 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
           }
 #pragma unroll
           for (int s = 0; s < 8; ++s) {
-            if (nn[s] >= 0 && (L[s] == kUnlabeled || (L[s] <= kRejBase && (kRejBase - L[s]) < tid))) {
+            if (nn[s] >= 0 && (L[s] == unl || (L[s] <= kRejBase && (kRejBase - L[s]) < tid && (!band.comp_on || band.comp[nn[s]] == band.idx_lo)))) {
               el[0] |= 1ull << s;
               atomicMin(claim + nn[s], tid * kKeyStride + s);
             }
@@ -192,7 +202,7 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
                 }
 #pragma unroll
                 for (int k = 0; k < kG; ++k) {
-                  if (nn[k] >= 0 && (L[k] == kUnlabeled || (L[k] <= kRejBase && (kRejBase - L[k]) < tid))) {
+                  if (nn[k] >= 0 && (L[k] == unl || (L[k] <= kRejBase && (kRejBase - L[k]) < tid && (!band.comp_on || band.comp[nn[k]] == band.idx_lo)))) {
                     el[w] |= 1ull << (g0 + k);
                     atomicMin(claim + nn[k], tid * kKeyStride + s0 + k);
                   }
@@ -203,7 +213,7 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
         }
       }
       __syncthreads();
-      if (mine && !acc) labels[cand] = kUnlabeled;  // ps/cluster_region.h:105
+      if (mine && !acc) labels[cand] = unl;  // ps/cluster_region.h:105
       unsigned long long win[kClW];
 #pragma unroll
       for (int w = 0; w < kClW; ++w) win[w] = 0ull;
@@ -279,7 +289,7 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
     // CheckAndFinalize, ps/cluster_region.h:111-116
     if (ninl >= a.min_inliers) {
       if (nreg < rcap) {
-        if (tid == 0) meta[nreg] = ClusterMeta{base, ninl, label_id};
+        if (tid == 0) meta[nreg] = ClusterMeta{base, ninl, band.comp_on ? seed : label_id};
         ++nreg;
         inl_total += ninl;
       } else {
@@ -295,7 +305,7 @@ __device__ __forceinline__ void cluster_grow_frame(const ClusterArgs& a, int f, 
   }
   // ps/segmentation.h:287-291
   __syncthreads();
-  if (any_failed) {
+  if (any_failed && !band.comp_on) {   // component mode: cluster_comp_restore_kernel does it for the whole frame
     const int i0 = band.on ? band.c_begin * rows : 0, i1 = band.on ? band.c_end * rows : N;
     for (int i = i0 + tid; i < i1; i += BLOCK)
       if (labels[i] == kAlreadyExamedPoint) labels[i] = kUnlabeled;
@@ -360,6 +370,7 @@ __global__ void __launch_bounds__(BLOCK, H1 ? 2 : 1) cluster_band_kernel(Cluster
   band.meta = t.meta + t.m_off[bnd];
   band.rcap = (bnd + 1 < (int)gridDim.x ? t.m_off[bnd + 1] : t.rcap_total) - t.m_off[bnd];
   band.out = t.out + 4 * bnd;
+  band.comp_on = 0; band.unl = kUnlabeled; band.idx_lo = 0; band.idx_hi = 0; band.comp = nullptr;
   cluster_grow_frame<BLOCK, H1>(a, 0, a.id_offset, s_warp, band);   // provisional ids: renumbered by the merge
 }
 

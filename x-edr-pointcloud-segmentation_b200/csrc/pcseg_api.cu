@@ -29,6 +29,7 @@
 #include "msort.cuh"
 #include "voxel_cluster.cuh"
 #include "grow_cluster_wave.cuh"
+#include "grow_cluster_comp.cuh"
 
 using namespace pcseg;
 
@@ -615,6 +616,127 @@ int run_cluster_banded(pcseg_batch* b, const float* xyz_dev, const pcseg_cluster
   return PCSEG_OK;
 }
 
+// One large frame, one CTA per connected component (grow_cluster_comp.cuh).  *used = false: not
+// applicable (fewer than two components that can yield a region) -- the caller takes another path.
+int run_cluster_components(pcseg_batch* b, const float* xyz_dev, const pcseg_cluster_config* cfg, int id_offset, bool* used) {
+  pcseg_ctx* c = b->ctx;
+  cudaStream_t stream = S(b);
+  *used = false;
+  const int rows = b->rows, cols = b->cols, h = cfg->half_search_window;
+  const size_t N = b->N;
+  if (N >= ((size_t)1 << 30)) return PCSEG_OK;
+  ClusterArgs a;
+  int st = make_cluster_args(b, xyz_dev, nullptr, 0, cfg, id_offset, 0, &a);
+  if (st) return st;
+  const int min_inl = std::max(cfg->min_region_inliers, 1);
+  DevBuf d_parent, d_count, d_hi, d_list, d_nlist;
+  const int list_cap = (int)std::min<size_t>(N / (size_t)min_inl + 1, (size_t)1 << 22);
+  CU_TRY(c, d_parent.ensure(N * sizeof(int)));
+  CU_TRY(c, d_count.ensure(N * sizeof(int)));
+  CU_TRY(c, d_hi.ensure(N * sizeof(int)));
+  CU_TRY(c, d_list.ensure((size_t)list_cap * 3 * sizeof(int)));
+  CU_TRY(c, d_nlist.ensure(sizeof(int)));
+  CU_TRY(c, cudaMemsetAsync(d_nlist.p, 0, sizeof(int), stream));
+  const unsigned grid = (unsigned)((N + 255) / 256);
+  cluster_comp_init_kernel<<<grid, 256, 0, stream>>>(xyz_dev, a.labels, (int)N, d_parent.as<int>(), d_count.as<int>(), d_hi.as<int>());
+  cluster_comp_link_kernel<<<grid, 256, 0, stream>>>(xyz_dev, rows, cols, h, a.sq_thr, d_parent.as<int>());
+  cluster_comp_flatten_kernel<<<grid, 256, 0, stream>>>((int)N, d_parent.as<int>(), a.labels, d_count.as<int>(), d_hi.as<int>());
+  cluster_comp_list_kernel<<<grid, 256, 0, stream>>>((int)N, d_parent.as<int>(), d_count.as<int>(), d_hi.as<int>(), min_inl,
+                                                     d_list.as<int>(), list_cap, d_nlist.as<int>());
+  c->launches += 4;
+  const unsigned rgrid = (unsigned)std::min<size_t>((N + 255) / 256, (size_t)148 * 16);
+  int nc = 0;
+  CU_TRY(c, cudaMemcpyAsync(&nc, d_nlist.p, sizeof(int), cudaMemcpyDeviceToHost, stream));
+  CU_TRY(c, cudaStreamSynchronize(stream));
+  if (nc > list_cap) nc = list_cap;   // cannot happen: a listed component has >= min_inl cells
+  struct Comp { int root, count, hi; };
+  std::vector<Comp> comps((size_t)nc);
+  if (nc > 0) CU_TRY(c, cudaMemcpy(comps.data(), d_list.p, (size_t)nc * 3 * sizeof(int), cudaMemcpyDeviceToHost));
+  std::sort(comps.begin(), comps.end(), [](const Comp& x, const Comp& y) { return x.root < y.root; });
+  // tables
+  std::vector<int> h_root(nc), h_hi(nc), h_qcap(nc), h_ioff(nc), h_moff(nc);
+  std::vector<long long> h_qoff(nc);
+  long long qtot = 0;
+  int mtot = 0, itot = 0;
+  for (int k = 0; k < nc; ++k) {
+    h_root[k] = comps[k].root; h_hi[k] = comps[k].hi;
+    int qc = 1024;
+    while (qc < comps[k].count) qc <<= 1;
+    h_qcap[k] = qc; h_qoff[k] = qtot; qtot += qc;
+    h_ioff[k] = itot; itot += comps[k].count;
+    h_moff[k] = mtot; mtot += comps[k].count / min_inl + 1;
+  }
+  int n_regions = 0, n_inliers = 0, err = 0, steps = 0;
+  if (nc > 0) {
+    DevBuf d_tab, d_queue, d_meta, d_out, d_mv;
+    const size_t tab_bytes = (size_t)nc * (5 * sizeof(int) + sizeof(long long));
+    CU_TRY(c, d_tab.ensure(tab_bytes));
+    CU_TRY(c, d_queue.ensure(std::max((size_t)qtot * 2, N) * sizeof(int)));   // later: scratch for the packed inlier lists
+    CU_TRY(c, d_meta.ensure((size_t)mtot * sizeof(ClusterMeta)));
+    CU_TRY(c, d_out.ensure((size_t)nc * 4 * sizeof(int)));
+    char* tp = d_tab.as<char>();
+    long long* p_qoff = reinterpret_cast<long long*>(tp);
+    int* p_root = reinterpret_cast<int*>(tp + (size_t)nc * sizeof(long long));
+    int* p_hi = p_root + nc; int* p_qcap = p_hi + nc; int* p_ioff = p_qcap + nc; int* p_moff = p_ioff + nc;
+    CU_TRY(c, cudaMemcpyAsync(p_qoff, h_qoff.data(), (size_t)nc * sizeof(long long), cudaMemcpyHostToDevice, stream));
+    CU_TRY(c, cudaMemcpyAsync(p_root, h_root.data(), (size_t)nc * sizeof(int), cudaMemcpyHostToDevice, stream));
+    CU_TRY(c, cudaMemcpyAsync(p_hi, h_hi.data(), (size_t)nc * sizeof(int), cudaMemcpyHostToDevice, stream));
+    CU_TRY(c, cudaMemcpyAsync(p_qcap, h_qcap.data(), (size_t)nc * sizeof(int), cudaMemcpyHostToDevice, stream));
+    CU_TRY(c, cudaMemcpyAsync(p_ioff, h_ioff.data(), (size_t)nc * sizeof(int), cudaMemcpyHostToDevice, stream));
+    CU_TRY(c, cudaMemcpyAsync(p_moff, h_moff.data(), (size_t)nc * sizeof(int), cudaMemcpyHostToDevice, stream));
+    ClusterCompTable t;
+    t.root = p_root; t.hi = p_hi; t.q_off = p_qoff; t.q_cap = p_qcap; t.inl_off = p_ioff; t.m_off = p_moff;
+    t.queue = d_queue.as<int>(); t.meta = d_meta.as<ClusterMeta>(); t.out = d_out.as<int>(); t.rcap_total = mtot;
+    t.comp = d_parent.as<int>();
+    if (a.half_window == 1) cluster_comp_kernel<kClusterBlock, true><<<nc, kClusterBlock, 0, stream>>>(a, t);
+    else cluster_comp_kernel<kClusterBlock, false><<<nc, kClusterBlock, 0, stream>>>(a, t);
+    ++c->launches;
+    CU_TRY(c, cudaGetLastError());
+    // the regions of all components in the reference's order: ascending seed index
+    std::vector<int> h_out((size_t)nc * 4);
+    std::vector<ClusterMeta> h_meta((size_t)mtot);
+    CU_TRY(c, cudaMemcpyAsync(h_out.data(), d_out.p, h_out.size() * sizeof(int), cudaMemcpyDeviceToHost, stream));
+    CU_TRY(c, cudaMemcpyAsync(h_meta.data(), d_meta.p, h_meta.size() * sizeof(ClusterMeta), cudaMemcpyDeviceToHost, stream));
+    CU_TRY(c, cudaStreamSynchronize(stream));
+    struct Reg { int seed, src, count; };
+    std::vector<Reg> regs;
+    for (int k = 0; k < nc; ++k) {
+      err |= h_out[4 * k + 2]; steps += h_out[4 * k + 3];
+      for (int r = 0; r < h_out[4 * k]; ++r) {
+        const ClusterMeta& m = h_meta[(size_t)h_moff[k] + r];
+        regs.push_back(Reg{m.label_id, m.inlier_begin, m.inlier_count});   // label_id carries the seed in component mode
+      }
+    }
+    std::sort(regs.begin(), regs.end(), [](const Reg& x, const Reg& y) { return x.seed < y.seed; });
+    if ((int)regs.size() > a.rcap) { err |= kErrRegionCap; regs.resize((size_t)a.rcap); }
+    n_regions = (int)regs.size();
+    std::vector<ClusterCompMove> mv((size_t)n_regions);
+    for (int r = 0; r < n_regions; ++r) {
+      mv[r] = ClusterCompMove{regs[r].src, regs[r].count, n_inliers, id_offset + r};
+      n_inliers += regs[r].count;
+    }
+    if (n_regions > 0) {
+      CU_TRY(c, d_mv.ensure((size_t)n_regions * sizeof(ClusterCompMove)));
+      CU_TRY(c, cudaMemcpyAsync(d_mv.p, mv.data(), (size_t)n_regions * sizeof(ClusterCompMove), cudaMemcpyHostToDevice, stream));
+      cluster_comp_pack_kernel<<<(unsigned)std::min(n_regions, 148 * 8), 256, 0, stream>>>(a, d_mv.as<ClusterCompMove>(), n_regions, d_queue.as<int>());
+      ++c->launches;
+    }
+    cluster_comp_stats_kernel<<<1, 1, 0, stream>>>(a, n_regions, n_inliers, err, steps);
+    if (n_regions > 0) cluster_band_copyback_kernel<<<296, 256, 0, stream>>>(a, d_queue.as<int>());
+    cluster_comp_restore_kernel<<<rgrid, 256, 0, stream>>>(a.labels, (int)N);
+    c->launches += 3;
+    CU_TRY(c, cudaGetLastError());
+    CU_TRY(c, cudaStreamSynchronize(stream));   // the tables above die with this scope
+  } else {
+    cluster_comp_stats_kernel<<<1, 1, 0, stream>>>(a, 0, 0, 0, 0);
+    cluster_comp_restore_kernel<<<rgrid, 256, 0, stream>>>(a.labels, (int)N);
+    c->launches += 2;
+    CU_TRY(c, cudaStreamSynchronize(stream));
+  }
+  *used = true;
+  return PCSEG_OK;
+}
+
 int map_error_flags(pcseg_ctx* c, int flags) {
   if (flags == 0) return PCSEG_OK;
   c->last_error = "per-frame capacity/trace error flags = " + std::to_string(flags);
@@ -1030,13 +1152,17 @@ int pcseg_segment_cluster(pcseg_ctx* c, const float* xyz, int rows, int cols, co
   if (n_seeds > 0) {
     const int* seeds_dev;
     // one large frame with the seed list "all indices descending" (ps/clustering_test.cc:57-59): independent
-    // column bands are grown concurrently (PCSEG_CLUSTER_BANDS=0 turns it off)
+    // parts are grown concurrently -- connected components, else column bands (PCSEG_CLUSTER_BANDS=0 turns
+    // both off)
     bool banded = false;
     const char* be = getenv("PCSEG_CLUSTER_BANDS");
     if (!(be && be[0] == '0') && N >= ((size_t)1 << 18) && (size_t)n_seeds == N && !is_device_ptr(seeds)) {
       bool alldesc = true;
       for (size_t k = 0; k < N && alldesc; ++k) alldesc = seeds[k] == (int)(N - 1 - k);
-      if (alldesc && (st = run_cluster_banded(b, b->xyz_dev, cfg, id_offset, &banded))) return st;
+      // first choice: one CTA per connected component (PCSEG_CLUSTER_COMPONENTS=0: column bands only)
+      const char* ce = getenv("PCSEG_CLUSTER_COMPONENTS");
+      if (alldesc && !(ce && ce[0] == '0') && (st = run_cluster_components(b, b->xyz_dev, cfg, id_offset, &banded))) return st;
+      if (alldesc && !banded && (st = run_cluster_banded(b, b->xyz_dev, cfg, id_offset, &banded))) return st;
     }
     if (!banded) {
       if ((st = check_seeds_host(seeds, n_seeds, N, c, &b->seeds, &seeds_dev))) return st;
