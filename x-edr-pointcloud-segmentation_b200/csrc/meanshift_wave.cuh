@@ -45,7 +45,7 @@
 namespace pcseg {
 
 constexpr int kMsTmpBase = 0x40000000;  // temporary label of rank k = kMsTmpBase + k
-constexpr int kMsWaveMax = 256;         // ranks per wave (claim key = rank * 1024 + thread)
+constexpr int kMsWaveMax = 1024;        // ranks per wave (claim key = rank * 1024 + thread < 2^20)
 
 struct MsWaveArgs {
   MsGrowArgs g;

@@ -1774,7 +1774,7 @@ int mean_shift_finish(pcseg_ctx* c, const float* xyz_dev, int rows, int cols, co
   } else {
     // waves of regions grown at the same time and resolved in order (meanshift_wave.cuh)
     const int kmax = (int)std::min<size_t>(kMsWaveMax, (size_t)S);
-    size_t cap_cells = (size_t)1 << 21;
+    size_t cap_cells = (size_t)1 << 18;   // ranks above 0: 1 MB each (rank 0 has room for every cell)
     if (const char* e = getenv("PCSEG_MS_SLOT_CAP")) cap_cells = (size_t)std::max(1, atoi(e));   // tests: force slot overflows
     const int slot_cap = (int)std::min<size_t>(N, cap_cells);
     DevBuf d_slots, d_wave;
@@ -1785,7 +1785,7 @@ int mean_shift_finish(pcseg_ctx* c, const float* xyz_dev, int rows, int cols, co
     g.first_alive = d_wave.as<int>() + kWvFirstAlive;
     w.g = g; w.slot_inliers = d_slots.as<int>(); w.slot0 = N; w.slot_cap = slot_cap; w.wave = d_wave.as<int>();
     int h_wave[4] = {0, 0, 0, 0};
-    int pos = 0, n_reg = 0, n_inl = 0, r_applied = 0, K = std::min(64, kmax);
+    int pos = 0, n_reg = 0, n_inl = 0, r_applied = 0, K = kmax;
     bool first = true;
     while (pos < S) {
       if (first || n_reg > r_applied) {   // dead-mode flags up to date before the candidates are picked
