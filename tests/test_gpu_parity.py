@@ -337,21 +337,6 @@ def test_mean_shift_full_parity(ctx, rows, cols, pitch, blobs, h, sort_mode, min
     _assert_ms_equal(g_lab, g_r, o_lab, o_r)
 
 
-def _speckle_cloud(rows, cols, seed, pitch=0.05):
-    """A sheet with random height steps, dropouts and isolated speckles: hundreds of connected components
-    of all sizes, regions that touch one another, candidates that are rejected inside a component
-    (quirk Q5) and components too small to yield a region."""
-    rng = np.random.default_rng(seed)
-    cc, rr = np.meshgrid(np.arange(cols), np.arange(rows), indexing="ij")
-    z = 0.35 * rng.integers(0, 4, size=(cols // 16 + 1, rows // 12 + 1))[cc // 16, rr // 12].astype(np.float64)
-    z += 0.02 * rng.standard_normal((cols, rows))
-    spk = rng.random((cols, rows)) < 0.04
-    z[spk] += rng.uniform(0.15, 0.6, size=int(spk.sum()))
-    p = np.stack([cc * pitch, rr * pitch, z], axis=-1).reshape(-1, 3).astype(np.float32)
-    p[rng.random(rows * cols) < 0.05] = np.nan
-    return np.ascontiguousarray(p)
-
-
 @pytest.mark.parametrize("rows,cols,h,thr,min_inl", [(512, 520, 1, 0.004, 7), (128, 2100, 2, 0.01, 10), (300, 900, 3, 0.02, 25)])
 def test_cluster_single_large_frame_paths(ctx, rows, cols, h, thr, min_inl):
     """pcseg_segment_cluster on one frame of >= 2^18 cells with the all-descending seed list: one CTA per
@@ -359,7 +344,7 @@ def test_cluster_single_large_frame_paths(ctx, rows, cols, h, thr, min_inl):
     frame (PCSEG_CLUSTER_BANDS=0) all equal the oracle."""
     import os
     assert rows * cols >= 1 << 18
-    xyz = _speckle_cloud(rows, cols, seed=rows + h)
+    xyz = synth.speckle_cloud(rows, cols, seed=rows + h)
     n = rows * cols
     labels = np.full(n, -1, np.int32)
     labels[np.random.default_rng(5).random(n) < 0.02] = 3      # cells a planar stage took
@@ -378,18 +363,6 @@ def test_cluster_single_large_frame_paths(ctx, rows, cols, h, thr, min_inl):
         assert_regions_equal(g_r, o_r, "cluster")
 
 
-def _terraces(rows, cols, tr, tc, pitch, step, seed, nan_frac=0.03):
-    """Tiles of tr x tc cells at heights step * ((ti + 2 tj) % 4), no gaps: the regions TOUCH (their
-    windows overlap) without merging, and cells within 1 m of a neighbour's mode cross the steps --
-    the case in which regions grown at the same time interact (meanshift_wave.cuh)."""
-    rng = np.random.default_rng(seed)
-    cc, rr = np.meshgrid(np.arange(cols), np.arange(rows), indexing="ij")
-    z = step * (((rr // tr) + 2 * (cc // tc)) % 4) + 0.002 * rng.standard_normal((cols, rows))
-    p = np.stack([cc * pitch, rr * pitch, z], axis=-1).reshape(-1, 3).astype(np.float32)
-    p[rng.random(rows * cols) < nan_frac] = np.nan
-    return np.ascontiguousarray(p)
-
-
 @pytest.mark.parametrize("rows,cols,tr,tc,pitch,step,h,min_inl", [
     (96, 120, 24, 30, 0.05, 0.6, 1, 7), (96, 120, 24, 30, 0.05, 0.6, 2, 7), (150, 150, 25, 25, 0.08, 0.3, 1, 20),
     (120, 160, 12, 16, 0.1, 0.7, 3, 5), (200, 200, 20, 20, 0.03, 0.5, 2, 300)])
@@ -397,7 +370,7 @@ def test_mean_shift_touching_regions(ctx, rows, cols, tr, tc, pitch, step, h, mi
     """Many regions that touch one another: the wave path (several regions in flight, resolved in
     order) and the serial path (PCSEG_MS_GROWTH=serial) both equal the oracle."""
     import os
-    xyz = _terraces(rows, cols, tr, tc, pitch, step, seed=rows + h)
+    xyz = synth.terraces(rows, cols, tr, tc, pitch, step, seed=rows + h)
     labels = np.full(rows * cols, -1, np.int32)
     cfg = dict(half_search_window=h, min_region_inliers=min_inl)
     o_lab, o_r, _ = oracle.mean_shift(xyz, rows, cols, labels, cfg=oracle.default_cluster_config(**cfg),

@@ -222,6 +222,33 @@ def c5_full(rows=2500, cols=4000):
     return c5(rows, cols, tiles=(max(rows // 20, 16), max(cols // 20, 16), 8))
 
 
+def terraces(rows, cols, tr, tc, pitch, step, seed, nan_frac=0.03):
+    """Tiles of tr x tc cells at heights step * ((ti + 2 tj) % 4), no gaps: the regions TOUCH (their
+    windows overlap) without merging, and cells within 1 m of a neighbour's mode cross the steps --
+    the case in which regions grown at the same time interact (meanshift_wave.cuh)."""
+    rng = np.random.default_rng(seed)
+    cc, rr = np.meshgrid(np.arange(cols), np.arange(rows), indexing="ij")
+    z = step * (((rr // tr) + 2 * (cc // tc)) % 4) + 0.002 * rng.standard_normal((cols, rows))
+    p = np.stack([cc * pitch, rr * pitch, z], axis=-1).reshape(-1, 3).astype(np.float32)
+    p[rng.random(rows * cols) < nan_frac] = np.nan
+    return np.ascontiguousarray(p)
+
+
+def speckle_cloud(rows, cols, seed, pitch=0.05):
+    """A sheet with random height steps, dropouts and isolated speckles: hundreds of connected components
+    of all sizes, regions that touch one another, candidates that are rejected inside a component
+    (quirk Q5) and components too small to yield a region."""
+    rng = np.random.default_rng(seed)
+    cc, rr = np.meshgrid(np.arange(cols), np.arange(rows), indexing="ij")
+    z = 0.35 * rng.integers(0, 4, size=(cols // 16 + 1, rows // 12 + 1))[cc // 16, rr // 12].astype(np.float64)
+    z += 0.02 * rng.standard_normal((cols, rows))
+    spk = rng.random((cols, rows)) < 0.04
+    z[spk] += rng.uniform(0.15, 0.6, size=int(spk.sum()))
+    p = np.stack([cc * pitch, rr * pitch, z], axis=-1).reshape(-1, 3).astype(np.float32)
+    p[rng.random(rows * cols) < 0.05] = np.nan
+    return np.ascontiguousarray(p)
+
+
 def clustering_test_cloud():
     """ps/clustering_test.cc:53-113 PointCloudData(): 10x10 golden cloud,
     returns (xyz[100,3], seeds[100]) with seed[99 - idx] = idx."""
