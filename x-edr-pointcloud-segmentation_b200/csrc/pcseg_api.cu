@@ -192,6 +192,13 @@ struct pcseg_batch {
   // overlap (pcseg_batch_submit / pcseg_batch_wait: the copies of one run under the kernels of
   // the other).  The context's cached single-frame workspace has none and uses the context's.
   cudaStream_t own_stream = nullptr, own_copy_in = nullptr, own_copy_out = nullptr;
+  // The normals kernel of a run goes to a LOW-priority stream of its own, the growth stages stay on
+  // the (high-priority) main stream: with several workspaces in flight the CTA scheduler then hands
+  // freed SM slots to the long, latency-bound growth CTAs of one workspace before the hundreds of
+  // thousands of short normals CTAs of another, which fill the issue slots the growth leaves idle
+  // instead of running in front of it.  cur_stream: what S() returns while the normals stage is enqueued.
+  cudaStream_t own_normals = nullptr, cur_stream = nullptr;
+  cudaEvent_t ev_nrm[2] = {nullptr, nullptr};
   bool in_flight = false, wait_copy_out = false;
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   std::vector<cudaEvent_t> chunk_ev;  // 2 per chunk (H2D done, normals done) + 2
@@ -257,7 +264,7 @@ __global__ void fill_int_kernel(int* p, size_t n, int v) {
 }
 
 // The stream set a workspace enqueues on: its own (pcseg_batch_create) or the context's.
-inline cudaStream_t S(const pcseg_batch* b) { return b->own_stream ? b->own_stream : b->ctx->stream; }
+inline cudaStream_t S(const pcseg_batch* b) { return b->cur_stream ? b->cur_stream : b->own_stream ? b->own_stream : b->ctx->stream; }
 inline cudaStream_t SIn(const pcseg_batch* b) { return b->own_copy_in ? b->own_copy_in : b->ctx->copy_in; }
 inline cudaStream_t SOut(const pcseg_batch* b) { return b->own_copy_out ? b->own_copy_out : b->ctx->copy_out; }
 
@@ -924,7 +931,7 @@ int get_scratch(pcseg_ctx* c, int rows, int cols, pcseg_batch** out) {
     // the single-frame entry points issue their copies on the context's stream: the cached
     // workspace must launch there too (S / SIn / SOut fall back to the context's streams)
     pcseg_batch* b = c->scratch;
-    for (cudaStream_t* s : {&b->own_stream, &b->own_copy_in, &b->own_copy_out})
+    for (cudaStream_t* s : {&b->own_stream, &b->own_copy_in, &b->own_copy_out, &b->own_normals})
       if (*s) { cudaStreamSynchronize(*s); cudaStreamDestroy(*s); *s = nullptr; }
   }
   *out = c->scratch;
@@ -2085,9 +2092,16 @@ int pcseg_batch_create(pcseg_ctx* c, int n_frames, int rows, int cols, pcseg_bat
   int st = batch_alloc(b);
   if (st) { pcseg_batch_destroy(b); return st; }
   for (auto& e : b->ev) cudaEventCreate(&e);
-  if (cudaStreamCreateWithFlags(&b->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
+  int prio_lo = 0, prio_hi = 0;   // numerically lower = higher priority
+  cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+  const char* pe = getenv("PCSEG_STREAM_PRIORITIES");
+  const bool prio = !(pe && pe[0] == '0') && prio_hi < prio_lo;
+  if (cudaStreamCreateWithPriority(&b->own_stream, cudaStreamNonBlocking, prio ? prio_hi : prio_lo) != cudaSuccess ||
       cudaStreamCreateWithFlags(&b->own_copy_in, cudaStreamNonBlocking) != cudaSuccess ||
-      cudaStreamCreateWithFlags(&b->own_copy_out, cudaStreamNonBlocking) != cudaSuccess) {
+      cudaStreamCreateWithFlags(&b->own_copy_out, cudaStreamNonBlocking) != cudaSuccess ||
+      (prio && (cudaStreamCreateWithPriority(&b->own_normals, cudaStreamNonBlocking, prio_lo) != cudaSuccess ||
+                cudaEventCreateWithFlags(&b->ev_nrm[0], cudaEventDisableTiming) != cudaSuccess ||
+                cudaEventCreateWithFlags(&b->ev_nrm[1], cudaEventDisableTiming) != cudaSuccess))) {
     pcseg_batch_destroy(b);
     return PCSEG_ERR_CUDA;
   }
@@ -2099,8 +2113,9 @@ void pcseg_batch_destroy(pcseg_batch* b) {
   if (!b) return;
   cudaSetDevice(b->ctx->device);
   cudaStreamSynchronize(b->ctx->stream);
-  for (cudaStream_t s : {b->own_stream, b->own_copy_in, b->own_copy_out})
+  for (cudaStream_t s : {b->own_stream, b->own_copy_in, b->own_copy_out, b->own_normals})
     if (s) { cudaStreamSynchronize(s); cudaStreamDestroy(s); }
+  for (auto& e : b->ev_nrm) if (e) cudaEventDestroy(e);
   DevBuf* all[] = {&b->xyz, &b->normals, &b->labels, &b->queue, &b->claim, &b->inl_planar, &b->inl_cluster,
                    &b->boundary, &b->bflags, &b->meta_planar, &b->meta_cluster, &b->stats, &b->inv_list,
                    &b->inv_count, &b->seeds, &b->n_seeds, &b->pk_offsets, &b->pk_planar, &b->pk_pinl,
@@ -2229,6 +2244,13 @@ namespace {
 int enqueue_normals_stage(pcseg_batch* b, const float* xyz, float* normals_out) {
   pcseg_ctx* c = b->ctx;
   const pcseg_pipeline_params* p = &b->run_params;
+  cudaStream_t main_stream = S(b);
+  if (b->own_normals) {   // behind everything already queued on the main stream
+    CU_TRY(c, cudaEventRecord(b->ev_nrm[0], main_stream));
+    CU_TRY(c, cudaStreamWaitEvent(b->own_normals, b->ev_nrm[0], 0));
+    b->cur_stream = b->own_normals;
+  }
+  struct Restore { pcseg_batch* b; ~Restore() { b->cur_stream = nullptr; } } restore{b};
   cudaStream_t stream = S(b), s_in = SIn(b), s_out = SOut(b);
   const size_t F = b->n_frames, N = b->N;
   const bool xyz_host = !is_device_ptr(xyz);
@@ -2279,6 +2301,10 @@ int enqueue_normals_stage(pcseg_batch* b, const float* xyz, float* normals_out) 
     }
   }
   cudaEventRecord(b->ev[1], stream);
+  if (stream != main_stream) {   // the growth stages wait for the normals
+    CU_TRY(c, cudaEventRecord(b->ev_nrm[1], stream));
+    CU_TRY(c, cudaStreamWaitEvent(main_stream, b->ev_nrm[1], 0));
+  }
   return PCSEG_OK;
 }
 
