@@ -7,7 +7,8 @@
 // 11x11 INDEX window around round(index), summed in the reference's window
 // order (delta_col outer, delta_row inner) in fp32, divided by (float)n.
 // Threads of a warp are 32 consecutive rows of one column, so their windows
-// overlap almost completely and the gathers are served by L1.
+// overlap almost completely and the gathers are served by L1 (one float4 {point, takes part}
+// per window cell, packed by meanshift_pack_kernel).
 #pragma once
 #include "grow_common.cuh"
 
@@ -28,7 +29,20 @@ struct MeanShiftArgs {
   int iterations;
   int cell_begin, cell_end;  // this launch's shard of seed cells
   ModeRecord* modes;         // indexed by (cell - cell_begin)
+  const float4* packed;      // [N] {x, y, z, takes part ? 1 : 0}: one 16-byte gather per window cell
 };
+
+// A window cell takes part iff it is unlabeled and its point has no NaN (:110-118).  Label and point are
+// packed into one float4 per cell, so the 605 window cells a seed visits cost one vector load each
+// instead of a label load and three scalar point loads.
+__global__ void __launch_bounds__(256) meanshift_pack_kernel(const float* __restrict__ xyz, const int* __restrict__ labels,
+                                                             int n, float4* packed) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const V3 p = ld3(xyz, i);
+  const bool part = labels[i] == kUnlabeled && !vhasnan(p);
+  packed[i] = make_float4(p.x, p.y, p.z, part ? 1.0f : 0.0f);
+}
 
 constexpr int kMsHalfWindow = 5;      // ps/mean_shift_segmentation.h:39
 constexpr int kMsMinCount = 50;       // 0.5 * 5 * 5 * 4, :245-247
@@ -57,9 +71,9 @@ __global__ void __launch_bounds__(256) meanshift_modes_kernel(MeanShiftArgs a) {
         const int rc = row + dr;
         if (rc < 0 || rc >= rows) continue;
         const int n = cc * rows + rc;
-        if (__ldg(a.labels + n) != kUnlabeled) continue;
-        const V3 p = ld3(a.xyz, n);
-        if (vhasnan(p)) continue;
+        const float4 q = __ldg(a.packed + n);
+        if (q.w == 0.0f) continue;
+        const V3 p{q.x, q.y, q.z};
         const V3 d = vsub(p, sp);
         if (vsqn(d) > 1.0f) continue;  // kSquareDistanceThreshold, :33,124
         shift = vadd(shift, d);

@@ -1563,13 +1563,20 @@ int pcseg_mean_shift_modes_range(pcseg_ctx* c, const float* xyz, int rows, int c
   MeanShiftArgs a;
   a.xyz = (const float*)xyz_dev; a.labels = (const int*)lab_dev; a.rows = rows; a.cols = cols;
   a.iterations = iterations; a.cell_begin = cell_begin; a.cell_end = cell_end; a.modes = modes_dev;
+  DevBuf spk;
+  {
+    const size_t Nall = (size_t)rows * cols;
+    if (spk.ensure(Nall * sizeof(float4)) != cudaSuccess) { sx.release(); sl.release(); so.release(); return PCSEG_ERR_CUDA; }
+    a.packed = spk.as<float4>();
+    meanshift_pack_kernel<<<(unsigned)((Nall + 255) / 256), 256, 0, c->stream>>>(a.xyz, a.labels, (int)Nall, spk.as<float4>());
+  }
   meanshift_modes_kernel<<<(unsigned)((M + 255) / 256), 256, 0, c->stream>>>(a);
-  ++c->launches;
+  c->launches += 2;
   cudaError_t e = cudaGetLastError();
   if (e == cudaSuccess && !out_dev)
     e = cudaMemcpyAsync(modes_out, modes_dev, M * sizeof(ModeRecord), cudaMemcpyDeviceToHost, c->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
-  sx.release(); sl.release(); so.release();
+  sx.release(); sl.release(); so.release(); spk.release();
   if (e != cudaSuccess) { c->last_error = cudaGetErrorString(e); return PCSEG_ERR_CUDA; }
   return PCSEG_OK;
 }
@@ -1922,8 +1929,12 @@ int pcseg_mean_shift(pcseg_ctx* c, const float* xyz, int rows, int cols, const p
   MeanShiftArgs a;
   a.xyz = (const float*)xyz_dev; a.labels = lab_dev; a.rows = rows; a.cols = cols;
   a.iterations = iterations; a.cell_begin = 0; a.cell_end = (int)N; a.modes = sm.as<ModeRecord>();
+  DevBuf spk;
+  if (spk.ensure(N * sizeof(float4)) != cudaSuccess) { sx.release(); sl.release(); sm.release(); return PCSEG_ERR_CUDA; }
+  a.packed = spk.as<float4>();
+  meanshift_pack_kernel<<<(unsigned)((N + 255) / 256), 256, 0, c->stream>>>(a.xyz, a.labels, (int)N, spk.as<float4>());
   meanshift_modes_kernel<<<(unsigned)((N + 255) / 256), 256, 0, c->stream>>>(a);
-  ++c->launches;
+  c->launches += 2;
   st = mean_shift_finish(c, (const float*)xyz_dev, rows, cols, sm.as<ModeRecord>(), cfg, id_offset, sort_mode,
                          lab_dev, out);
   if (st == PCSEG_OK && lab_dev != labels) {
