@@ -1278,18 +1278,19 @@ int oracle_cluster_unorganized(const float* xyz, int n, float radius,
     res->inlier_indices.insert(res->inlier_indices.end(), l.begin(), l.end());
     res->inlier_offsets.push_back(static_cast<int>(res->inlier_indices.size()));
     res->label_ids.push_back(id_offset + r);
-    double lane[32][3] = {};
+    constexpr int kLanes = 256;   // vox_stats_kernel: thread t of 256 adds the elements t, t + 256, ...
+    double lane[kLanes][3] = {};
     float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
-    for (size_t k = 0; k < l.size(); ++k) {   // lane k % 32 adds its elements in ascending order
+    for (size_t k = 0; k < l.size(); ++k) {   // lane k % 256 adds its elements in ascending order
       const float* p = xyz + 3 * static_cast<size_t>(l[k]);
       for (int c = 0; c < 3; ++c) {
-        lane[k % 32][c] += static_cast<double>(p[c]);
+        lane[k % kLanes][c] += static_cast<double>(p[c]);
         mn[c] = std::fmin(mn[c], p[c]);
         mx[c] = std::fmax(mx[c], p[c]);
       }
     }
     double tot[3] = {0.0, 0.0, 0.0};
-    for (int k = 0; k < 32; ++k)
+    for (int k = 0; k < kLanes; ++k)
       for (int c = 0; c < 3; ++c) tot[c] += lane[k][c];
     for (int c = 0; c < 3; ++c) res->centroids.push_back(static_cast<float>(tot[c] / static_cast<double>(l.size())));
     for (int c = 0; c < 3; ++c) res->bboxes.push_back(mn[c]);

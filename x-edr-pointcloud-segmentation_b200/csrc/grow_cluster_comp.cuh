@@ -68,12 +68,19 @@ __global__ void __launch_bounds__(256) cluster_comp_link_kernel(const float* __r
 // root of every cell -> its code in the label array, member count and largest member index per root
 __global__ void __launch_bounds__(256) cluster_comp_flatten_kernel(int n, int* parent, int* labels, int* count, int* hi) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n || parent[i] < 0) return;
-  const int r = vox_find(parent, i);
-  parent[i] = r;   // roots only ever point to themselves: safe while other threads still search
-  labels[i] = kCompUnlabeledBase + r;
-  atomicAdd(&count[r], 1);
-  atomicMax(&hi[r], i);
+  const bool part = i < n && parent[i] >= 0;
+  int r = -1;
+  if (part) {
+    r = vox_find(parent, i);
+    parent[i] = r;   // roots only ever point to themselves: safe while other threads still search
+    labels[i] = kCompUnlabeledBase + r;
+  }
+  // one atomic pair per (warp, root): the lanes of a warp are consecutive cells, mostly of one component
+  const unsigned peers = __match_any_sync(0xffffffffu, r);
+  if (part && (int)(threadIdx.x & 31) == __ffs(peers) - 1) {
+    atomicAdd(&count[r], __popc(peers));
+    atomicMax(&hi[r], i - (int)(threadIdx.x & 31) + 31 - __clz(peers));   // the highest lane of the group
+  }
 }
 
 // components that can yield a region: {root, count, hi} appended to list (order irrelevant, sorted on the host)

@@ -2063,7 +2063,7 @@ int pcseg_cluster_unorganized(pcseg_ctx* c, const float* xyz, int n, const pcseg
     }
     CU_TRY(c, d_cen.ensure((size_t)R * 12));
     CU_TRY(c, d_box.ensure((size_t)R * 24));
-    vox_stats_kernel<<<(unsigned)(((size_t)R * 32 + 255) / 256), 256, 0, st>>>((const float*)xyz_dev, d_idx[cur].as<int>(),
+    vox_stats_kernel<<<(unsigned)R, kVoxStatsBlock, 0, st>>>((const float*)xyz_dev, d_idx[cur].as<int>(),
                                                                               d_rb.as<int>(), d_rc.as<int>(), R,
                                                                               d_cen.as<float>(), d_box.as<float>());
     ++c->launches;

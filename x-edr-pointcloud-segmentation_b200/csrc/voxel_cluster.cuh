@@ -285,10 +285,15 @@ __global__ void __launch_bounds__(256) vox_union_pairs_kernel(VoxArgs a, const u
 // 3: flatten + member counts
 __global__ void __launch_bounds__(256) vox_flatten_kernel(VoxArgs a) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= a.n || a.slot_of[i] < 0) return;
-  const int r = vox_find(a.parent, i);
-  a.parent[i] = r;
-  atomicAdd(&a.count[r], 1);
+  const bool part = i < a.n && a.slot_of[i] >= 0;
+  int r = -1;
+  if (part) {
+    r = vox_find(a.parent, i);
+    a.parent[i] = r;
+  }
+  // one atomic per (warp, root) instead of one per point: a few dozen roots take all the increments
+  const unsigned peers = __match_any_sync(0xffffffffu, r);
+  if (part && (int)(threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&a.count[r], __popc(peers));
 }
 
 // 4: packed (is an accepted root, its member count) per point for the scan: low word -> region
@@ -333,30 +338,28 @@ __global__ void __launch_bounds__(256) vox_iota_kernel(int* idx, int n) {
   if (k < n) idx[k] = k;
 }
 
-// 6: centroid + extent of every region: one warp per region.  Fixed summation order (restated by the
-// oracle): lane l adds the elements l, l + 32, ... of the sorted inlier list in double; the total is
-// lanes 0 .. 31 added in that order; centroid = (float)(total / count).
-__global__ void __launch_bounds__(256) vox_stats_kernel(const float* __restrict__ xyz, const int* __restrict__ inliers,
-                                                        const int* __restrict__ reg_begin, const int* __restrict__ reg_count,
-                                                        int n_regions, float* centroid, float* bbox) {
-  const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
+// 6: centroid + extent of every region: one CTA of 256 threads per region.  Fixed summation order
+// (restated by the oracle): thread t adds the elements t, t + 256, ... of the sorted inlier list in
+// double; the total is threads 0 .. 255 added in that order; centroid = (float)(total / count).
+constexpr int kVoxStatsBlock = 256;
+__global__ void __launch_bounds__(kVoxStatsBlock) vox_stats_kernel(const float* __restrict__ xyz, const int* __restrict__ inliers,
+                                                                   const int* __restrict__ reg_begin, const int* __restrict__ reg_count,
+                                                                   int n_regions, float* centroid, float* bbox) {
+  __shared__ double s_sum[kVoxStatsBlock][3];
+  __shared__ float s_mn[kVoxStatsBlock / 32][3], s_mx[kVoxStatsBlock / 32][3];
+  const int r = blockIdx.x;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   if (r >= n_regions) return;
   const int b = reg_begin[r], n = reg_count[r];
   double sx = 0.0, sy = 0.0, sz = 0.0;
   float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
-  for (int i = lane; i < n; i += 32) {
+  for (int i = t; i < n; i += kVoxStatsBlock) {
     const V3 p = ld3(xyz, inliers[b + i]);
     sx += (double)p.x; sy += (double)p.y; sz += (double)p.z;
     mn[0] = fminf(mn[0], p.x); mn[1] = fminf(mn[1], p.y); mn[2] = fminf(mn[2], p.z);
     mx[0] = fmaxf(mx[0], p.x); mx[1] = fmaxf(mx[1], p.y); mx[2] = fmaxf(mx[2], p.z);
   }
-  double tx = 0.0, ty = 0.0, tz = 0.0;
-  for (int l = 0; l < 32; ++l) {
-    tx += __shfl_sync(0xffffffffu, sx, l);
-    ty += __shfl_sync(0xffffffffu, sy, l);
-    tz += __shfl_sync(0xffffffffu, sz, l);
-  }
+  s_sum[t][0] = sx; s_sum[t][1] = sy; s_sum[t][2] = sz;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1)
 #pragma unroll
@@ -364,9 +367,16 @@ __global__ void __launch_bounds__(256) vox_stats_kernel(const float* __restrict_
       mn[k] = fminf(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
       mx[k] = fmaxf(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
     }
-  if (lane == 0) {
-    centroid[3 * r] = (float)(tx / (double)n); centroid[3 * r + 1] = (float)(ty / (double)n); centroid[3 * r + 2] = (float)(tz / (double)n);
-    for (int k = 0; k < 3; ++k) { bbox[6 * r + k] = mn[k]; bbox[6 * r + 3 + k] = mx[k]; }
+  if (lane == 0)
+    for (int k = 0; k < 3; ++k) { s_mn[warp][k] = mn[k]; s_mx[warp][k] = mx[k]; }
+  __syncthreads();
+  if (t < 3) {   // one coordinate each, threads 0 .. 255 in order
+    double tot = 0.0;
+    for (int l = 0; l < kVoxStatsBlock; ++l) tot += s_sum[l][t];
+    centroid[3 * r + t] = (float)(tot / (double)n);
+    float lo = s_mn[0][t], hi = s_mx[0][t];
+    for (int w = 1; w < kVoxStatsBlock / 32; ++w) { lo = fminf(lo, s_mn[w][t]); hi = fmaxf(hi, s_mx[w][t]); }
+    bbox[6 * r + t] = lo; bbox[6 * r + 3 + t] = hi;
   }
 }
 
