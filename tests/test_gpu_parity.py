@@ -337,7 +337,8 @@ def test_mean_shift_full_parity(ctx, rows, cols, pitch, blobs, h, sort_mode, min
     _assert_ms_equal(g_lab, g_r, o_lab, o_r)
 
 
-@pytest.mark.parametrize("rows,cols,h,thr,min_inl", [(512, 520, 1, 0.004, 7), (128, 2100, 2, 0.01, 10), (300, 900, 3, 0.02, 25)])
+@pytest.mark.parametrize("rows,cols,h,thr,min_inl", [(512, 520, 1, 0.004, 7), (128, 2100, 2, 0.01, 10), (300, 900, 3, 0.02, 25),
+                                                     (270, 1000, 5, 0.03, 40), (512, 513, 1, 0.004, 1)])
 def test_cluster_single_large_frame_paths(ctx, rows, cols, h, thr, min_inl):
     """pcseg_segment_cluster on one frame of >= 2^18 cells with the all-descending seed list: one CTA per
     connected component (default), column bands only (PCSEG_CLUSTER_COMPONENTS=0) and one CTA for the
