@@ -364,6 +364,49 @@ def test_cluster_single_large_frame_paths(ctx, rows, cols, h, thr, min_inl):
         assert_regions_equal(g_r, o_r, "cluster")
 
 
+def test_cluster_single_large_frame_degenerate(ctx):
+    """One frame of >= 2^18 cells with nothing to grow (every cell labelled / every point NaN), with a single
+    unlabeled cell, and with one component only: the component path equals the oracle."""
+    rows, cols = 512, 520
+    n = rows * cols
+    seeds = np.arange(n - 1, -1, -1, dtype=np.int32)
+    xyz = synth.speckle_cloud(rows, cols, seed=77)
+    cfg = dict(squared_distance_threshold=0.004, half_search_window=1, min_region_inliers=1)
+    cases = []
+    cases.append((xyz, np.full(n, 5, np.int32)))                                  # every cell labelled
+    cases.append((np.full((n, 3), np.nan, np.float32), np.full(n, -1, np.int32)))  # every point NaN
+    one = np.full(n, 5, np.int32); one[12345] = -1
+    p1 = xyz.copy(); p1[12345] = (1.0, 2.0, 3.0)
+    cases.append((p1, one))                                                       # a single unlabeled cell
+    flat = np.zeros((n, 3), np.float32)
+    cc, rr = np.meshgrid(np.arange(cols), np.arange(rows), indexing="ij")
+    flat[:, 0] = cc.reshape(-1) * 0.01; flat[:, 1] = rr.reshape(-1) * 0.01
+    cases.append((flat, np.full(n, -1, np.int32)))                                # one component = the frame
+    for k, (pts, lab) in enumerate(cases):
+        o_lab, o_r = oracle.segment_cluster(pts, rows, cols, seeds, lab, cfg=oracle.default_cluster_config(**cfg), id_offset=2)
+        g_lab, g_r = ctx.segment_cluster(pts, rows, cols, seeds, lab, cfg=cfg, id_offset=2)
+        assert np.array_equal(g_lab, o_lab), k
+        assert_regions_equal(g_r, o_r, "cluster")
+        assert o_r.n == (0, 0, 1, 1)[k]
+
+
+def test_mean_shift_single_seed_and_tiny_clouds(ctx):
+    """Fewer modes than a wave has ranks: 1 x 1 ... 12 x 12 clouds, and a cloud with one unlabeled cell."""
+    for rows, cols in ((1, 1), (2, 3), (12, 12), (11, 40)):
+        xyz = synth.c5(rows=rows, cols=cols, n_blobs=1, pitch=0.05, nan_frac=0.0)
+        labels = np.full(rows * cols, -1, np.int32)
+        cfg = dict(half_search_window=1, min_region_inliers=1)
+        o_lab, o_r, _ = oracle.mean_shift(xyz, rows, cols, labels, cfg=oracle.default_cluster_config(**cfg), iterations=2)
+        g_lab, g_r = ctx.mean_shift(xyz, rows, cols, labels, cfg=cfg, iterations=2)
+        _assert_ms_equal(g_lab, g_r, o_lab, o_r)
+    rows, cols = 40, 50
+    xyz = synth.c5(rows=rows, cols=cols, n_blobs=3, pitch=0.05, nan_frac=0.0)
+    labels = np.full(rows * cols, 7, np.int32); labels[777] = -1
+    o_lab, o_r, _ = oracle.mean_shift(xyz, rows, cols, labels, iterations=3)
+    g_lab, g_r = ctx.mean_shift(xyz, rows, cols, labels, iterations=3)
+    _assert_ms_equal(g_lab, g_r, o_lab, o_r)
+
+
 @pytest.mark.parametrize("rows,cols,tr,tc,pitch,step,h,min_inl", [
     (96, 120, 24, 30, 0.05, 0.6, 1, 7), (96, 120, 24, 30, 0.05, 0.6, 2, 7), (150, 150, 25, 25, 0.08, 0.3, 1, 20),
     (120, 160, 12, 16, 0.1, 0.7, 3, 5), (200, 200, 20, 20, 0.03, 0.5, 2, 300)])
