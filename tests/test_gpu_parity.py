@@ -390,6 +390,36 @@ def test_cluster_single_large_frame_degenerate(ctx):
         assert o_r.n == (0, 0, 1, 1)[k]
 
 
+def test_reserved_label_ranges(ctx):
+    """The wave and component paths borrow label values for temporary codes: a caller grid that already
+    holds such values is refused (mean shift) or takes the other path (cluster growth) -- never corrupted."""
+    rows, cols = 512, 520
+    n = rows * cols
+    xyz = synth.speckle_cloud(rows, cols, seed=78)
+    seeds = np.arange(n - 1, -1, -1, dtype=np.int32)
+    labels = np.full(n, -1, np.int32)
+    labels[1000:1010] = np.iinfo(np.int32).min + 5          # inside the component-code range
+    cfg = dict(squared_distance_threshold=0.004, half_search_window=1, min_region_inliers=7)
+    o_lab, o_r = oracle.segment_cluster(xyz, rows, cols, seeds, labels, cfg=oracle.default_cluster_config(**cfg))
+    g_lab, g_r = ctx.segment_cluster(xyz, rows, cols, seeds, labels, cfg=cfg)
+    assert np.array_equal(g_lab, o_lab)
+    assert_regions_equal(g_r, o_r, "cluster")
+    c5 = synth.c5(rows=60, cols=80, n_blobs=4, pitch=0.05)
+    lab = np.full(60 * 80, -1, np.int32)
+    lab[17] = 0x40000000
+    with pytest.raises(pcseg.PcsegError) as e:
+        ctx.mean_shift(c5, 60, 80, lab, iterations=2)
+    assert e.value.status == 6 and "0x40000000" in str(e.value)
+    import os
+    os.environ["PCSEG_MS_GROWTH"] = "serial"                 # the serial walk has no such limit
+    try:
+        g_lab, g_r = ctx.mean_shift(c5, 60, 80, lab, iterations=2)
+    finally:
+        del os.environ["PCSEG_MS_GROWTH"]
+    o_lab, o_r, _ = oracle.mean_shift(c5, 60, 80, lab, iterations=2)
+    _assert_ms_equal(g_lab, g_r, o_lab, o_r)
+
+
 def test_mean_shift_single_seed_and_tiny_clouds(ctx):
     """Fewer modes than a wave has ranks: 1 x 1 ... 12 x 12 clouds, and a cloud with one unlabeled cell."""
     for rows, cols in ((1, 1), (2, 3), (12, 12), (11, 40)):

@@ -263,6 +263,16 @@ __global__ void fill_int_kernel(int* p, size_t n, int v) {
   for (; i < n; i += stride) p[i] = v;
 }
 
+// *flag |= 1 if any label lies outside [lo, hi): the single-cloud fast paths borrow label values outside
+// that range for their temporary codes and must not meet them in the caller's grid
+__global__ void label_range_kernel(const int* __restrict__ p, size_t n, int lo, int hi, int* flag) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  bool bad = false;
+  for (; i < n; i += stride) { const int v = p[i]; bad |= v < lo || v >= hi; }
+  if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(flag, 1);
+}
+
 // The stream set a workspace enqueues on: its own (pcseg_batch_create) or the context's.
 inline cudaStream_t S(const pcseg_batch* b) { return b->cur_stream ? b->cur_stream : b->own_stream ? b->own_stream : b->ctx->stream; }
 inline cudaStream_t SIn(const pcseg_batch* b) { return b->own_copy_in ? b->own_copy_in : b->ctx->copy_in; }
@@ -637,6 +647,16 @@ int run_cluster_components(pcseg_batch* b, const float* xyz_dev, const pcseg_clu
   if (st) return st;
   const int min_inl = std::max(cfg->min_region_inliers, 1);
   DevBuf d_parent, d_count, d_hi, d_list, d_nlist;
+  {   // the component codes live below kCompUnlabeledBase + 2^30: a caller grid with such values takes another path
+    CU_TRY(c, d_nlist.ensure(sizeof(int)));
+    CU_TRY(c, cudaMemsetAsync(d_nlist.p, 0, sizeof(int), stream));
+    label_range_kernel<<<148 * 8, 256, 0, stream>>>(a.labels, N, kCompUnlabeledBase + (1 << 30), INT_MAX, d_nlist.as<int>());
+    int bad = 0;
+    CU_TRY(c, cudaMemcpyAsync(&bad, d_nlist.p, sizeof(int), cudaMemcpyDeviceToHost, stream));
+    CU_TRY(c, cudaStreamSynchronize(stream));
+    ++c->launches;
+    if (bad) return PCSEG_OK;
+  }
   const int list_cap = (int)std::min<size_t>(N / (size_t)min_inl + 1, (size_t)1 << 22);
   CU_TRY(c, d_parent.ensure(N * sizeof(int)));
   CU_TRY(c, d_count.ensure(N * sizeof(int)));
@@ -1787,6 +1807,20 @@ int mean_shift_finish(pcseg_ctx* c, const float* xyz_dev, int rows, int cols, co
     }
   } else {
     // waves of regions grown at the same time and resolved in order (meanshift_wave.cuh)
+    {   // their temporary labels start at kMsTmpBase: the caller's grid must stay below
+      CU_TRY(c, cudaMemsetAsync(d_out.as<int>() + 1, 0, sizeof(int), c->stream));
+      label_range_kernel<<<148 * 8, 256, 0, c->stream>>>(labels_dev, N, INT_MIN, kMsTmpBase, d_out.as<int>() + 1);
+      int bad = 0;
+      CU_TRY(c, cudaMemcpyAsync(&bad, d_out.as<int>() + 1, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+      CU_TRY(c, cudaStreamSynchronize(c->stream));
+      CU_TRY(c, cudaMemsetAsync(d_out.as<int>() + 1, 0, sizeof(int), c->stream));
+      ++c->launches;
+      if (bad) {
+        c->last_error = "mean shift: label values >= 0x40000000 in the caller's grid (reserved for temporary labels); "
+                        "PCSEG_MS_GROWTH=serial has no such limit";
+        return PCSEG_ERR_UNSUPPORTED;
+      }
+    }
     const int kmax = (int)std::min<size_t>(kMsWaveMax, (size_t)S);
     size_t cap_cells = (size_t)1 << 18;   // ranks above 0: 1 MB each (rank 0 has room for every cell)
     if (const char* e = getenv("PCSEG_MS_SLOT_CAP")) cap_cells = (size_t)std::max(1, atoi(e));   // tests: force slot overflows
