@@ -148,7 +148,9 @@ int pcseg_mean_shift_sort_order(pcseg_ctx*, const float* intensities, int n, int
 
 /* Replaces ps/mean_shift_segmentation.h:207-330 SlidingMeanShift (iteration
  * phase + sort + growth).  sort_mode 0 = the reference's std::sort permutation
- * (libstdc++ introsort replayed on the device), 1 = stable.  Everything runs on the device. */
+ * (libstdc++ introsort replayed on the device), 1 = stable.  Everything runs on the device.
+ * Label values >= 0x40000000 in the caller's grid are refused (PCSEG_ERR_UNSUPPORTED): the growth
+ * phase uses that range for temporary labels (environment PCSEG_MS_GROWTH=serial lifts the limit). */
 int pcseg_mean_shift(pcseg_ctx*, const float* xyz, int rows, int cols,
                      const pcseg_cluster_config* cfg, int iterations,
                      int initial_region_id_offset, int sort_mode, int* labels,
