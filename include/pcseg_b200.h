@@ -65,7 +65,7 @@ typedef struct {
 typedef struct {
   int min_region_inliers;             /* 7   */
   float squared_distance_threshold;   /* 1.0 */
-  int half_search_window;             /* 1   (<= 3 supported) */
+  int half_search_window;             /* 1   (<= 7 supported) */
 } pcseg_cluster_config;
 
 void pcseg_default_normals_params(pcseg_normals_params*);
