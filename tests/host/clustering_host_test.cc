@@ -173,6 +173,25 @@ int main() {
     EXPECT(s_last.size() <= planes.size());
   }
 
+  // --- unorganized clustering (extension): two blobs 2 m apart and a lone point ---
+  {
+    std::vector<float> u;
+    for (int k = 0; k < 40; ++k) { u.push_back(0.01f * k); u.push_back(0.0f); u.push_back(1.0f); }
+    for (int k = 0; k < 25; ++k) { u.push_back(2.0f + 0.01f * k); u.push_back(0.5f); u.push_back(1.0f); }
+    u.push_back(9.0f); u.push_back(9.0f); u.push_back(9.0f);
+    std::vector<int> ul(66, -1);
+    std::vector<B::ClusterRegion> ur;
+    B::ClusterUnorganized(ctx, u.data(), 66, 0.1f, 5, 3, ul.data(), &ur);
+    EXPECT(ur.size() == 2);
+    if (ur.size() == 2) {
+      EXPECT(ur[0].label_id() == 3 && ur[1].label_id() == 4);
+      EXPECT(ur[0].inlier_indices().size() == 40 && ur[1].inlier_indices().size() == 25);
+      EXPECT(ur[0].Centroid() && std::fabs(ur[0].Centroid()->x - 0.195f) < 1e-5f);
+      EXPECT(ur[1].ExtentMin() && ur[1].ExtentMin()->x == 2.0f && ur[1].ExtentMax()->y == 0.5f);
+    }
+    EXPECT(ul[0] == 3 && ul[64] == 4 && ul[65] == -1);
+  }
+
   if (g_failures == 0) std::printf("PASS clustering_host_test: %zu clusters, %zu planes, %zu mean-shift regions\n",
                                    regions.size(), planes.size(), ms.size());
   return g_failures == 0 ? 0 : 1;

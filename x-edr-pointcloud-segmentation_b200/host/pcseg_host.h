@@ -181,12 +181,16 @@ class ClusterRegion {
   const std::vector<int>& inlier_indices() const { return inlier_indices_; }
   int label_id() const { return label_id_; }
   const std::optional<Float3>& Seed() const { return seed_; }
+  // ClusterUnorganized only (no counterpart in the reference): centroid and axis-aligned extent
+  const std::optional<Float3>& Centroid() const { return centroid_; }
+  const std::optional<Float3>& ExtentMin() const { return extent_min_; }
+  const std::optional<Float3>& ExtentMax() const { return extent_max_; }
 
  private:
   friend struct RegionAccess;
   int label_id_ = 0;
   std::vector<int> inlier_indices_;
-  std::optional<Float3> seed_;
+  std::optional<Float3> seed_, centroid_, extent_min_, extent_max_;
 };
 
 // Fills the region objects from a C-ABI result handle.
@@ -232,6 +236,16 @@ struct RegionAccess {
         const float* s = pcseg_regions_seed_points(r) + 3 * k;
         c.seed_ = Float3{s[0], s[1], s[2]};
       }
+    }
+  }
+  static void FillStats(const pcseg_regions* r, std::vector<ClusterRegion>* out) {
+    const float* cen = pcseg_regions_centroids(r);
+    const float* box = pcseg_regions_bboxes(r);
+    for (size_t k = 0; k < out->size(); ++k) {
+      ClusterRegion& c = (*out)[k];
+      c.centroid_ = Float3{cen[3 * k], cen[3 * k + 1], cen[3 * k + 2]};
+      c.extent_min_ = Float3{box[6 * k], box[6 * k + 1], box[6 * k + 2]};
+      c.extent_max_ = Float3{box[6 * k + 3], box[6 * k + 4], box[6 * k + 5]};
     }
   }
 };
@@ -322,6 +336,22 @@ void SegmentRegions(Context& ctx, const PointsT& points, const std::vector<int>&
                                       initial_id_offset, labels->Data(), &r),
                 "SegmentRegions<ClusterRegion>");
   RegionAccess::Fill(r, regions, false);
+  pcseg_regions_free(r);
+}
+
+// No counterpart in the reference (it clusters organized grids only): fixed-radius Euclidean clustering of an
+// UNORGANIZED cloud of n points (xyz: 3 floats each) through a voxel hash, pcseg_cluster_unorganized.
+// labels (n ints, in/out): points with another value than kUnlabeled (-1) do not take part.
+inline void ClusterUnorganized(Context& ctx, const float* xyz, int n, float radius, int min_region_inliers,
+                               int initial_id_offset, int* labels, std::vector<ClusterRegion>* regions) {
+  if (!regions || !labels || !xyz) CheckOk(ctx.get(), PCSEG_ERR_NULL, "ClusterUnorganized");
+  pcseg_voxel_cluster_config cfg;
+  cfg.radius = radius;
+  cfg.min_region_inliers = min_region_inliers;
+  pcseg_regions* r = nullptr;
+  CheckOk(ctx.get(), pcseg_cluster_unorganized(ctx.get(), xyz, n, &cfg, initial_id_offset, labels, &r), "ClusterUnorganized");
+  RegionAccess::Fill(r, regions, false);
+  RegionAccess::FillStats(r, regions);
   pcseg_regions_free(r);
 }
 
